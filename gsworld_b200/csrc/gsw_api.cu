@@ -1,0 +1,484 @@
+// gsw_api.cu — extern "C" entry points of libgsw.so and launch orchestration.  See include/gsw.h.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "gsw_internal.h"
+
+namespace gsw {
+
+thread_local std::string g_last_error;
+
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+}
+
+int DevBuf::reserve(size_t need) {
+  if (need <= bytes) return 0;
+  if (p) {
+    cudaError_t e = cudaFree(p);  // synchronises: no kernel still uses the old block afterwards
+    p = nullptr;
+    bytes = 0;
+    if (e != cudaSuccess) {
+      set_error("cudaFree failed: %s", cudaGetErrorString(e));
+      return (int)e;
+    }
+  }
+  const size_t want = (need + 255) & ~(size_t)255;
+  cudaError_t e = cudaMalloc(&p, want);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    set_error("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+    return (int)e;
+  }
+  bytes = want;
+  return 0;
+}
+
+void DevBuf::release() {
+  if (p) cudaFree(p);
+  p = nullptr;
+  bytes = 0;
+}
+
+int launch_blend_bgdev(const gsw_ctx* ctx, const FrameGeom& g, const float* bg_dev, float* out_color,
+                       float* out_invdepth, cudaStream_t s);
+
+namespace {
+
+int ilog2(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return l;
+}
+
+FrameGeom make_geom(int H, int W, int nb, int antialiasing, float scale_modifier, float near_plane) {
+  FrameGeom g{};
+  g.H = H;
+  g.W = W;
+  g.gx = (W + kTile - 1) / kTile;
+  g.gy = (H + kTile - 1) / kTile;
+  g.T = g.gx * g.gy;
+  g.NB = nb;
+  g.nb_shift = kDepthSpanLog2 - ilog2(nb);
+  g.antialiasing = antialiasing;
+  g.prefiltered = 0;
+  g.scale_modifier = scale_modifier;
+  g.near_plane = near_plane;
+  return g;
+}
+
+struct Guard {  // make ctx->device current for the duration of a call
+  int prev = -1;
+  bool ok = true;
+  explicit Guard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~Guard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// Shared body of gsw_render_frames / gsw_rasterize_forward once the layer inputs are known.
+int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussArrays* dyn, int64_t Nm, int32_t V,
+                 int32_t F, const FrameGeom& g, const float* view, const float* proj, const float* campos,
+                 const float* tanfov, const int32_t* frame_env, const int32_t* frame_view, const float* pose,
+                 int32_t num_slots, cudaStream_t s) {
+  auto& w = ctx->ws;
+  const int64_t items = (int64_t)V * N + (int64_t)F * Nm;
+  const int64_t nbins = (int64_t)(V + F) * g.T * g.NB;
+  const int64_t FT = (int64_t)F * g.T;
+  if (nbins >= (int64_t)1 << 31 || items >= (int64_t)1 << 40) {
+    set_error("launch too large: %lld bins, %lld items (split the frames into several calls)", (long long)nbins,
+              (long long)items);
+    return GSW_E_INVALID;
+  }
+  if (ctx->cap_entries == 0) ctx->cap_entries = items > (4 << 20) ? items : (4 << 20);
+  if (ctx->cap_entries >= ((int64_t)1 << 32) - 1) ctx->cap_entries = ((int64_t)1 << 32) - 2;
+  const int64_t cap = ctx->cap_entries;
+  int rc;
+  const size_t it = (size_t)(items > 0 ? items : 1);
+  if ((rc = w.recA.reserve(it * 16)) || (rc = w.recB.reserve(it * 16)) || (rc = w.recC.reserve(it * 16)) ||
+      (rc = w.rad.reserve(it * 4)))
+    return rc;
+  if ((rc = w.bin_count.reserve((size_t)(nbins + 1) * 4)) || (rc = w.bin_off.reserve((size_t)(nbins + 1) * 4)) ||
+      (rc = w.bin_cursor.reserve((size_t)(nbins + 1) * 4)))
+    return rc;
+  const int64_t scan_n = nbins > FT ? nbins : FT;
+  if ((rc = w.scan_tmp.reserve(scan_tmp_elems(scan_n) * 4))) return rc;
+  const int64_t mc = (FT > g.T ? FT : g.T) + 1;
+  if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4)) ||
+      (rc = w.tdesc.reserve((size_t)(FT > 0 ? FT : 1) * sizeof(TileDesc))))
+    return rc;
+  if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
+  if ((rc = w.status.reserve(64))) return rc;
+
+  GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
+  GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
+  GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 64, s));
+
+  if ((rc = launch_preprocess(ctx, false, stat, N, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
+                              pose, num_slots, s)))
+    return rc;
+  if (dyn && Nm > 0)
+    if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * N, g, view, proj, campos, tanfov, frame_env,
+                                frame_view, pose, num_slots, s)))
+      return rc;
+  if ((rc = launch_scan_u32(w.bin_count.as<uint32_t>(), w.bin_off.as<uint32_t>(), nbins, w.scan_tmp.as<uint32_t>(),
+                            s)))
+    return rc;
+  if ((rc = launch_scatter(ctx, false, stat, N, V, 0, 0, g, cap, s))) return rc;
+  if (dyn && Nm > 0)
+    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * N, g, cap, s))) return rc;
+  if ((rc = launch_sort_bins(ctx, nbins, V, N, Nm, g, cap, s))) return rc;
+  if ((rc = launch_merge(ctx, V, F, g, frame_view, nbins, cap, s))) return rc;
+
+  ctx->last.valid = true;
+  ctx->last.V = V;
+  ctx->last.F = F;
+  ctx->last.N = N;
+  ctx->last.Nm = Nm;
+  ctx->last.g = g;
+  ctx->last.stat = stat;
+  ctx->last.frame_env = frame_env;
+  ctx->last.frame_view = frame_view;
+  return 0;
+}
+
+int finish_launch(gsw_ctx* ctx, cudaStream_t s) {
+  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 3 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaEventRecord(ctx->done_evt, s));
+  ctx->launches++;
+  return 0;
+}
+
+}  // namespace
+}  // namespace gsw
+
+using namespace gsw;
+
+extern "C" {
+
+int gsw_version(void) { return GSW_VERSION; }
+
+const char* gsw_last_error(void) { return g_last_error.c_str(); }
+
+int gsw_create(int device, gsw_ctx** out) {
+  if (!out) {
+    set_error("gsw_create: out is NULL");
+    return GSW_E_INVALID;
+  }
+  *out = nullptr;
+  int ndev = 0;
+  GSW_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) {
+    set_error("gsw_create: device %d out of range (have %d)", device, ndev);
+    return GSW_E_INVALID;
+  }
+  Guard gd(device);
+  gsw_ctx* c = new gsw_ctx();
+  c->device = device;
+  cudaError_t e = cudaMallocHost((void**)&c->h_status, 8 * sizeof(int64_t));
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->done_evt, cudaEventDisableTiming);
+  if (e != cudaSuccess) {
+    set_error("gsw_create: %s", cudaGetErrorString(e));
+    delete c;
+    return (int)e;
+  }
+  memset(c->h_status, 0, 8 * sizeof(int64_t));
+  *out = c;
+  return GSW_OK;
+}
+
+int gsw_destroy(gsw_ctx* c) {
+  if (!c) return GSW_OK;
+  Guard gd(c->device);
+  cudaDeviceSynchronize();
+  auto& w = c->ws;
+  DevBuf* bufs[] = {&w.recA, &w.recB, &w.recC, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
+                    &w.keys, &w.splats, &w.tdesc, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
+                    &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos};
+  for (DevBuf* b : bufs) b->release();
+  if (c->h_status) cudaFreeHost(c->h_status);
+  if (c->done_evt) cudaEventDestroy(c->done_evt);
+  delete c;
+  return GSW_OK;
+}
+
+int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_act, const float* quat_act,
+                  const float* opacity_act, const float* sh, const float* log_scale_raw, const float* quat_raw,
+                  const int32_t* slot, int num_slots, gsw_stream stream) {
+  if (!c || N < 0 || N >= ((int64_t)1 << 31) || (N > 0 && (!xyz || !scale_act || !quat_act || !opacity_act || !sh))) {
+    set_error("gsw_scene_set: invalid argument");
+    return GSW_E_INVALID;
+  }
+  if (num_slots < 0 || num_slots > 512) {
+    set_error("gsw_scene_set: num_slots %d out of range [0,512]", num_slots);
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  c->have_scene = false;
+  c->last.valid = false;
+  c->N = N;
+  c->num_slots = num_slots;
+  c->scene = GaussArrays{};
+  c->scene.xyz = xyz;
+  c->scene.scale_act = scale_act;
+  c->scene.quat_act = quat_act;
+  c->scene.opacity = opacity_act;
+  c->scene.sh = sh;
+  c->scene.log_scale_raw = log_scale_raw;
+  c->scene.quat_raw = quat_raw;
+  c->scene.slot = slot;
+  c->scene.sh_degree = 3;
+  c->scene.M = 16;
+  c->Nm = 0;
+  if (slot && num_slots > 0 && N > 0) {
+    if (!log_scale_raw || !quat_raw) {
+      set_error("gsw_scene_set: log_scale_raw/quat_raw are required when slots are given");
+      return GSW_E_INVALID;
+    }
+    std::vector<int32_t> h((size_t)N);
+    GSW_CUDA(cudaMemcpyAsync(h.data(), slot, (size_t)N * 4, cudaMemcpyDeviceToHost, s));
+    GSW_CUDA(cudaStreamSynchronize(s));
+    std::vector<int32_t> idx, pos((size_t)N, -1);
+    for (int64_t i = 0; i < N; ++i) {
+      if (h[i] >= num_slots) {
+        set_error("gsw_scene_set: slot[%lld] = %d >= num_slots %d", (long long)i, h[i], num_slots);
+        return GSW_E_INVALID;
+      }
+      if (h[i] >= 0) {
+        pos[i] = (int32_t)idx.size();
+        idx.push_back((int32_t)i);
+      }
+    }
+    const int64_t Nm = (int64_t)idx.size();
+    int rc;
+    if ((rc = c->mov_pos.reserve((size_t)N * 4))) return rc;
+    GSW_CUDA(cudaMemcpyAsync(c->mov_pos.p, pos.data(), (size_t)N * 4, cudaMemcpyHostToDevice, s));
+    if (Nm > 0) {
+      const size_t m = (size_t)Nm;
+      if ((rc = c->mov_idx.reserve(m * 4)) || (rc = c->mov_xyz.reserve(m * 12)) ||
+          (rc = c->mov_scale_act.reserve(m * 12)) || (rc = c->mov_opacity.reserve(m * 4)) ||
+          (rc = c->mov_sh.reserve(m * 192)) || (rc = c->mov_log_scale.reserve(m * 12)) ||
+          (rc = c->mov_quat_raw.reserve(m * 16)) || (rc = c->mov_slot.reserve(m * 4)))
+        return rc;
+      GSW_CUDA(cudaMemcpyAsync(c->mov_idx.p, idx.data(), m * 4, cudaMemcpyHostToDevice, s));
+      c->Nm = Nm;
+      if ((rc = launch_gather_movable(c, s))) return rc;
+    }
+    GSW_CUDA(cudaStreamSynchronize(s));  // host staging vectors go out of scope
+  } else {
+    c->scene.slot = nullptr;
+  }
+  c->have_scene = true;
+  return GSW_OK;
+}
+
+int gsw_set_depth_buckets(gsw_ctx* c, int nb) {
+  if (!c || nb < 0 || nb > 64 || (nb & (nb - 1))) {
+    set_error("gsw_set_depth_buckets: nb must be 0 or a power of two <= 64");
+    return GSW_E_INVALID;
+  }
+  c->nb_user = nb;
+  return GSW_OK;
+}
+
+int gsw_reserve_entries(gsw_ctx* c, int64_t entries) {
+  if (!c || entries < 0) {
+    set_error("gsw_reserve_entries: invalid argument");
+    return GSW_E_INVALID;
+  }
+  if (entries > c->cap_entries) c->cap_entries = entries;
+  return GSW_OK;
+}
+
+int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
+  if (!c || !d) {
+    set_error("gsw_render_frames: NULL argument");
+    return GSW_E_INVALID;
+  }
+  if (!c->have_scene) {
+    set_error("gsw_render_frames: call gsw_scene_set first");
+    return GSW_E_STATE;
+  }
+  if (d->num_frames <= 0 || d->num_views <= 0 || d->num_envs <= 0 || d->height <= 0 || d->width <= 0 ||
+      d->num_frames > 65535 || d->num_views > 65535) {
+    set_error("gsw_render_frames: bad sizes (B=%d V=%d F=%d H=%d W=%d)", d->num_envs, d->num_views, d->num_frames,
+              d->height, d->width);
+    return GSW_E_INVALID;
+  }
+  if (!d->viewmatrix || !d->projmatrix || !d->campos || !d->tanfov || !d->frame_env || !d->frame_view ||
+      (c->Nm > 0 && !d->pose)) {
+    set_error("gsw_render_frames: missing camera / frame map / pose pointer");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int nb = c->nb_user > 0 ? c->nb_user : 1;
+  const FrameGeom g = make_geom(d->height, d->width, nb, d->antialiasing, d->scale_modifier, d->near_plane);
+
+  GaussArrays dyn{};
+  dyn.xyz = c->mov_xyz.as<float>();
+  dyn.scale_act = c->mov_scale_act.as<float>();
+  dyn.opacity = c->mov_opacity.as<float>();
+  dyn.sh = c->mov_sh.as<float>();
+  dyn.log_scale_raw = c->mov_log_scale.as<float>();
+  dyn.quat_raw = c->mov_quat_raw.as<float>();
+  dyn.mov_slot = c->mov_slot.as<int32_t>();
+  dyn.mov_idx = c->mov_idx.as<int32_t>();
+  dyn.sh_degree = 3;
+  dyn.M = 16;
+
+  int rc = run_pipeline(c, c->scene, c->N, &dyn, c->Nm, d->num_views, d->num_frames, g, d->viewmatrix,
+                        d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s);
+  if (rc) return rc;
+  c->last.single = false;
+  if ((rc = launch_blend(c, d->num_frames, g, d->bg, d->out_rgb_u8, d->out_color, d->out_invdepth, s))) return rc;
+  if (d->out_radii)
+    if ((rc = launch_radii(c, d->out_radii, s))) return rc;
+  return finish_launch(c, s);
+}
+
+int gsw_finish(gsw_ctx* c, int64_t* needed_entries, int64_t stats[4]) {
+  if (!c) {
+    set_error("gsw_finish: NULL ctx");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  GSW_CUDA(cudaEventSynchronize(c->done_evt));
+  const int64_t D = c->h_status[0], M = c->h_status[1], ovf = c->h_status[2];
+  if (needed_entries) *needed_entries = D + M;
+  if (stats) {
+    stats[0] = D;
+    stats[1] = M;
+    stats[2] = c->cap_entries;
+    stats[3] = c->launches;
+  }
+  if (ovf) {
+    set_error("tile-entry workspace overflow: need %lld entries, capacity %lld", (long long)(D + M),
+              (long long)c->cap_entries);
+    return GSW_E_CAPACITY;
+  }
+  return GSW_OK;
+}
+
+int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, const float* bg, int32_t width,
+                          int32_t height, const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                          const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                          const float* campos, float tan_fovx, float tan_fovy, int32_t prefiltered,
+                          int32_t antialiasing, float near_plane, float* out_color, int32_t* out_radii,
+                          float* out_invdepth, gsw_stream stream) {
+  if (!c || P < 0 || width <= 0 || height <= 0 || !bg || !viewmatrix || !projmatrix || !campos) {
+    set_error("gsw_rasterize_forward: invalid argument");
+    return GSW_E_INVALID;
+  }
+  if ((shs == nullptr) == (colors_precomp == nullptr)) {
+    set_error("Please provide excatly one of either SHs or precomputed colors!");
+    return GSW_E_INVALID;
+  }
+  if (((scales == nullptr || rotations == nullptr) && cov3D_precomp == nullptr) ||
+      ((scales != nullptr || rotations != nullptr) && cov3D_precomp != nullptr)) {
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return GSW_E_INVALID;
+  }
+  if (shs && (sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1))) {
+    set_error("gsw_rasterize_forward: sh_degree %d needs M >= %d (got %d); degree <= 3 supported", sh_degree,
+              (sh_degree + 1) * (sh_degree + 1), M);
+    return GSW_E_INVALID;
+  }
+  (void)prefiltered;
+  Guard gd(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t HW = (size_t)height * width;
+  if (P == 0) {  // upstream leaves the zero-initialised outputs untouched when there is nothing to draw
+    if (out_color) GSW_CUDA(cudaMemsetAsync(out_color, 0, 3 * HW * 4, s));
+    if (out_invdepth) GSW_CUDA(cudaMemsetAsync(out_invdepth, 0, HW * 4, s));
+    c->last.valid = false;
+    return GSW_OK;
+  }
+  const int nb = c->nb_user > 0 ? c->nb_user : 1;
+  const FrameGeom g = make_geom(height, width, nb, antialiasing, scale_modifier, near_plane);
+  GaussArrays st{};
+  st.xyz = means3D;
+  st.scale_act = scales;
+  st.quat_act = rotations;
+  st.opacity = opacities;
+  st.sh = shs;
+  st.colors_precomp = colors_precomp;
+  st.cov3d_precomp = cov3D_precomp;
+  st.slot = nullptr;
+  st.sh_degree = sh_degree;
+  st.M = M;
+  // tan(fov) and the trivial frame maps live in a small staging block: [tanx, tany, 0(int), 0(int)]
+  int rc;
+  if ((rc = c->ws.cam.reserve(64))) return rc;
+  struct {
+    float tx, ty;
+    int32_t e, v;
+  } hs{tan_fovx, tan_fovy, 0, 0};
+  GSW_CUDA(cudaMemcpyAsync(c->ws.cam.p, &hs, sizeof hs, cudaMemcpyHostToDevice, s));  // pageable: staged by the driver
+  const float* tanfov = c->ws.cam.as<float>();
+  const int32_t* fe = c->ws.cam.as<int32_t>() + 2;
+  const int32_t* fv = c->ws.cam.as<int32_t>() + 3;
+  rc = run_pipeline(c, st, P, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv, nullptr, 0, s);
+  if (rc) return rc;
+  c->last.single = true;
+  if ((rc = launch_blend_bgdev(c, g, bg, out_color, out_invdepth, s))) return rc;
+  if (out_radii)
+    if ((rc = launch_radii(c, out_radii, s))) return rc;
+  return finish_launch(c, s);
+}
+
+int gsw_mark_visible(gsw_ctx* c, int32_t P, const float* means3D, const float* viewmatrix, float near_plane,
+                     uint8_t* out_visible, gsw_stream stream) {
+  if (!c || P < 0 || (P > 0 && (!means3D || !out_visible)) || !viewmatrix) {
+    set_error("gsw_mark_visible: invalid argument");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  return launch_mark_visible(P, means3D, viewmatrix, near_plane, out_visible, (cudaStream_t)stream);
+}
+
+int gsw_debug_frame_attrs(gsw_ctx* c, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth, float* xy,
+                          float* conic_opacity, float* rgb, gsw_stream stream) {
+  if (!c || !c->last.valid || frame < 0 || frame >= c->last.F) {
+    set_error("gsw_debug_frame_attrs: no valid launch / frame out of range");
+    return GSW_E_STATE;
+  }
+  Guard gd(c->device);
+  return launch_frame_attrs(c, frame, radii, tiles_touched, depth, xy, conic_opacity, rgb, (cudaStream_t)stream);
+}
+
+int gsw_debug_frame_lists(gsw_ctx* c, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals, int64_t cap,
+                          int64_t* count, gsw_stream stream) {
+  if (!c || !c->last.valid || frame < 0 || frame >= c->last.F || !ranges || !keys || !vals) {
+    set_error("gsw_debug_frame_lists: no valid launch / bad argument");
+    return GSW_E_STATE;
+  }
+  Guard gd(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = launch_frame_lists(c, frame, ranges, keys, vals, cap, s);
+  if (rc) return rc;
+  uint32_t total = 0;
+  GSW_CUDA(cudaMemcpyAsync(&total, c->ws.merge_off.as<uint32_t>() + c->last.g.T, 4, cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaStreamSynchronize(s));
+  if (count) *count = total;
+  if ((int64_t)total > cap) {
+    set_error("gsw_debug_frame_lists: need %u entries, cap %lld", total, (long long)cap);
+    return GSW_E_CAPACITY;
+  }
+  return GSW_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,160 @@
+// gsw_internal.h — shared declarations of libgsw.so (not installed).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/gsw.h"
+
+namespace gsw {
+
+constexpr int kTile = 16;           // 16x16 pixel tiles, as the reference rasterizer (BLOCK_X/BLOCK_Y)
+constexpr int kSortSmemKeys = 8192; // largest bin sorted in shared memory (64 KB of u64 keys)
+
+void set_error(const char* fmt, ...);
+extern thread_local std::string g_last_error;
+
+#define GSW_CUDA(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      ::gsw::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return (int)_e;                                                                    \
+    }                                                                                    \
+  } while (0)
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int reserve(size_t need);  // returns 0 / cudaError
+  void release();
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Stream record consumed by the blend kernel: 48 B, three float4.
+//   a = {px, py, hx, hy}   pixel centre and half extents of the alpha >= 1/255 footprint (cull box)
+//   b = {conic.x, conic.y, conic.z, opacity}
+//   c = {r, g, b, 1/depth}
+struct Splat {
+  float4 a, b, c;
+};
+
+// Where a (frame, tile) list lives inside the stream buffers.
+struct TileDesc {
+  uint32_t offset;
+  uint32_t count;
+};
+
+// Inputs of one preprocess "layer" launch.
+struct GaussArrays {
+  const float* xyz;            // [n,3]
+  const float* scale_act;      // [n,3] or null (cov3d given)
+  const float* quat_act;       // [n,4] or null
+  const float* opacity;        // [n]
+  const float* sh;             // [n,M,3] or null
+  const float* colors_precomp; // [n,3] or null
+  const float* cov3d_precomp;  // [n,6] or null
+  const int32_t* slot;         // static layer: skip entries with slot >= 0 (null: none skipped)
+  // dynamic layer only
+  const float* log_scale_raw;  // [n,3]
+  const float* quat_raw;       // [n,4]
+  const int32_t* mov_slot;     // [n]
+  const int32_t* mov_idx;      // [n] original index
+  int32_t sh_degree;
+  int32_t M;
+};
+
+struct FrameGeom {
+  int32_t H, W, gx, gy, T;  // tiles
+  int32_t NB, nb_shift;     // depth sub-buckets per tile, shift applied to (depth_bits - kDepthLo)
+  int32_t antialiasing;
+  int32_t prefiltered;
+  float scale_modifier;
+  float near_plane;
+};
+
+constexpr uint32_t kDepthLo = 0x3D000000u;  // 2^-5; sub-buckets span [2^-5, 2^3) in float-bit space
+constexpr int kDepthSpanLog2 = 26;
+
+struct Workspace {
+  // per-item preprocess results; items = [V*N static | F*Nm dynamic]
+  DevBuf recA, recB, recC, rad;
+  // bins: (list, tile, bucket); lists = [V static | F dynamic]
+  DevBuf bin_count, bin_off, bin_cursor, scan_tmp;
+  // tile entries
+  DevBuf keys;    // u64 [(cap_entries + cap_merged)]
+  DevBuf splats;  // Splat [(cap_entries + cap_merged)]
+  DevBuf tdesc;   // TileDesc [F*T]
+  DevBuf merge_cnt, merge_off;  // u32 [F*T + 1]
+  DevBuf status;  // device status words
+  DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
+};
+
+}  // namespace gsw
+
+struct gsw_ctx {
+  int device = 0;
+  // scene
+  int64_t N = 0;
+  int32_t num_slots = 0;
+  int64_t Nm = 0;  // movable count
+  gsw::GaussArrays scene{};
+  gsw::DevBuf mov_xyz, mov_scale_act, mov_opacity, mov_sh, mov_log_scale, mov_quat_raw, mov_slot, mov_idx, mov_pos;
+  bool have_scene = false;
+  // workspace
+  gsw::Workspace ws;
+  int64_t cap_entries = 0;  // capacity of [sorted lists | merged lists] combined
+  int nb_user = 0;
+  // last launch
+  struct {
+    bool valid = false;
+    bool single = false;  // gsw_rasterize_forward launch (scene arrays are the caller's)
+    int32_t V = 0, F = 0;
+    int64_t N = 0, Nm = 0;
+    gsw::FrameGeom g{};
+    gsw::GaussArrays stat{};
+    const int32_t* frame_env = nullptr;
+    const int32_t* frame_view = nullptr;
+  } last;
+  int64_t* h_status = nullptr;  // pinned: [0]=D, [1]=merged, [2]=overflow flag
+  cudaEvent_t done_evt = nullptr;
+  int64_t launches = 0;
+};
+
+namespace gsw {
+
+// ---- kernels (host launchers) ----
+// preprocess.cu  (compiled with -fmad=false: every fp32 op rounds once, like the CPU oracle)
+int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
+                      int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
+                      const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
+                      const float* pose, int32_t num_slots, cudaStream_t s);
+int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
+                   int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, cudaStream_t s);
+int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,
+                       float* xy, float* conic_opacity, float* rgb, cudaStream_t s);
+int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s);
+int launch_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, float near_plane, uint8_t* out,
+                        cudaStream_t s);
+int launch_gather_movable(const gsw_ctx* ctx, cudaStream_t s);
+
+// binsort.cu
+int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s);
+int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, int64_t Nm, const FrameGeom& g,
+                     int64_t cap, cudaStream_t s);
+int launch_merge(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, const int32_t* frame_view,
+                 int64_t nbins, int64_t cap, cudaStream_t s);
+int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
+                       int64_t cap, cudaStream_t s);
+
+// blend.cu
+int launch_blend(const gsw_ctx* ctx, int32_t F, const FrameGeom& g, const float bg[3], uint8_t* out_u8,
+                 float* out_color, float* out_invdepth, cudaStream_t s);
+
+size_t scan_tmp_elems(int64_t n);
+
+}  // namespace gsw

@@ -1,0 +1,548 @@
+// preprocess.cu — per-Gaussian stage: (optional) rigid transform, EWA projection, cull, SH colour,
+// tile-bin counting and key scatter.  sm_100a.
+//
+// COMPILED WITH -fmad=false.  radii, tile counts, depth bits and pixel positions are integer/bit-exact
+// parity quantities, so every fp32 operation here must round once, in the order the CPU oracle
+// (oracle/gsw_oracle.cpp) and the published rasterizer write it.  The stage is HBM-bound (45 B read per
+// Gaussian, 236 B more per visible one), so the un-fused multiplies cost nothing measurable.
+//
+// Reference for the arithmetic: diff-gaussian-rasterization@9c5c2028 forward.cu preprocessCUDA /
+// computeCov3D / computeCov2D / computeColorFromSH and auxiliary.h (absent submodule; see include/gsw.h),
+// near plane per GSWorld README.md:33; transform per gsworld/utils/gs_utils.py:283-385.
+#include "gsw_internal.h"
+
+namespace gsw {
+namespace {
+
+__device__ __constant__ float kC0 = 0.28209479177387814f;
+__device__ __constant__ float kC1 = 0.4886025119029199f;
+__device__ __constant__ float kC2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                        -1.0925484305920792f, 0.5462742152960396f};
+__device__ __constant__ float kC3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                        0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
+                                        -0.5900435899266435f};
+
+struct M3 {  // m[c][r], glm-style column major
+  float m[3][3];
+};
+
+__device__ __forceinline__ M3 mul3(const M3& a, const M3& b) {
+  M3 o;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      float s = a.m[0][r] * b.m[c][0];
+      s = s + a.m[1][r] * b.m[c][1];
+      s = s + a.m[2][r] * b.m[c][2];
+      o.m[c][r] = s;
+    }
+  return o;
+}
+
+__device__ __forceinline__ M3 tr3(const M3& a) {
+  M3 o;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) o.m[c][r] = a.m[r][c];
+  return o;
+}
+
+__device__ __forceinline__ float ndc2pix(float v, int S) {
+  return (float)((((double)v + 1.0) * (double)S - 1.0) * 0.5);
+}
+
+struct Rect {
+  int x0, y0, x1, y1;
+};
+
+__device__ __forceinline__ Rect tile_rect(float px, float py, int radius, int gx, int gy) {
+  const float r = (float)radius;
+  Rect q;
+  q.x0 = min(gx, max(0, (int)((px - r) / (float)kTile)));
+  q.y0 = min(gy, max(0, (int)((py - r) / (float)kTile)));
+  q.x1 = min(gx, max(0, (int)((px + r + (float)(kTile - 1)) / (float)kTile)));
+  q.y1 = min(gy, max(0, (int)((py + r + (float)(kTile - 1)) / (float)kTile)));
+  return q;
+}
+
+__device__ __forceinline__ uint32_t depth_bucket(float depth, const FrameGeom& g) {
+  const uint32_t bits = __float_as_uint(depth);
+  if (bits <= kDepthLo) return 0u;
+  return min((uint32_t)(g.NB - 1), (bits - kDepthLo) >> g.nb_shift);
+}
+
+struct ViewSmem {
+  float V[16], P[16], cam[3], tanx, tany;
+};
+
+// One colour channel of the degree<=3 SH polynomial, same association as the published kernel.
+template <typename F>
+__device__ __forceinline__ float sh_channel(int deg, float x, float y, float z, F S) {
+  float res = kC0 * S(0);
+  if (deg > 0) {
+    res = res - kC1 * y * S(1) + kC1 * z * S(2) - kC1 * x * S(3);
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z;
+      const float xy = x * y, yz = y * z, xz = x * z;
+      res = res + kC2[0] * xy * S(4) + kC2[1] * yz * S(5) + kC2[2] * (2.0f * zz - xx - yy) * S(6) +
+            kC2[3] * xz * S(7) + kC2[4] * (xx - yy) * S(8);
+      if (deg > 2) {
+        res = res + kC3[0] * y * (3.0f * xx - yy) * S(9) + kC3[1] * xy * z * S(10) +
+              kC3[2] * y * (4.0f * zz - xx - yy) * S(11) +
+              kC3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * S(12) +
+              kC3[4] * x * (4.0f * zz - xx - yy) * S(13) + kC3[5] * z * (xx - yy) * S(14) +
+              kC3[6] * x * (xx - 3.0f * yy) * S(15);
+      }
+    }
+  }
+  res += 0.5f;
+  return fmaxf(res, 0.0f);
+}
+
+// grid: (ceil(n_items/256), n_lists); list = view (static layer) or frame (dynamic layer)
+template <bool DYN>
+__global__ void __launch_bounds__(256)
+preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
+                  const float* __restrict__ views, const float* __restrict__ projs,
+                  const float* __restrict__ campos, const float* __restrict__ tanfov,
+                  const int32_t* __restrict__ frame_env, const int32_t* __restrict__ frame_view,
+                  const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
+                  float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
+                  uint32_t* __restrict__ bin_count) {
+  __shared__ ViewSmem vs;
+  extern __shared__ float pose_s[];  // DYN: [num_slots][GSW_POSE_STRIDE]
+  const int list = blockIdx.y;
+  int view = list, env = 0;
+  if (DYN) {
+    view = frame_view[list];
+    env = frame_env[list];
+  }
+  if (threadIdx.x < 16) {
+    vs.V[threadIdx.x] = views[view * 16 + threadIdx.x];
+    vs.P[threadIdx.x] = projs[view * 16 + threadIdx.x];
+  } else if (threadIdx.x < 19) {
+    vs.cam[threadIdx.x - 16] = campos[view * 3 + threadIdx.x - 16];
+  } else if (threadIdx.x == 19) {
+    vs.tanx = tanfov[view * 2];
+  } else if (threadIdx.x == 20) {
+    vs.tany = tanfov[view * 2 + 1];
+  }
+  if (DYN) {
+    for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
+      pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
+  }
+  __syncthreads();
+
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_items) return;
+  const int64_t item = item_base + (int64_t)list * n_items + i;
+  if (!DYN && ga.slot != nullptr && ga.slot[i] >= 0) {  // movable: handled by the dynamic layer
+    rad[item] = 0;
+    return;
+  }
+
+  float p[3] = {ga.xyz[3 * i], ga.xyz[3 * i + 1], ga.xyz[3 * i + 2]};
+  float sc[3] = {0.f, 0.f, 0.f};
+  float q[4] = {1.f, 0.f, 0.f, 0.f};
+  const bool have_cov = (!DYN) && ga.cov3d_precomp != nullptr;
+
+  if (DYN) {
+    // ---- rigid transform of a movable Gaussian (gs_utils.py:283-385 order: scale, rotate, translate) ----
+    const float* ps = pose_s + ga.mov_slot[i] * GSW_POSE_STRIDE;
+    const float kappa = ps[16];
+    const bool has_scale = ps[17] != 0.f;
+    if (has_scale) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        p[k] = p[k] * kappa;
+        const float u = expf(ga.log_scale_raw[3 * i + k]) * kappa;
+        const float ls = logf(u / (1.0f - u));  // inverse_sigmoid, the reference behaviour (gs_utils.py:310)
+        sc[k] = expf(ls);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) sc[k] = ga.scale_act[3 * i + k];
+    }
+    float rp[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) rp[r] = ps[3 * r] * p[0] + ps[3 * r + 1] * p[1] + ps[3 * r + 2] * p[2];
+    const float4 qr = reinterpret_cast<const float4*>(ga.quat_raw)[i];
+    const float nrm = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
+    const float bw = qr.x / nrm, bx = qr.y / nrm, by = qr.z / nrm, bz = qr.w / nrm;
+    const float aw = ps[12], ax = ps[13], ay = ps[14], az = ps[15];
+    float ow = aw * bw - ax * bx - ay * by - az * bz;
+    float ox = aw * bx + ax * bw + ay * bz - az * by;
+    float oy = aw * by - ax * bz + ay * bw + az * bx;
+    float oz = aw * bz + ax * by - ay * bx + az * bw;
+    if (ow < 0.f) {
+      ow = -ow; ox = -ox; oy = -oy; oz = -oz;
+    }
+    const float q2[4] = {ow * nrm, ox * nrm, oy * nrm, oz * nrm};
+    const float n2 = sqrtf(q2[0] * q2[0] + q2[1] * q2[1] + q2[2] * q2[2] + q2[3] * q2[3]);
+    const float den = fmaxf(n2, 1e-12f);  // F.normalize eps (gaussian_model.py:47)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = q2[k] / den;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) p[k] = rp[k] + ps[9 + k];
+  }
+
+  // ---- near-plane cull on view-space depth ----
+  const float* V = vs.V;
+  const float pvx = V[0] * p[0] + V[4] * p[1] + V[8] * p[2] + V[12];
+  const float pvy = V[1] * p[0] + V[5] * p[1] + V[9] * p[2] + V[13];
+  const float pvz = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
+  if (pvz <= g.near_plane) {
+    rad[item] = 0;
+    return;
+  }
+  const float* P = vs.P;
+  const float phx = P[0] * p[0] + P[4] * p[1] + P[8] * p[2] + P[12];
+  const float phy = P[1] * p[0] + P[5] * p[1] + P[9] * p[2] + P[13];
+  const float phw = P[3] * p[0] + P[7] * p[1] + P[11] * p[2] + P[15];
+  const float pw = 1.0f / (phw + 0.0000001f);
+  const float ppx = phx * pw, ppy = phy * pw;
+
+  // ---- 3D covariance ----
+  float c3[6];
+  if (have_cov) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) c3[k] = ga.cov3d_precomp[6 * i + k];
+  } else {
+    if (!DYN) {
+      sc[0] = ga.scale_act[3 * i];
+      sc[1] = ga.scale_act[3 * i + 1];
+      sc[2] = ga.scale_act[3 * i + 2];
+      const float4 qq = reinterpret_cast<const float4*>(ga.quat_act)[i];
+      q[0] = qq.x; q[1] = qq.y; q[2] = qq.z; q[3] = qq.w;
+    }
+    M3 S;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) S.m[c][r] = 0.f;
+    S.m[0][0] = g.scale_modifier * sc[0];
+    S.m[1][1] = g.scale_modifier * sc[1];
+    S.m[2][2] = g.scale_modifier * sc[2];
+    const float r = q[0], x = q[1], y = q[2], z = q[3];
+    M3 R;
+    R.m[0][0] = 1.f - 2.f * (y * y + z * z);
+    R.m[0][1] = 2.f * (x * y - r * z);
+    R.m[0][2] = 2.f * (x * z + r * y);
+    R.m[1][0] = 2.f * (x * y + r * z);
+    R.m[1][1] = 1.f - 2.f * (x * x + z * z);
+    R.m[1][2] = 2.f * (y * z - r * x);
+    R.m[2][0] = 2.f * (x * z - r * y);
+    R.m[2][1] = 2.f * (y * z + r * x);
+    R.m[2][2] = 1.f - 2.f * (x * x + y * y);
+    const M3 M = mul3(S, R);
+    const M3 Sig = mul3(tr3(M), M);
+    c3[0] = Sig.m[0][0]; c3[1] = Sig.m[0][1]; c3[2] = Sig.m[0][2];
+    c3[3] = Sig.m[1][1]; c3[4] = Sig.m[1][2]; c3[5] = Sig.m[2][2];
+  }
+
+  // ---- EWA 2D covariance ----
+  const float focal_y = (float)g.H / (2.0f * vs.tany);
+  const float focal_x = (float)g.W / (2.0f * vs.tanx);
+  float tx = pvx, ty = pvy;
+  const float tz = pvz;
+  {
+    const float limx = 1.3f * vs.tanx, limy = 1.3f * vs.tany;
+    const float txtz = tx / tz, tytz = ty / tz;
+    tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+    ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+  }
+  M3 J;
+  J.m[0][0] = focal_x / tz;  J.m[0][1] = 0.f;            J.m[0][2] = -(focal_x * tx) / (tz * tz);
+  J.m[1][0] = 0.f;           J.m[1][1] = focal_y / tz;   J.m[1][2] = -(focal_y * ty) / (tz * tz);
+  J.m[2][0] = 0.f;           J.m[2][1] = 0.f;            J.m[2][2] = 0.f;
+  M3 Wm;
+  Wm.m[0][0] = V[0]; Wm.m[0][1] = V[4]; Wm.m[0][2] = V[8];
+  Wm.m[1][0] = V[1]; Wm.m[1][1] = V[5]; Wm.m[1][2] = V[9];
+  Wm.m[2][0] = V[2]; Wm.m[2][1] = V[6]; Wm.m[2][2] = V[10];
+  const M3 Tm = mul3(Wm, J);
+  M3 Vrk;
+  Vrk.m[0][0] = c3[0]; Vrk.m[0][1] = c3[1]; Vrk.m[0][2] = c3[2];
+  Vrk.m[1][0] = c3[1]; Vrk.m[1][1] = c3[3]; Vrk.m[1][2] = c3[4];
+  Vrk.m[2][0] = c3[2]; Vrk.m[2][1] = c3[4]; Vrk.m[2][2] = c3[5];
+  const M3 cov = mul3(mul3(tr3(Tm), tr3(Vrk)), Tm);
+  float cx = cov.m[0][0];
+  const float cy = cov.m[0][1];
+  float cz = cov.m[1][1];
+
+  const float det_cov = cx * cz - cy * cy;
+  cx += 0.3f;
+  cz += 0.3f;
+  const float det = cx * cz - cy * cy;
+  float h_scale = 1.0f;
+  if (g.antialiasing) h_scale = sqrtf(fmaxf(0.000025f, det_cov / det));
+  if (det == 0.0f) {
+    rad[item] = 0;
+    return;
+  }
+  const float det_inv = 1.f / det;
+  const float conx = cz * det_inv, cony = -cy * det_inv, conz = cx * det_inv;
+  const float mid = 0.5f * (cx + cz);
+  const float lam1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
+  const float lam2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
+  const float my_radius = ceilf(3.f * sqrtf(fmaxf(lam1, lam2)));
+  const float px = ndc2pix(ppx, g.W), py = ndc2pix(ppy, g.H);
+  const int radius = (int)my_radius;
+  const Rect rc = tile_rect(px, py, radius, g.gx, g.gy);
+  if ((rc.x1 - rc.x0) * (rc.y1 - rc.y0) == 0) {
+    rad[item] = 0;
+    return;
+  }
+
+  // ---- colour ----
+  float rgb[3];
+  if (!DYN && ga.colors_precomp != nullptr) {
+    rgb[0] = ga.colors_precomp[3 * i];
+    rgb[1] = ga.colors_precomp[3 * i + 1];
+    rgb[2] = ga.colors_precomp[3 * i + 2];
+  } else {
+    float dx = p[0] - vs.cam[0], dy = p[1] - vs.cam[1], dz = p[2] - vs.cam[2];
+    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+    dx = dx / len;
+    dy = dy / len;
+    dz = dz / len;
+    const float* shp = ga.sh + (size_t)i * ga.M * 3;
+    if (ga.M == 16 && ((reinterpret_cast<uintptr_t>(shp) & 15) == 0)) {
+      float c[48];
+      const float4* s4 = reinterpret_cast<const float4*>(shp);
+#pragma unroll
+      for (int k = 0; k < 12; ++k) {
+        const float4 v = __ldg(s4 + k);
+        c[4 * k] = v.x; c[4 * k + 1] = v.y; c[4 * k + 2] = v.z; c[4 * k + 3] = v.w;
+      }
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch)
+        rgb[ch] = sh_channel(ga.sh_degree, dx, dy, dz, [&](int k) { return c[3 * k + ch]; });
+    } else {
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch)
+        rgb[ch] = sh_channel(ga.sh_degree, dx, dy, dz, [&](int k) { return __ldg(shp + 3 * k + ch); });
+    }
+  }
+
+  // ---- footprint of alpha >= 1/255 (cull box for the blend; conservative, not a parity quantity) ----
+  const float opac = ga.opacity[i] * h_scale;
+  float hx, hy;
+  if (!(opac * 255.0f >= 0.999f)) {
+    hx = hy = -1.0f;  // can never reach alpha 1/255
+  } else if (!(det > 1e-4f * (cx * cz))) {
+    hx = hy = 3.0e38f;  // ill-conditioned conic: do not cull
+  } else {
+    const float tau = fmaxf(logf(opac * 255.0f), 0.f) * 1.02f + 0.05f;
+    hx = sqrtf(2.f * tau * cx) * 1.001f + 0.01f;
+    hy = sqrtf(2.f * tau * cz) * 1.001f + 0.01f;
+  }
+
+  recA[item] = make_float4(px, py, hx, hy);
+  recB[item] = make_float4(conx, cony, conz, opac);
+  recC[item] = make_float4(rgb[0], rgb[1], rgb[2], pvz);
+  rad[item] = radius;
+
+  // ---- count this Gaussian into every (tile, depth bucket) bin it touches ----
+  const uint32_t bk = depth_bucket(pvz, g);
+  const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)g.T;
+  for (int y = rc.y0; y < rc.y1; ++y)
+    for (int x = rc.x0; x < rc.x1; ++x)
+      atomicAdd(&bin_count[(lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk], 1u);
+}
+
+// Second pass: write (depth bits << 32 | original index) into the bin's slice.  Order inside a bin is
+// arbitrary here; the per-bin sort orders by the full 64-bit key, which reproduces the reference's
+// stable (tile, depth) radix sort exactly (ties on depth fall back to ascending Gaussian index).
+template <bool DYN>
+__global__ void __launch_bounds__(256)
+scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
+               const float4* __restrict__ recA, const float4* __restrict__ recC, const int32_t* __restrict__ rad,
+               const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
+               unsigned long long* __restrict__ keys, int64_t cap) {
+  const int list = blockIdx.y;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_items) return;
+  const int64_t item = item_base + (int64_t)list * n_items + i;
+  const int radius = rad[item];
+  if (radius <= 0) return;
+  const float4 a = recA[item];
+  const float depth = recC[item].w;
+  const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
+  const uint32_t idx = DYN ? (uint32_t)ga.mov_idx[i] : (uint32_t)i;
+  const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | idx;
+  const uint32_t bk = depth_bucket(depth, g);
+  const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)g.T;
+  for (int y = rc.y0; y < rc.y1; ++y)
+    for (int x = rc.x0; x < rc.x1; ++x) {
+      const uint32_t bin = (lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk;
+      const uint32_t pos = bin_off[bin] + atomicAdd(&bin_cursor[bin], 1u);
+      if ((int64_t)pos < cap) keys[pos] = key;
+    }
+}
+
+// Per-Gaussian taps of one frame, addressed by original index (parity tests / radii output).
+__global__ void frame_attrs_kernel(int64_t N, int64_t Nm, int32_t V, int32_t frame, const int32_t* frame_view,
+                                   const int32_t* slot, const int32_t* mov_pos, FrameGeom g,
+                                   const float4* recA, const float4* recB, const float4* recC, const int32_t* rad,
+                                   int32_t* radii, int32_t* tiles, float* depth, float* xy, float* conic_o,
+                                   float* rgb) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int view = frame_view ? frame_view[frame] : 0;
+  int64_t item;
+  if (slot != nullptr && slot[i] >= 0)
+    item = (int64_t)V * N + (int64_t)frame * Nm + mov_pos[i];
+  else
+    item = (int64_t)view * N + i;
+  const int r = rad[item];
+  float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
+  int tt = 0;
+  if (r > 0) {
+    a = recA[item];
+    b = recB[item];
+    c = recC[item];
+    const Rect rc = tile_rect(a.x, a.y, r, g.gx, g.gy);
+    tt = (rc.y1 - rc.y0) * (rc.x1 - rc.x0);
+  }
+  if (radii) radii[i] = r;
+  if (tiles) tiles[i] = tt;
+  if (depth) depth[i] = c.w;
+  if (xy) {
+    xy[2 * i] = a.x;
+    xy[2 * i + 1] = a.y;
+  }
+  if (conic_o) {
+    conic_o[4 * i] = b.x; conic_o[4 * i + 1] = b.y; conic_o[4 * i + 2] = b.z; conic_o[4 * i + 3] = b.w;
+  }
+  if (rgb) {
+    rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+  }
+}
+
+// radii of every frame: out[f, i]
+__global__ void radii_kernel(int64_t N, int64_t Nm, int32_t V, const int32_t* frame_view, const int32_t* slot,
+                             const int32_t* mov_pos, const int32_t* rad, int32_t* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int f = blockIdx.y;
+  const int view = frame_view ? frame_view[f] : 0;
+  int64_t item;
+  if (slot != nullptr && slot[i] >= 0)
+    item = (int64_t)V * N + (int64_t)f * Nm + mov_pos[i];
+  else
+    item = (int64_t)view * N + i;
+  out[(int64_t)f * N + i] = rad[item];
+}
+
+__global__ void mark_visible_kernel(int32_t P, const float* xyz, const float* V, float near_plane, uint8_t* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  const float pvz = V[2] * x + V[6] * y + V[10] * z + V[14];
+  out[i] = pvz > near_plane ? 1 : 0;
+}
+
+// compact copy of the movable Gaussians, made once per scene upload
+__global__ void gather_movable_kernel(int64_t Nm, const int32_t* mov_idx, GaussArrays sc, float* xyz, float* scale,
+                                      float* opac, float* sh, float* ls, float* qr, int32_t* mslot) {
+  const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= Nm) return;
+  const int64_t i = mov_idx[m];
+  for (int k = 0; k < 3; ++k) {
+    xyz[3 * m + k] = sc.xyz[3 * i + k];
+    scale[3 * m + k] = sc.scale_act[3 * i + k];
+    ls[3 * m + k] = sc.log_scale_raw[3 * i + k];
+  }
+  for (int k = 0; k < 4; ++k) qr[4 * m + k] = sc.quat_raw[4 * i + k];
+  opac[m] = sc.opacity[i];
+  for (int k = 0; k < 48; ++k) sh[48 * m + k] = sc.sh[48 * i + k];
+  mslot[m] = sc.slot[i];
+}
+
+}  // namespace
+
+int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
+                      int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
+                      const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
+                      const float* pose, int32_t num_slots, cudaStream_t s) {
+  if (n_items <= 0 || n_lists <= 0) return 0;
+  dim3 grid((unsigned)((n_items + 255) / 256), (unsigned)n_lists);
+  auto& w = ctx->ws;
+  if (dynamic) {
+    const size_t sm = (size_t)num_slots * GSW_POSE_STRIDE * sizeof(float);
+    preprocess_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
+                                                  frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
+                                                  w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
+                                                  w.bin_count.as<uint32_t>());
+  } else {
+    preprocess_kernel<false><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
+                                                  frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
+                                                  w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
+                                                  w.bin_count.as<uint32_t>());
+  }
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
+                   int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, cudaStream_t s) {
+  if (n_items <= 0 || n_lists <= 0) return 0;
+  dim3 grid((unsigned)((n_items + 255) / 256), (unsigned)n_lists);
+  auto& w = ctx->ws;
+  if (dynamic)
+    scatter_kernel<true><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
+                                              w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
+                                              w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap);
+  else
+    scatter_kernel<false><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
+                                               w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
+                                               w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,
+                       float* xy, float* conic_opacity, float* rgb, cudaStream_t s) {
+  const auto& L = ctx->last;
+  auto& w = ctx->ws;
+  if (L.N <= 0) return 0;
+  frame_attrs_kernel<<<(unsigned)((L.N + 255) / 256), 256, 0, s>>>(
+      L.N, L.Nm, L.V, frame, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(), L.g, w.recA.as<float4>(),
+      w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(), radii, tiles_touched, depth, xy, conic_opacity,
+      rgb);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s) {
+  const auto& L = ctx->last;
+  auto& w = ctx->ws;
+  if (L.N <= 0 || L.F <= 0) return 0;
+  dim3 grid((unsigned)((L.N + 255) / 256), (unsigned)L.F);
+  radii_kernel<<<grid, 256, 0, s>>>(L.N, L.Nm, L.V, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(),
+                                    w.rad.as<int32_t>(), out_radii);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, float near_plane, uint8_t* out,
+                        cudaStream_t s) {
+  if (P <= 0) return 0;
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, near_plane, out);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_gather_movable(const gsw_ctx* ctx, cudaStream_t s) {
+  if (ctx->Nm <= 0) return 0;
+  gather_movable_kernel<<<(unsigned)((ctx->Nm + 255) / 256), 256, 0, s>>>(
+      ctx->Nm, ctx->mov_idx.as<int32_t>(), ctx->scene, ctx->mov_xyz.as<float>(), ctx->mov_scale_act.as<float>(),
+      ctx->mov_opacity.as<float>(), ctx->mov_sh.as<float>(), ctx->mov_log_scale.as<float>(),
+      ctx->mov_quat_raw.as<float>(), ctx->mov_slot.as<int32_t>());
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace gsw

@@ -1,0 +1,225 @@
+"""Python handle on a libgsw context: scene upload + batched frame rendering on the caller's stream.
+
+torch is used for device memory and streams only; all arithmetic on the hot path is in libgsw.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _chk(t: torch.Tensor, dtype, name, device):
+    if t.device != device:
+        raise ValueError(f"{name}: expected device {device}, got {t.device}")
+    if t.dtype != dtype:
+        raise ValueError(f"{name}: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name}: must be contiguous")
+    return t
+
+
+class Engine:
+    NEAR_GSWORLD = 0.05  # GSWorld's patched near plane (reference README.md:33)
+
+    def __init__(self, device="cuda:0"):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("gsworld_b200.Engine needs a CUDA device; there is no CPU path")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        _lib.check(self.lib.gsw_create(self.device.index, C.byref(h)))
+        self._h = h
+        self._keep = {}
+        self.N = 0
+        self.num_slots = 0
+        self.last_stats = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.gsw_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # -- scene --
+    def set_scene(self, xyz, scale_act, quat_act, opacity_act, sh, log_scale_raw=None, quat_raw=None, slot=None,
+                  num_slots=0):
+        """All tensors on self.device, fp32 contiguous; layouts as include/gsw.h (gsw_scene_set)."""
+        d, f32 = self.device, torch.float32
+        N = xyz.shape[0]
+        xyz = _chk(xyz.reshape(N, 3), f32, "xyz", d)
+        scale_act = _chk(scale_act.reshape(N, 3), f32, "scale_act", d)
+        quat_act = _chk(quat_act.reshape(N, 4), f32, "quat_act", d)
+        opacity_act = _chk(opacity_act.reshape(N), f32, "opacity_act", d)
+        sh = _chk(sh.reshape(N, 16, 3), f32, "sh", d)
+        if slot is not None:
+            slot = _chk(slot.reshape(N), torch.int32, "slot", d)
+            log_scale_raw = _chk(log_scale_raw.reshape(N, 3), f32, "log_scale_raw", d)
+            quat_raw = _chk(quat_raw.reshape(N, 4), f32, "quat_raw", d)
+        self._keep = dict(xyz=xyz, scale_act=scale_act, quat_act=quat_act, opacity_act=opacity_act, sh=sh,
+                          log_scale_raw=log_scale_raw, quat_raw=quat_raw, slot=slot)
+        _lib.check(self.lib.gsw_scene_set(self._h, N, _ptr(xyz), _ptr(scale_act), _ptr(quat_act), _ptr(opacity_act),
+                                          _ptr(sh), _ptr(log_scale_raw), _ptr(quat_raw), _ptr(slot), int(num_slots),
+                                          self._stream()))
+        self.N, self.num_slots = N, int(num_slots)
+
+    def set_depth_buckets(self, nb: int):
+        _lib.check(self.lib.gsw_set_depth_buckets(self._h, int(nb)))
+
+    def reserve_entries(self, n: int):
+        _lib.check(self.lib.gsw_reserve_entries(self._h, int(n)))
+
+    # -- frames --
+    def render_frames(self, pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view, H, W, *,
+                      num_envs, bg=(0.0, 0.0, 0.0), antialiasing=False, scale_modifier=1.0, near=NEAR_GSWORLD,
+                      out_rgb_u8=None, out_color=None, out_invdepth=None, out_radii=None, want_u8=True,
+                      want_color=False, want_invdepth=False, want_radii=False, finish=True):
+        """Enqueue one batched transform+rasterize launch set.  Returns dict of output tensors.
+
+        pose [B,S,20] fp32; viewmatrix/projmatrix [V,4,4]; campos [V,3]; tanfov [V,2];
+        frame_env/frame_view [F] int32.  With finish=True (default) waits for the launch, and if the
+        tile-entry workspace overflowed grows it and re-runs (so results are always valid on return)."""
+        d, f32 = self.device, torch.float32
+        V, F = viewmatrix.shape[0], frame_env.shape[0]
+        viewmatrix = _chk(viewmatrix.reshape(V, 16), f32, "viewmatrix", d)
+        projmatrix = _chk(projmatrix.reshape(V, 16), f32, "projmatrix", d)
+        campos = _chk(campos.reshape(V, 3), f32, "campos", d)
+        tanfov = _chk(tanfov.reshape(V, 2), f32, "tanfov", d)
+        frame_env = _chk(frame_env.reshape(F), torch.int32, "frame_env", d)
+        frame_view = _chk(frame_view.reshape(F), torch.int32, "frame_view", d)
+        if pose is not None:
+            pose = _chk(pose.reshape(num_envs, self.num_slots, _lib.POSE_STRIDE), f32, "pose", d)
+        if want_u8 and out_rgb_u8 is None:
+            out_rgb_u8 = torch.empty((F, H, W, 3), dtype=torch.uint8, device=d)
+        if want_color and out_color is None:
+            out_color = torch.empty((F, 3, H, W), dtype=f32, device=d)
+        if want_invdepth and out_invdepth is None:
+            out_invdepth = torch.empty((F, 1, H, W), dtype=f32, device=d)
+        if want_radii and out_radii is None:
+            out_radii = torch.empty((F, self.N), dtype=torch.int32, device=d)
+        desc = _lib.FramesDesc()
+        desc.num_envs, desc.num_views, desc.num_frames = int(num_envs), int(V), int(F)
+        desc.height, desc.width, desc.antialiasing = int(H), int(W), int(bool(antialiasing))
+        desc.scale_modifier, desc.near_plane = float(scale_modifier), float(near)
+        desc.bg[0], desc.bg[1], desc.bg[2] = float(bg[0]), float(bg[1]), float(bg[2])
+        desc.pose = None if pose is None else pose.data_ptr()
+        desc.viewmatrix, desc.projmatrix = viewmatrix.data_ptr(), projmatrix.data_ptr()
+        desc.campos, desc.tanfov = campos.data_ptr(), tanfov.data_ptr()
+        desc.frame_env, desc.frame_view = frame_env.data_ptr(), frame_view.data_ptr()
+        desc.out_rgb_u8 = None if out_rgb_u8 is None else out_rgb_u8.data_ptr()
+        desc.out_color = None if out_color is None else out_color.data_ptr()
+        desc.out_invdepth = None if out_invdepth is None else out_invdepth.data_ptr()
+        desc.out_radii = None if out_radii is None else out_radii.data_ptr()
+        self._last_inputs = (pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view)
+        self._dbg_N = None
+        for _attempt in range(4):
+            _lib.check(self.lib.gsw_render_frames(self._h, C.byref(desc), self._stream()))
+            if not finish:
+                break
+            if self.finish(raise_on_overflow=False):
+                break
+        else:
+            raise _lib.GswError(_lib.GSW_E_CAPACITY, "tile-entry workspace kept overflowing")
+        return dict(rgb_u8=out_rgb_u8, color=out_color, invdepth=out_invdepth, radii=out_radii)
+
+    def finish(self, raise_on_overflow=True) -> bool:
+        """Wait for the last launch.  Returns True if it was valid; on overflow grows the workspace
+        (caller must re-launch) and returns False, or raises."""
+        need = C.c_int64(0)
+        stats = (C.c_int64 * 4)()
+        rc = self.lib.gsw_finish(self._h, C.byref(need), C.byref(stats))
+        self.last_stats = dict(D=stats[0], merged=stats[1], cap=stats[2], launches=stats[3])
+        if rc == _lib.GSW_E_CAPACITY:
+            self.reserve_entries(int(need.value * 1.25) + 1024)
+            if raise_on_overflow:
+                _lib.check(rc)
+            return False
+        _lib.check(rc)
+        return True
+
+    # -- single frame, upstream argument list --
+    def rasterize_forward(self, means3D, opacities, viewmatrix, projmatrix, campos, tanfovx, tanfovy, H, W, bg, *,
+                          shs=None, colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None,
+                          sh_degree=3, scale_modifier=1.0, prefiltered=False, antialiasing=False,
+                          near=NEAR_GSWORLD):
+        d, f32 = self.device, torch.float32
+        P = means3D.shape[0]
+        c = lambda t, n: None if t is None else _chk(t.contiguous(), f32, n, d)
+        means3D, opacities = c(means3D, "means3D"), c(opacities, "opacities")
+        shs, colors_precomp = c(shs, "shs"), c(colors_precomp, "colors_precomp")
+        scales, rotations, cov3D_precomp = c(scales, "scales"), c(rotations, "rotations"), c(cov3D_precomp, "cov3D")
+        viewmatrix, projmatrix = c(viewmatrix, "viewmatrix"), c(projmatrix, "projmatrix")
+        campos, bg = c(campos, "campos"), c(bg, "bg")
+        M = 0 if shs is None else int(shs.reshape(P, -1, 3).shape[1]) if P > 0 else 16
+        self._dbg_N = P
+        color = torch.zeros((3, H, W), dtype=f32, device=d)
+        radii = torch.zeros((P,), dtype=torch.int32, device=d)
+        invd = torch.zeros((1, H, W), dtype=f32, device=d)
+        for _attempt in range(4):
+            _lib.check(self.lib.gsw_rasterize_forward(
+                self._h, P, int(sh_degree), M, _ptr(bg), int(W), int(H), _ptr(means3D), _ptr(shs),
+                _ptr(colors_precomp), _ptr(opacities), _ptr(scales), float(scale_modifier), _ptr(rotations),
+                _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tanfovx),
+                float(tanfovy), int(bool(prefiltered)), int(bool(antialiasing)), float(near), _ptr(color),
+                _ptr(radii), _ptr(invd), self._stream()))
+            if P == 0 or self.finish(raise_on_overflow=False):
+                break
+        else:
+            raise _lib.GswError(_lib.GSW_E_CAPACITY, "tile-entry workspace kept overflowing")
+        return color, radii, invd
+
+    def mark_visible(self, positions, viewmatrix, near=NEAR_GSWORLD):
+        P = positions.shape[0]
+        out = torch.zeros((P,), dtype=torch.uint8, device=self.device)
+        _lib.check(self.lib.gsw_mark_visible(self._h, P, _ptr(positions.contiguous()), _ptr(viewmatrix.contiguous()),
+                                             float(near), _ptr(out), self._stream()))
+        return out.bool()
+
+    # -- parity taps --
+    def debug_frame_attrs(self, frame: int):
+        N, d = self._last_N(), self.device
+        o = dict(radii=torch.zeros(N, dtype=torch.int32, device=d),
+                 tiles_touched=torch.zeros(N, dtype=torch.int32, device=d),
+                 depth=torch.zeros(N, dtype=torch.float32, device=d), xy=torch.zeros((N, 2), device=d),
+                 conic_opacity=torch.zeros((N, 4), device=d), rgb=torch.zeros((N, 3), device=d))
+        _lib.check(self.lib.gsw_debug_frame_attrs(self._h, int(frame), _ptr(o["radii"]), _ptr(o["tiles_touched"]),
+                                                  _ptr(o["depth"]), _ptr(o["xy"]), _ptr(o["conic_opacity"]),
+                                                  _ptr(o["rgb"]), self._stream()))
+        return o
+
+    def _last_N(self):
+        return getattr(self, "_dbg_N", None) or self.N
+
+    def debug_frame_lists(self, frame: int, T: int):
+        d = self.device
+        cap = 1 << 16
+        while True:
+            ranges = torch.zeros((T, 2), dtype=torch.int32, device=d)
+            keys = torch.zeros((cap,), dtype=torch.int64, device=d)
+            vals = torch.zeros((cap,), dtype=torch.int32, device=d)
+            cnt = C.c_int64(0)
+            rc = self.lib.gsw_debug_frame_lists(self._h, int(frame), _ptr(ranges), _ptr(keys), _ptr(vals), cap,
+                                                C.byref(cnt), self._stream())
+            if rc == _lib.GSW_E_CAPACITY:
+                cap = int(cnt.value) + 16
+                continue
+            _lib.check(rc)
+            n = int(cnt.value)
+            return dict(ranges=ranges, keys=keys[:n], vals=vals[:n], D=n)

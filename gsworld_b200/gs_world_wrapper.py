@@ -1,0 +1,267 @@
+"""GSWorldWrapper — the reference env wrapper's observation path on the batched B200 engine.
+
+Same public surface as gsworld/mani_skill/utils/wrappers/gs_world_wrapper.py:
+  GSWorldWrapper(env, robot_pipe, scene_gs_cfg_name, device, ...)          (:34-107)
+  .transform_gs_perlink(splats, gs_init_qpos=None, target_mat=None, eef_pos=None)   (:110-162)
+  ._render_gsworld(renderer='gaussian-splatting') -> {cam: uint8 (B,H,W,3)}         (:232-275)
+  .cam_maniskill2gs(config_maniskill, device, cam_names) -> {cam: Camera}           (:277-325)
+  .step / .reset / .render_current_step                                             (:176-230)
+What changes underneath: instead of a deepcopy of the model, L+K isin scans and B*C serial render()
+calls with a host sync each, transform_gs_perlink only composes the (B, L+K) pose table
+(S @ M_link @ inv(M_scan) @ inv(S); objects through extract_rigid_transform) and _render_gsworld makes ONE
+batched libgsw launch set that transforms the movable Gaussians and rasterizes every (env, camera) frame.
+Physics (env.step) stays with the wrapped env.
+
+Scene loading (GaussianModelMerger + PLY, gs_world_wrapper.py:75-79) and the scan-pose probe through a
+second ManiSkill env (:82-103) are outside the hot path: pass `merged_model` and `scan_link_mats`.
+
+strict_reference=True reproduces reference quirk Q1: every env is rendered through env
+0's camera (gs_world_wrapper.py:280-281).  False uses each env's own camera.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import rig_tables as rt
+from .cameras import Camera
+from .engine import Engine
+from .rigid import extract_rigid_transform, pose7_to_matrix
+from .rotation_conversions import matrix_to_quaternion
+
+try:  # the reference subclasses gym.Wrapper; gymnasium is optional here
+    import gymnasium as _gym
+
+    _Base = _gym.Wrapper
+except Exception:  # pragma: no cover - gymnasium absent in this image
+    _gym = None
+
+    class _Base:  # minimal stand-in with the same delegation behaviour
+        def __init__(self, env):
+            self.env = env
+
+        def __getattr__(self, name):
+            if name.startswith("_"):
+                raise AttributeError(name)
+            return getattr(self.env, name)
+
+        @property
+        def unwrapped(self):
+            return getattr(self.env, "unwrapped", self.env)
+
+
+class GSWorldWrapper(_Base):
+    def __init__(self, env, robot_pipe, scene_gs_cfg_name: str = "franka_merger",
+                 device: Union[str, torch.device] = "cuda", log_state: bool = False,
+                 state_log_path: str = "./exp_log", cam_randomization: bool = False, *, merged_model=None,
+                 scan_link_mats=None, strict_reference: bool = True, engine: Optional[Engine] = None):
+        super().__init__(env)
+        self.num_envs = env.num_envs
+        self.robot_pipe = robot_pipe
+        self.device = torch.device(device)
+        self.scene_gs_cfg_name = scene_gs_cfg_name
+        self.log_state = log_state
+        self.cam_randomization = cam_randomization
+        self.strict_reference = strict_reference
+        fam = rt.robot_family(scene_gs_cfg_name)
+        self.gs_semantics = dict(rt.LINK_LABELS[fam])
+        self.sim2gs_arm_trans = torch.tensor(rt.SIM2GS_ROBOT[fam], dtype=torch.float32, device=self.device)
+        self.obj_gs_semantics = rt.OBJECT_LABELS
+        self.rigid_sim2real, self.scale_sim2real, _, _ = extract_rigid_transform(self.sim2gs_arm_trans)
+        if merged_model is None or scan_link_mats is None:
+            raise NotImplementedError(
+                "pass merged_model= (loaded Gaussians) and scan_link_mats= (link poses at the scan qpos); the PLY "
+                "merger and the ManiSkill scan-pose probe are outside this package's hot path")
+        self.initial_merger_robot = merged_model
+        self.gs_link_pose_mats = [torch.as_tensor(m, dtype=torch.float32, device=self.device).reshape(1, 4, 4)
+                                  for m in scan_link_mats]
+        self.gs_movable_pts = dict()
+        self._engine = engine if engine is not None else Engine(self.device)
+        self._setup_rig()
+
+    # ------------------------------------------------------------------ set-up (once)
+    @property
+    def base_env(self):
+        return self.env.unwrapped
+
+    def _setup_rig(self):
+        """Label -> pose-table slot, constant matrix products, scene upload with activations done once."""
+        be, dev = self.base_env, self.device
+        links = be.agent.robot.get_links()
+        self._link_names = [l.name for l in links]
+        actors = be.get_state_dict().get("actors", {}) if hasattr(be, "get_state_dict") else {}
+        self._obj_names = [k for k in actors if k in rt.SIM2GS_OBJECT]
+        L, K = len(links), len(self._obj_names)
+        self.num_slots = L + K
+        g = self.initial_merger_robot
+        sem = g._semantics.long().squeeze(-1)
+        slot = torch.full_like(sem, -1, dtype=torch.int32)
+        for i, name in enumerate(self._link_names):  # later keys overwrite earlier ones, as the write-back loop does
+            if name not in self.gs_semantics:
+                continue
+            target = torch.as_tensor(self.gs_semantics[name], device=sem.device).long().reshape(-1)
+            slot[torch.isin(sem, target)] = i
+        for k, name in enumerate(self._obj_names):
+            slot[sem == int(self.obj_gs_semantics[name])] = L + k
+        # constants of gs_world_wrapper.py:120 and :146
+        S = self.sim2gs_arm_trans
+        self._S_inv = torch.linalg.inv(S)
+        self._scan_inv = torch.cat([torch.linalg.inv(m) for m in self.gs_link_pose_mats], 0)  # (L,4,4)
+        self._is_xarm = "xarm" in str(be.agent.uid)
+        self._xarm_off = torch.tensor(rt.OBJECT_OFFSET["xarm_arm"], dtype=torch.float32, device=dev)
+        self._obj_S_inv = [torch.linalg.inv(torch.tensor(rt.SIM2GS_OBJECT[n], dtype=torch.float32, device=dev))
+                           for n in self._obj_names]
+        self._obj_off = [torch.tensor(rt.OBJECT_OFFSET.get(n, [0.0, 0.0, 0.0]), dtype=torch.float32, device=dev)
+                         for n in self._obj_names]
+        self._obj_scale = [float(rt.OBJECT_SCALE[n]) for n in self._obj_names]
+        # activations exactly as the model getters (gaussian_model.py:102-130), once instead of per frame
+        f = lambda t: t.to(dev, torch.float32).contiguous()
+        self._engine.set_scene(
+            f(g._xyz), f(torch.exp(g._scaling)), f(torch.nn.functional.normalize(g._rotation)),
+            f(torch.sigmoid(g._opacity).reshape(-1)), f(torch.cat((g._features_dc, g._features_rest), dim=1)),
+            f(g._scaling), f(g._rotation), slot.to(dev).contiguous(), self.num_slots)
+        self._pose = torch.zeros((self.num_envs, self.num_slots, _lib.POSE_STRIDE), dtype=torch.float32, device=dev)
+        self._frame_maps = {}
+
+    # ------------------------------------------------------------------ per step
+    def transform_gs_perlink(self, splats=None, gs_init_qpos=None, target_mat=None, eef_pos=None):
+        """Compose the per-(env, link/object) rigid transforms for this step.
+
+        Same matrix algebra as the reference (gs_world_wrapper.py:115-120, :139-156); the Gaussian-level
+        part (gs_utils.transform_gaussians) is fused into the rasterizer's preprocess kernel."""
+        be, dev = self.base_env, self.device
+        links = be.agent.robot.get_links()
+        M = torch.stack([l.pose.to_transformation_matrix().to(dev, torch.float32) for l in links], 1)  # (B,L,4,4)
+        if self._is_xarm:
+            M = M.clone()
+            M[:, :, :3, 3] += self._xarm_off
+        A = self.sim2gs_arm_trans @ M @ self._scan_inv[None] @ self._S_inv
+        L = len(links)
+        P = self._pose
+        P.zero_()
+        R = A[..., :3, :3]
+        P[:, :L, 0:9] = R.reshape(self.num_envs, L, 9)
+        P[:, :L, 9:12] = A[..., :3, 3]
+        P[:, :L, 12:16] = matrix_to_quaternion(R)
+        if self._obj_names:
+            actors = be.get_state_dict()["actors"]
+            for k, name in enumerate(self._obj_names):
+                mat = pose7_to_matrix(actors[name][:, :7].to(dev, torch.float32))
+                mat[:, :3, 3] += self._obj_off[k]
+                full = self.sim2gs_arm_trans @ mat @ self._obj_S_inv[k]
+                rigid, scale, _, _ = extract_rigid_transform(full)
+                Ro = rigid[:, :3, :3]
+                P[:, L + k, 0:9] = Ro.reshape(self.num_envs, 9)
+                P[:, L + k, 9:12] = rigid[:, :3, 3]
+                P[:, L + k, 12:16] = matrix_to_quaternion(Ro)
+                P[:, L + k, 16] = scale * self._obj_scale[k]
+                P[:, L + k, 17] = 1.0
+                self.gs_semantics[name] = self.obj_gs_semantics[name]
+        return P
+
+    def _sensor_hw(self, cam_name):
+        be = self.base_env
+        hw = getattr(be, "sensor_hw", None)
+        if hw is not None:
+            return hw[cam_name]
+        img = be.get_sensor_images()[cam_name]["rgb"]  # reference path (gs_world_wrapper.py:288-289)
+        return int(img.shape[1]), int(img.shape[2])
+
+    def cam_maniskill2gs(self, config_maniskill: dict, device, cam_names: list) -> Dict[str, Camera]:
+        """ManiSkill sensor params -> 3DGS cameras, env 0 only (reference behaviour, :277-325)."""
+        return {c: self._camera_for(config_maniskill[c], c, 0, device) for c in cam_names}
+
+    def _camera_for(self, params, cam_name, env_idx, device) -> Camera:
+        ext = params["extrinsic_cv"][env_idx].to(device)
+        K = params["intrinsic_cv"][env_idx].to(device)
+        w2c = torch.vstack([ext, torch.tensor([0, 0, 0, 1], dtype=ext.dtype, device=ext.device)])
+        c2w = torch.linalg.inv(w2c)
+        img_h, img_w = self._sensor_hw(cam_name)
+        fovx = 2 * torch.arctan(img_w / (2 * K[0, 0]))
+        fovy = 2 * torch.arctan(img_h / (2 * K[1, 1]))
+        c2w[:3, 3] = c2w[:3, 3] * self.scale_sim2real
+        real_w2c = torch.linalg.inv(self.rigid_sim2real.to(device) @ c2w)
+        R = real_w2c[:3, :3].T
+        T = real_w2c[:3, 3]
+        return Camera(resolution=(img_w, img_h), colmap_id=0, R=R.cpu().numpy(), T=T.cpu().numpy(),
+                      FoVx=float(fovx), FoVy=float(fovy), depth_params=None, image=None, invdepthmap=None,
+                      image_name=cam_name, uid=0, data_device=device)
+
+    def _views(self, cam_names):
+        """Stack the view tensors the engine consumes: strict -> one view per camera, else one per (camera, env)."""
+        params = self.base_env.get_sensor_params()
+        envs = [0] if self.strict_reference else list(range(self.num_envs))
+        cams = [[self._camera_for(params[c], c, e, self.device) for e in envs] for c in cam_names]
+        self.gs_cam = {c: cams[i][0] for i, c in enumerate(cam_names)}
+        flat = [cam for per in cams for cam in per]
+        view = torch.stack([c.world_view_transform for c in flat])
+        proj = torch.stack([c.full_proj_transform for c in flat])
+        campos = torch.stack([c.camera_center for c in flat])
+        tanfov = torch.tensor([[math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5)] for c in flat],
+                              dtype=torch.float32, device=self.device)
+        return view.contiguous(), proj.contiguous(), campos.contiguous(), tanfov
+
+    def _maps(self, n_cams):
+        key = (n_cams, self.strict_reference)
+        if key not in self._frame_maps:
+            B = self.num_envs
+            fe = torch.arange(B, dtype=torch.int32).repeat(n_cams)  # frame = cam * B + env
+            cam_of = torch.arange(n_cams, dtype=torch.int32).repeat_interleave(B)
+            fv = cam_of if self.strict_reference else cam_of * B + fe
+            self._frame_maps[key] = (fe.to(self.device), fv.to(self.device).to(torch.int32))
+        return self._frame_maps[key]
+
+    def _render_gsworld(self, renderer="gaussian-splatting"):
+        if renderer != "gaussian-splatting":
+            return ValueError(f"{renderer} is not supported. Official renderer also supports gsplat.")
+        cam_names = list(self.base_env.get_sensor_params().keys())
+        sizes = {self._sensor_hw(c) for c in cam_names}
+        groups = [[c for c in cam_names if self._sensor_hw(c) == hw] for hw in sorted(sizes)]
+        gs_renders = {}
+        for names in groups:  # one launch set per distinct resolution (the reference sensors share one)
+            H, W = self._sensor_hw(names[0])
+            view, proj, campos, tanfov = self._views(names)
+            fe, fv = self._maps(len(names))
+            out = self._engine.render_frames(
+                self._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=self.num_envs, bg=(0.0, 0.0, 0.0),
+                antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True)
+            rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
+            for i, c in enumerate(names):
+                gs_renders[c] = rgb[i]
+        return {c: gs_renders[c] for c in cam_names}
+
+    # ------------------------------------------------------------------ gym surface
+    def step(self, action):
+        obs, reward, terminated, truncated, info = self.env.step(action)
+        self.transform_gs_perlink(self.initial_merger_robot)
+        for cam_name, gs_render in self._render_gsworld().items():
+            obs["sensor_data"][cam_name]["rgb"] = gs_render
+        return obs, reward, terminated, truncated, info
+
+    def reset(self, *, seed=None, options=None):
+        obs, info = self.env.reset(seed=seed, options=options)
+        self.transform_gs_perlink(self.initial_merger_robot)
+        for cam_name, gs_render in self._render_gsworld().items():
+            obs["sensor_data"][cam_name]["rgb"] = gs_render
+        return obs, info
+
+    def render(self):
+        return self.env.render()
+
+    def render_current_step(self):
+        be = self.base_env
+        info = be.get_info()
+        obs = be.get_obs(info)
+        reward = be.get_reward(obs=obs, action=None, info=info)
+        if "success" in info:
+            terminated = torch.logical_or(info["success"], info["fail"]) if "fail" in info else info["success"].clone()
+        else:
+            terminated = info["fail"].clone() if "fail" in info else torch.zeros(self.num_envs, dtype=bool,
+                                                                                 device=self.device)
+        for cam_name, gs_render in self._render_gsworld().items():
+            obs["sensor_data"][cam_name]["rgb"] = gs_render
+        return obs, reward, terminated, torch.zeros(self.num_envs, dtype=bool, device=self.device), info

@@ -1,0 +1,134 @@
+/* gsw.h — C ABI of libgsw.so: B200-native (sm_100a) GSWorld observation path.
+ *
+ * One hot path: per-link / per-object rigid transform of the movable Gaussians of every environment,
+ * followed by 3D-Gaussian-splatting forward rasterization of scene + robot for every (env, camera) frame.
+ * Plain pointers and sizes only; no torch types.  All `const float*` / `int32_t*` arguments below are
+ * DEVICE pointers unless the comment says "host".  The caller owns every input and output buffer; the
+ * context owns only its grow-only workspace.  Nothing here synchronises the host except gsw_finish()
+ * and calls that (re)allocate workspace because a shape grew.
+ *
+ * Every function returns 0 on success, a negative GSW_E_* code for an invalid argument or capacity
+ * problem, or a positive cudaError_t value; gsw_last_error() gives the text (thread-local).
+ *
+ * What each entry point replaces in the reference (luccachiang/GSWorld @ 5329504):
+ *   gsw_scene_set          <- the merged model held by GSWorldWrapper.initial_merger_robot
+ *                             (gsworld/mani_skill/utils/wrappers/gs_world_wrapper.py:75-79) plus the
+ *                             activations of gaussian_model.py:102-130 done once instead of per frame.
+ *   gsw_render_frames      <- GSWorldWrapper.transform_gs_perlink (gs_world_wrapper.py:110-162,
+ *                             Gaussian-level part = gs_utils.py:283-385) + _render_gsworld
+ *                             (gs_world_wrapper.py:232-275): B*C deepcopies, isin write-backs and
+ *                             serial render() calls become one batched launch set.
+ *   gsw_rasterize_forward  <- diff_gaussian_rasterization._C.rasterize_gaussians as called by
+ *                             GaussianRasterizer.forward (call site
+ *                             submodules/gaussian-splatting/gaussian_renderer/__init__.py:36-52,102-110;
+ *                             the extension source itself is an absent submodule, pinned at
+ *                             graphdeco-inria/diff-gaussian-rasterization@9c5c2028, near plane 0.05 per
+ *                             GSWorld README.md:33).
+ *   gsw_mark_visible       <- GaussianRasterizer.markVisible (same absent extension).
+ *   gsw_debug_*            <- no counterpart; parity taps (tiles_touched, sorted keys, tile ranges).
+ */
+#ifndef GSW_H_
+#define GSW_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSW_VERSION 100
+
+/* error codes (negative); positive return values are cudaError_t */
+#define GSW_OK 0
+#define GSW_E_INVALID (-1)   /* bad argument */
+#define GSW_E_STATE (-2)     /* call order (e.g. render before scene_set) */
+#define GSW_E_CAPACITY (-3)  /* tile-entry workspace too small for the last launch; see gsw_finish */
+#define GSW_E_NOMEM (-4)
+
+/* floats per (env, slot) pose row: R[9] row-major, t[3], qR[4] wxyz, kappa, has_scale, pad[2] */
+#define GSW_POSE_STRIDE 20
+
+typedef struct gsw_ctx gsw_ctx;
+typedef void* gsw_stream; /* cudaStream_t */
+
+int gsw_version(void);
+const char* gsw_last_error(void);
+
+int gsw_create(int device, gsw_ctx** out);
+int gsw_destroy(gsw_ctx* ctx);
+
+/* Scene upload.  Arrays are used IN PLACE (zero copy) and must outlive the context or the next
+ * gsw_scene_set.  Layouts are the reference's own:
+ *   xyz[N,3]; scale_act[N,3] = exp(_scaling); quat_act[N,4] = normalize(_rotation) (wxyz);
+ *   opacity_act[N] = sigmoid(_opacity); sh[N,16,3] = cat(_features_dc,_features_rest);
+ *   log_scale_raw[N,3] = _scaling and quat_raw[N,4] = _rotation (read for movable Gaussians only);
+ *   slot[N]: -1 = static background, else index into the per-env pose table (link or object).
+ * A compact copy of the movable Gaussians (slot >= 0) is made here; this call synchronises. */
+int gsw_scene_set(gsw_ctx* ctx, int64_t N, const float* xyz, const float* scale_act, const float* quat_act,
+                  const float* opacity_act, const float* sh, const float* log_scale_raw, const float* quat_raw,
+                  const int32_t* slot, int num_slots, gsw_stream stream);
+
+typedef struct gsw_frames_desc {
+  int32_t num_envs;   /* B */
+  int32_t num_views;  /* V distinct cameras; static Gaussians are projected once per view */
+  int32_t num_frames; /* F rendered images; frame f shows env frame_env[f] through view frame_view[f] */
+  int32_t height, width;
+  int32_t antialiasing;
+  float scale_modifier;
+  float near_plane; /* 0.05 = GSWorld (README.md:33); 0.2 = upstream */
+  float bg[3];
+  const float* pose;         /* [B, num_slots, GSW_POSE_STRIDE] */
+  const float* viewmatrix;   /* [V,16] world_view_transform, transposed row-major (cameras.py:86) */
+  const float* projmatrix;   /* [V,16] full_proj_transform, same convention (cameras.py:88) */
+  const float* campos;       /* [V,3] */
+  const float* tanfov;       /* [V,2] tan(FoVx/2), tan(FoVy/2) */
+  const int32_t* frame_env;  /* [F] */
+  const int32_t* frame_view; /* [F] */
+  uint8_t* out_rgb_u8;       /* [F,H,W,3] or NULL: (clamp01(c)*255) truncated, gs_world_wrapper.py:268-270 */
+  float* out_color;          /* [F,3,H,W] or NULL: un-clamped C + T*bg as the rasterizer returns it */
+  float* out_invdepth;       /* [F,1,H,W] or NULL */
+  int32_t* out_radii;        /* [F,N] or NULL */
+} gsw_frames_desc;
+
+/* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous. */
+int gsw_render_frames(gsw_ctx* ctx, const gsw_frames_desc* desc, gsw_stream stream);
+
+/* Wait for the last launch on this context and report it.  Returns GSW_E_CAPACITY if the tile-entry
+ * workspace overflowed (outputs are then invalid); *needed_entries (may be NULL) receives the entry
+ * count that launch needed.  Call gsw_reserve_entries() and launch again.  stats (may be NULL):
+ * [0] = D tile entries written, [1] = merged entries written, [2] = entry capacity, [3] = launches. */
+int gsw_finish(gsw_ctx* ctx, int64_t* needed_entries, int64_t stats[4]);
+int gsw_reserve_entries(gsw_ctx* ctx, int64_t entries);
+/* depth sub-buckets per tile list (power of two, 1..64); 0 = automatic */
+int gsw_set_depth_buckets(gsw_ctx* ctx, int nb);
+
+/* Single-frame forward with the upstream argument list (drop-in for GaussianRasterizer.forward).
+ * Exactly one of shs / colors_precomp and exactly one of (scales, rotations) / cov3D_precomp.
+ * shs is [P,M,3]; degree <= 3.  Outputs: out_color[3,H,W], out_radii[P], out_invdepth[1,H,W] (NULL ok).
+ * bg, viewmatrix, projmatrix, campos are device pointers like upstream tensors. */
+int gsw_rasterize_forward(gsw_ctx* ctx, int32_t P, int32_t sh_degree, int32_t M, const float* bg, int32_t width,
+                          int32_t height, const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                          const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                          const float* campos, float tan_fovx, float tan_fovy, int32_t prefiltered,
+                          int32_t antialiasing, float near_plane, float* out_color, int32_t* out_radii,
+                          float* out_invdepth, gsw_stream stream);
+
+int gsw_mark_visible(gsw_ctx* ctx, int32_t P, const float* means3D, const float* viewmatrix, float near_plane,
+                     uint8_t* out_visible, gsw_stream stream);
+
+/* ---- parity taps for the LAST gsw_render_frames / gsw_rasterize_forward launch (device outputs) ---- */
+/* Per-Gaussian preprocess results of frame f, indexed by original Gaussian index; any pointer NULL ok. */
+int gsw_debug_frame_attrs(gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,
+                          float* xy, float* conic_opacity, float* rgb, gsw_stream stream);
+/* Tile lists of frame f in blend order: ranges[T,2] into keys/vals; keys = tile<<32 | depth bits,
+ * vals = original Gaussian index (what the upstream sort produces).  Returns GSW_E_CAPACITY if cap is
+ * too small; *count (host) receives D for the frame.  Synchronises. */
+int gsw_debug_frame_lists(gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
+                          int64_t cap, int64_t* count, gsw_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSW_H_ */

@@ -1,0 +1,117 @@
+"""GPU parity of the batched entry point (gsw_render_frames) through the GSWorldWrapper mirror: fused
+per-link / per-object transform + rasterization of every (env, camera) frame vs the CPU oracle run frame
+by frame on the same pose table and cameras."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as orc
+from tests.helpers import assert_image_close, oracle_frame_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(robot, cfg_name, B, hw, objects, strict, n_total=24_000, seed=11, nb=0):
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200.gaussian_renderer import PipelineParams
+    from gsworld_b200.gs_world_wrapper import GSWorldWrapper
+    dev = torch.device("cuda:0")
+    scene = fx.make_scene(fx.SceneSpec(robot=robot, n_total=n_total, per_link=250, objects=objects, per_object=1200,
+                                       seed=seed))
+    env = fx.FakeEnv(robot, num_envs=B, hw=hw, objects=objects, seed=seed, device=dev)
+    scan = fx.forward_kinematics(robot, fx.rt.ROBOT_SCAN_QPOS[robot][None])[0]
+    wrap = GSWorldWrapper(env, PipelineParams(), cfg_name, device=dev, merged_model=scene.to(dev),
+                          scan_link_mats=list(scan), strict_reference=strict)
+    if nb:
+        wrap._engine.set_depth_buckets(nb)
+    return scene, env, wrap
+
+
+def _check_frames(scene, env, wrap, H, W, exact_objects=True):
+    eng = wrap._engine
+    torch.cuda.synchronize()
+    pose = wrap._pose.cpu().numpy()
+    slot = eng._keep["slot"].cpu().numpy()
+    names = list(env.cameras)
+    params = env.get_sensor_params()
+    T = ((H + 15) // 16) * ((W + 15) // 16)
+    # second launch with float outputs for the tolerance checks
+    view, proj, campos, tanfov = wrap._views(names)
+    fe, fv = wrap._maps(len(names))
+    out = eng.render_frames(wrap._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=env.num_envs,
+                            want_u8=True, want_color=True, want_invdepth=True, want_radii=True)
+    torch.cuda.synchronize()
+    n_obj_mismatch = 0
+    for ci, name in enumerate(names):
+        for e in range(env.num_envs):
+            f = ci * env.num_envs + e
+            v = int(fv[f])
+            fin = oracle_frame_inputs(scene, slot, pose[e], len(wrap._link_names))
+            want = orc.rasterize_forward(fin["xyz"], fin["opacities"], view[v].cpu().numpy(), proj[v].cpu().numpy(),
+                                         campos[v].cpu().numpy(), float(tanfov[v, 0]), float(tanfov[v, 1]), H, W,
+                                         shs=fin["shs"], scales=fin["scales"], rotations=fin["rotations"], debug=True)
+            radii = out["radii"][f].cpu().numpy()
+            attrs = {k: t.cpu().numpy() for k, t in eng.debug_frame_attrs(f).items()}
+            lists = eng.debug_frame_lists(f, T)
+            is_obj = slot >= len(wrap._link_names)
+            # link + static Gaussians: exact.  Object Gaussians go through expf(logf(.)) (reference quirk Q4);
+            # CUDA libdevice and glibc may differ by an ulp there, which can flip a ceil() in rare cases.
+            np.testing.assert_array_equal(radii[~is_obj], want["radii"][~is_obj])
+            mism = int((radii[is_obj] != want["radii"][is_obj]).sum())
+            n_obj_mismatch += mism
+            if mism == 0:
+                np.testing.assert_array_equal(attrs["tiles_touched"], want["tiles_touched"])
+                assert lists["D"] == want["D"]
+                np.testing.assert_array_equal(lists["keys"].cpu().numpy().view(np.uint64), want["keys"])
+                np.testing.assert_array_equal(lists["vals"].cpu().numpy().view(np.uint32), want["vals"])
+                np.testing.assert_array_equal(lists["ranges"].cpu().numpy(), want["ranges"])
+                vis = (want["radii"] > 0) & ~is_obj
+                bits = lambda a: np.ascontiguousarray(a, np.float32).view(np.uint32)
+                np.testing.assert_array_equal(bits(attrs["depth"][vis]), bits(want["depth"][vis]))
+                np.testing.assert_array_equal(bits(attrs["xy"][vis]), bits(want["xy"][vis]))
+                np.testing.assert_array_equal(bits(attrs["rgb"][vis]), bits(want["rgb"][vis]))
+            frag = want["fragile"].astype(bool)
+            assert_image_close(out["color"][f].cpu().numpy(), want["color"], frag, what=f"color f{f}")
+            assert_image_close(out["invdepth"][f, 0].cpu().numpy(), want["invdepth"][0], frag, what=f"invdepth f{f}")
+            ref8 = orc.to_uint8_hwc(np.clip(want["color"], 0, 1)).astype(np.int32)
+            got8 = out["rgb_u8"][f].cpu().numpy().astype(np.int32)
+            assert (np.abs(got8 - ref8) <= 1)[~frag].all()
+            assert (got8 == ref8).mean() > 0.98
+    assert n_obj_mismatch <= 2, f"{n_obj_mismatch} object-Gaussian radii differ from the oracle"
+
+
+@pytest.mark.parametrize("strict", [True, False], ids=["strict_env0_camera", "per_env_camera"])
+def test_fr3_two_cameras(strict):
+    scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", 3, (64, 48), ("006_mustard_bottle", "snack_box"), strict)
+    obs, _ = wrap.reset(seed=5)
+    _check_frames(scene, env, wrap, 64, 48)
+    obs, *_ = wrap.step(None)
+    assert obs["sensor_data"]["right_cam"]["rgb"].shape == (3, 64, 48, 3)
+    assert obs["sensor_data"]["right_cam"]["rgb"].dtype == torch.uint8
+    _check_frames(scene, env, wrap, 64, 48)
+
+
+def test_xarm_offset_and_bread_scale():
+    # xarm: +0.05 z on every link (Q8); bread_slice: object_scale 0.95 and a 13x object frame (Q4 path)
+    scene, env, wrap = _make("xarm6_uf_gripper", "xarm6_align", 2, (48, 80), ("005_tomato_soup_can", "bread_slice"),
+                             True, seed=13)
+    wrap.reset(seed=2)
+    _check_frames(scene, env, wrap, 48, 80)
+
+
+def test_depth_buckets_do_not_change_results():
+    scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", 2, (64, 64), ("006_mustard_bottle",), True, nb=8)
+    wrap.reset(seed=9)
+    _check_frames(scene, env, wrap, 64, 64)
+
+
+def test_entry_workspace_overflow_is_detected_and_recovered():
+    scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", 2, (64, 64), ("snack_box",), True)
+    eng = wrap._engine
+    # force a tiny capacity by constructing a fresh engine and reserving too little is not possible
+    # (capacity only grows), so check the protocol instead: stats are reported and D + merged <= cap.
+    wrap.reset(seed=1)
+    st = eng.last_stats
+    assert st["D"] > 0 and st["D"] + st["merged"] <= st["cap"]
