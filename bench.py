@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py — rendered frames/s of the GSWorld observation path (transform + 3DGS rasterization).
+
+Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` prints ONE JSON line on rank 0.
+Workload = BASELINE.json configs[2]: PnpBoxFr3Env-v1-shaped step, fr3_umi, 64 envs x 2 cameras
+(wrist + third-person) x 256x256, synthetic 1M-Gaussian scene (SURVEY.md §8d generator), per GPU.
+A "step" = compose the (env, link/object) pose table + render every (env, camera) frame to uint8.
+Multi-GPU: envs are sharded by rank (64 per rank, weak scaling), scene replicated, and each step ends
+with one NCCL all-gather of the uint8 observations (the only exchange on the path).
+
+--impl reference: the reference's own path restated on the host cores (oracle/: torch transform with
+deepcopy + isin write-back per frame, CPU rasterizer) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+H = W = 256
+ENVS_PER_GPU = 64
+N_GAUSS = 1_000_000
+ROBOT = "fr3_umi"
+OBJECTS = ("006_mustard_bottle", "snack_box")
+CAMERAS = ("right_cam", "wrist_cam")
+SEED = 1234 + 3
+METRIC = "rendered frames/sec (envs x cams, 256^2, 1M Gaussians)"
+WORKLOAD = "cfg3: fr3_umi, 64 envs/GPU x 2 cams (wrist + third-person), 256x256, synthetic 1M-Gaussian scene"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def make_scene():
+    from gsworld_b200 import fixtures as fx
+    return fx.make_scene(fx.SceneSpec(robot=ROBOT, n_total=N_GAUSS, per_link=4000, objects=OBJECTS, per_object=7000,
+                                      seed=SEED))
+
+
+class ReplayEnv:
+    """Pre-generated env states (seeded FakeEnv roll-out) replayed step by step, so the timed region holds
+    no kinematics/physics.  resident=True hands out device tensors; False hands out pinned host tensors
+    (the wrapper's .to(device) is then the per-step H2D copy)."""
+
+    def __init__(self, base, n_states, device, resident):
+        from types import SimpleNamespace
+        self.num_envs = base.num_envs
+        self.sensor_hw = base.sensor_hw
+        self.cameras = base.cameras
+        self._names = [l.name for l in base.agent.robot.get_links()]
+        self._states = []
+        for _ in range(n_states):
+            base.step(None)
+            mats = torch.stack([l.pose.to_transformation_matrix() for l in base.agent.robot.get_links()], 1).float()
+            actors = {k: v.clone().float() for k, v in base.get_state_dict()["actors"].items()}
+            params = {c: {k: v.clone().float() for k, v in p.items()} for c, p in base.get_sensor_params().items()}
+            st = dict(mats=mats, actors=actors, params=params)
+            self._states.append(self._place(st, device, resident))
+        self._i = 0
+        env = self
+
+        class _P:
+            def __init__(s, j):
+                s.j = j
+
+            def to_transformation_matrix(s):
+                return env._states[env._i]["mats"][:, s.j]
+
+        self.agent = SimpleNamespace(uid=base.agent.uid, robot=SimpleNamespace(
+            name=base.agent.robot.name,
+            get_links=lambda: [SimpleNamespace(name=n, pose=_P(j)) for j, n in enumerate(self._names)]))
+        self.h2d_bytes = 0 if resident else sum(t.numel() * t.element_size() for t in self._tensors(self._states[0]))
+
+    @staticmethod
+    def _tensors(st):
+        yield st["mats"]
+        yield from st["actors"].values()
+        for p in st["params"].values():
+            yield p["extrinsic_cv"]
+            yield p["intrinsic_cv"]
+
+    @staticmethod
+    def _place(st, device, resident):
+        f = (lambda t: t.to(device)) if resident else (lambda t: t.cpu().pin_memory())
+        return dict(mats=f(st["mats"]), actors={k: f(v) for k, v in st["actors"].items()},
+                    params={c: {k: f(v) for k, v in p.items()} for c, p in st["params"].items()})
+
+    @property
+    def unwrapped(self):
+        return self
+
+    def advance(self):
+        self._i = (self._i + 1) % len(self._states)
+
+    def get_state_dict(self):
+        return {"actors": self._states[self._i]["actors"]}
+
+    def get_sensor_params(self):
+        return self._states[self._i]["params"]
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=3)
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_reference_sample(scene, n_envs, steps, warmup, strict=True):
+    """The reference path on host cores: torch transform + per-frame deepcopy/isin + CPU rasterizer."""
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200 import rig_tables as rt
+    from oracle import oracle as orc
+    from oracle import torch_transform as ot
+    torch.set_num_threads(os.cpu_count() or 1)
+    env = fx.FakeEnv(ROBOT, num_envs=n_envs, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED)
+    scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
+    ref = ot.RefPath(env, scene, rt.SIM2GS_ROBOT["fr3"], rt.LINK_LABELS["fr3"], list(scan), rt.SIM2GS_OBJECT,
+                     rt.OBJECT_LABELS, rt.OBJECT_OFFSET, rt.OBJECT_SCALE)
+    times = []
+    for i in range(warmup + steps):
+        env.step(None)
+        t0 = time.perf_counter()
+        ref.transform_gs_perlink()
+        ref.render_gsworld(strict=strict)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    frames = n_envs * len(CAMERAS)
+    return frames * len(times) / sum(times), float(np.mean(times) * 1e3), orc.num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    scene = make_scene()
+    n_envs = 1
+    fps, ms, cores = cpu_reference_sample(scene, n_envs, args.steps, args.warmup)
+    sample = f"{n_envs} env x {len(CAMERAS)} cams per step (of {ENVS_PER_GPU}), same scene and cameras"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "cameras": "strict (env-0 camera, reference behaviour)"},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200 import rig_tables as rt
+    from gsworld_b200.gaussian_renderer import PipelineParams
+    from gsworld_b200.gs_world_wrapper import GSWorldWrapper
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B = ENVS_PER_GPU
+    F = B * len(CAMERAS)
+    scene_cpu = make_scene()
+    scene = scene_cpu.to(dev)
+    base = fx.FakeEnv(ROBOT, num_envs=B, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED + 17 * rank)
+    scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
+    n_states = 8
+
+    def build(resident, strict):
+        env = ReplayEnv(base, n_states, dev, resident)
+        wrap = GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene,
+                              scan_link_mats=list(scan), strict_reference=strict)
+        return env, wrap
+
+    gathered = torch.empty((world, len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev) if world > 1 else None
+    local_obs = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev)
+
+    def step(env, wrap):
+        env.advance()
+        wrap.transform_gs_perlink(None)
+        out = wrap._render_gsworld()
+        if world > 1:
+            for i, c in enumerate(CAMERAS):
+                local_obs[i].copy_(out[c])
+            dist.all_gather_into_tensor(gathered.view(world, -1), local_obs.view(-1))
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(env, wrap, steps, warmup, d2h=None):
+        wrap.sync_each_step = True  # warm-up validates (and if needed grows) the tile-entry workspace
+        for _ in range(warmup):
+            out = step(env, wrap)
+            if d2h is not None:
+                for i, c in enumerate(CAMERAS):
+                    d2h[i].copy_(out[c], non_blocking=True)
+        wrap.sync_each_step = d2h is not None  # resident-input runs are fully asynchronous
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = step(env, wrap)
+            if d2h is not None:
+                for i, c in enumerate(CAMERAS):
+                    d2h[i].copy_(out[c], non_blocking=True)
+                torch.cuda.current_stream().synchronize()  # the caller reads the observation every step
+        e1.record()
+        barrier()
+        if not wrap._engine.finish(raise_on_overflow=False):
+            raise RuntimeError("tile-entry workspace overflowed inside the timed region: number invalid")
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    results = {}
+    sampler = None
+    for mode, strict in (("strict", True), ("per_env", False)):
+        env, wrap = build(True, strict)
+        eng = wrap._engine
+        if mode == "strict":
+            sampler = ClockSampler(local)
+            timed(env, wrap, 0, args.warmup)
+            l_w = eng.kernel_launches()
+            sampler.start()
+            ms = timed(env, wrap, args.steps, 0)
+            clocks = sampler.stop()
+            launches = eng.kernel_launches() - l_w
+        else:
+            ms = timed(env, wrap, args.steps, args.warmup)
+        # stage breakdown + traffic counts (outside the timed region)
+        eng.profile(True)
+        acc = {}
+        for _ in range(3):
+            step(env, wrap)
+            for k, v in eng.stage_ms().items():
+                acc[k] = acc.get(k, 0.0) + v / 3
+        eng.profile(False)
+        st = dict(eng.last_stats)
+        results[mode] = dict(ms=ms, fps=world * F * args.steps / (ms * 1e-3), stages=acc, stats=st,
+                             V=int(wrap._views(list(CAMERAS))[0].shape[0]))
+        if mode == "strict":
+            results[mode].update(clocks=clocks, launches=launches)
+            # e2e: host (pinned) inputs every step, uint8 observations read back to pinned host memory
+            env_h, wrap_h = build(False, True)
+            pinned = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8).pin_memory()
+            ms_e = timed(env_h, wrap_h, args.steps, args.warmup, d2h=pinned)
+            results["e2e"] = dict(ms=ms_e, fps=world * F * args.steps / (ms_e * 1e-3), h2d=env_h.h2d_bytes,
+                                  d2h=pinned.numel())
+            del env_h, wrap_h
+        del env, wrap
+        torch.cuda.empty_cache()
+
+    if rank == 0:
+        r = results["strict"]
+        peak, peak_src = peaks()
+        Nm = int((scene_cpu._semantics.reshape(-1) >= 0).sum())
+        D, M = r["stats"]["D"], r["stats"]["merged"]
+        stages = r["stages"]
+        dom = max(stages, key=stages.get)
+        # algorithmic bytes per launch of each stage: N static reads once per VIEW,
+        # movable Gaussians once per FRAME, D tile entries, M merged entries.
+        V = r["V"]
+        alg = {
+            "preprocess_static": V * N_GAUSS * (12 + 12 + 16 + 4 + 4 + 4),
+            "preprocess_dynamic": F * Nm * (12 + 12 + 12 + 16 + 4 + 4 + 4 + 4),
+            "scatter": (V * N_GAUSS + F * Nm) * 4 + D * 8,
+            "sort": D * (8 + 8 + 48 + 48),
+            "merge": M * 2 * 56,
+            "blend": (D + M) * 48 + F * H * W * 3,  # upper bound: early termination reads less
+        }
+        ach = alg.get(dom, 0) / (stages[dom] * 1e-3) / 1e9 if stages[dom] > 0 else 0.0
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            fps_c, ms_c, cores = cpu_reference_sample(scene_cpu, 1, 3, 1)
+            cpu = {"value": fps_c, "unit": "frames/s", "cores": cores, "kind": "port",
+                   "sample": f"1 env x 2 cams per step (of {B}), 3 steps, same 1M-Gaussian scene, oracle/ port"}
+        line = {
+            "metric": METRIC, "value": r["fps"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "envs_per_gpu": B, "frames_per_step_per_gpu": F, "views": V,
+                       "cameras": "strict (env-0 camera for every env = reference behaviour, gs_world_wrapper.py:280-281)",
+                       "l2": "inputs larger than L2 (236 MB scene + GB-scale workspace per step), no explicit flush",
+                       "parallelism": f"env-sharded x{world}, scene replicated, uint8 all-gather"},
+            "e2e": {"value": results["e2e"]["fps"], "unit": "frames/s", "h2d_bytes_per_step": results["e2e"]["h2d"],
+                    "d2h_bytes_per_step": results["e2e"]["d2h"], "ms_per_step": results["e2e"]["ms"] / args.steps},
+            "gpu_launches": r["launches"],
+            "clocks": r["clocks"],
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel_ms": stages[dom]},
+            "stages_ms": {k: round(v, 4) for k, v in stages.items()},
+            "stage_gbs": {k: round(alg[k] / (stages[k] * 1e-3) / 1e9, 1) for k in alg if stages.get(k, 0) > 0},
+            "counts": {"N": N_GAUSS, "movable": Nm, "D": D, "merged": M},
+            "per_env_cameras": {"value": results["per_env"]["fps"], "ms_per_step": results["per_env"]["ms"] / args.steps,
+                                "views": results["per_env"]["V"],
+                                "stages_ms": {k: round(v, 4) for k, v in results["per_env"]["stages"].items()},
+                                "counts": results["per_env"]["stats"]},
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.steps is None:
+        args.steps = 10 if args.impl == "reference" else 20
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

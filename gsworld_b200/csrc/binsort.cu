@@ -304,6 +304,7 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t*
   scan_local_kernel<<<(unsigned)nb, kScanBlock, 0, s>>>(in, out_excl, n, sums);
   scan_sums_kernel<<<1, kScanBlock, 0, s>>>(sums, nb, total);
   scan_add_kernel<<<(unsigned)nb, kScanBlock, 0, s>>>(out_excl, n, sums, total);
+  count_launches(3);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -325,6 +326,7 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, in
   sort_bins_kernel<true><<<(unsigned)nbins, 512, 0, s>>>(
       w.bin_off.as<uint32_t>(), nbins, V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
       w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>(), cap);
+  count_launches(2);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -342,6 +344,7 @@ int launch_merge(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, c
                                             w.merge_off.as<uint32_t>(), w.keys.as<unsigned long long>(),
                                             w.splats.as<Splat>(), w.tdesc.as<TileDesc>(), cap,
                                             w.status.as<long long>());
+  count_launches(2);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -357,6 +360,7 @@ int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint6
   frame_lists_kernel<<<T, 256, 0, s>>>(T, frame, w.tdesc.as<TileDesc>(), w.merge_off.as<uint32_t>(),
                                        w.keys.as<unsigned long long>(), ranges,
                                        reinterpret_cast<unsigned long long*>(keys), vals, cap);
+  count_launches(2);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

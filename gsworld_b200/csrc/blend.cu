@@ -117,6 +117,7 @@ int launch_blend(const gsw_ctx* ctx, int32_t F, const FrameGeom& g, const float 
   auto& w = ctx->ws;
   blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.tdesc.as<TileDesc>(), w.splats.as<Splat>(), g, bg[0], bg[1], bg[2],
                                             nullptr, out_u8, out_color, out_invdepth);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -126,6 +127,7 @@ int launch_blend_bgdev(const gsw_ctx* ctx, const FrameGeom& g, const float* bg_d
   auto& w = ctx->ws;
   blend_kernel<<<(unsigned)g.T, 256, 0, s>>>(w.tdesc.as<TileDesc>(), w.splats.as<Splat>(), g, 0.f, 0.f, 0.f, bg_dev,
                                              nullptr, out_color, out_invdepth);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

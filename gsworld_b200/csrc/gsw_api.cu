@@ -1,4 +1,5 @@
 // gsw_api.cu — extern "C" entry points of libgsw.so and launch orchestration.  See include/gsw.h.
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -9,6 +10,8 @@
 namespace gsw {
 
 thread_local std::string g_last_error;
+static std::atomic<long long> g_launches{0};
+void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
   char buf[1024];
@@ -123,22 +126,32 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 64, s));
+  auto mark = [&](int k) {
+    if (ctx->profile) cudaEventRecord(ctx->stage_evt[k], s);
+  };
 
+  mark(0);
   if ((rc = launch_preprocess(ctx, false, stat, N, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
                               pose, num_slots, s)))
     return rc;
+  mark(1);
   if (dyn && Nm > 0)
     if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * N, g, view, proj, campos, tanfov, frame_env,
                                 frame_view, pose, num_slots, s)))
       return rc;
+  mark(2);
   if ((rc = launch_scan_u32(w.bin_count.as<uint32_t>(), w.bin_off.as<uint32_t>(), nbins, w.scan_tmp.as<uint32_t>(),
                             s)))
     return rc;
+  mark(3);
   if ((rc = launch_scatter(ctx, false, stat, N, V, 0, 0, g, cap, s))) return rc;
   if (dyn && Nm > 0)
     if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * N, g, cap, s))) return rc;
+  mark(4);
   if ((rc = launch_sort_bins(ctx, nbins, V, N, Nm, g, cap, s))) return rc;
+  mark(5);
   if ((rc = launch_merge(ctx, V, F, g, frame_view, nbins, cap, s))) return rc;
+  mark(6);
 
   ctx->last.valid = true;
   ctx->last.V = V;
@@ -187,6 +200,7 @@ int gsw_create(int device, gsw_ctx** out) {
   c->device = device;
   cudaError_t e = cudaMallocHost((void**)&c->h_status, 8 * sizeof(int64_t));
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->done_evt, cudaEventDisableTiming);
+  for (int k = 0; k <= kNumStages && e == cudaSuccess; ++k) e = cudaEventCreate(&c->stage_evt[k]);
   if (e != cudaSuccess) {
     set_error("gsw_create: %s", cudaGetErrorString(e));
     delete c;
@@ -209,6 +223,8 @@ int gsw_destroy(gsw_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   if (c->h_status) cudaFreeHost(c->h_status);
   if (c->done_evt) cudaEventDestroy(c->done_evt);
+  for (int k = 0; k <= kNumStages; ++k)
+    if (c->stage_evt[k]) cudaEventDestroy(c->stage_evt[k]);
   delete c;
   return GSW_OK;
 }
@@ -344,8 +360,10 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   if (rc) return rc;
   c->last.single = false;
   if ((rc = launch_blend(c, d->num_frames, g, d->bg, d->out_rgb_u8, d->out_color, d->out_invdepth, s))) return rc;
+  if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (d->out_radii)
     if ((rc = launch_radii(c, d->out_radii, s))) return rc;
+  if (c->profile) cudaEventRecord(c->stage_evt[8], s);
   return finish_launch(c, s);
 }
 
@@ -372,6 +390,32 @@ int gsw_finish(gsw_ctx* c, int64_t* needed_entries, int64_t stats[4]) {
   return GSW_OK;
 }
 
+long long gsw_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int gsw_profile_enable(gsw_ctx* c, int on) {
+  if (!c) {
+    set_error("gsw_profile_enable: NULL ctx");
+    return GSW_E_INVALID;
+  }
+  c->profile = on != 0;
+  return GSW_OK;
+}
+
+int gsw_profile_read(gsw_ctx* c, float* stage_ms, int n) {
+  if (!c || !stage_ms || n < kNumStages) {
+    set_error("gsw_profile_read: need room for %d stages", kNumStages);
+    return GSW_E_INVALID;
+  }
+  if (!c->profile) {
+    set_error("gsw_profile_read: profiling is off (gsw_profile_enable)");
+    return GSW_E_STATE;
+  }
+  Guard gd(c->device);
+  GSW_CUDA(cudaEventSynchronize(c->stage_evt[kNumStages]));
+  for (int k = 0; k < kNumStages; ++k) GSW_CUDA(cudaEventElapsedTime(&stage_ms[k], c->stage_evt[k], c->stage_evt[k + 1]));
+  return GSW_OK;
+}
+
 int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, const float* bg, int32_t width,
                           int32_t height, const float* means3D, const float* shs, const float* colors_precomp,
                           const float* opacities, const float* scales, float scale_modifier, const float* rotations,
@@ -382,6 +426,14 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   if (!c || P < 0 || width <= 0 || height <= 0 || !bg || !viewmatrix || !projmatrix || !campos) {
     set_error("gsw_rasterize_forward: invalid argument");
     return GSW_E_INVALID;
+  }
+  if (P == 0) {  // upstream leaves the zero-initialised outputs untouched when there is nothing to draw
+    Guard gd0(c->device);
+    const size_t HW0 = (size_t)height * width;
+    if (out_color) GSW_CUDA(cudaMemsetAsync(out_color, 0, 3 * HW0 * 4, (cudaStream_t)stream));
+    if (out_invdepth) GSW_CUDA(cudaMemsetAsync(out_invdepth, 0, HW0 * 4, (cudaStream_t)stream));
+    c->last.valid = false;
+    return GSW_OK;
   }
   if ((shs == nullptr) == (colors_precomp == nullptr)) {
     set_error("Please provide excatly one of either SHs or precomputed colors!");
@@ -400,13 +452,6 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   (void)prefiltered;
   Guard gd(c->device);
   cudaStream_t s = (cudaStream_t)stream;
-  const size_t HW = (size_t)height * width;
-  if (P == 0) {  // upstream leaves the zero-initialised outputs untouched when there is nothing to draw
-    if (out_color) GSW_CUDA(cudaMemsetAsync(out_color, 0, 3 * HW * 4, s));
-    if (out_invdepth) GSW_CUDA(cudaMemsetAsync(out_invdepth, 0, HW * 4, s));
-    c->last.valid = false;
-    return GSW_OK;
-  }
   const int nb = c->nb_user > 0 ? c->nb_user : 1;
   const FrameGeom g = make_geom(height, width, nb, antialiasing, scale_modifier, near_plane);
   GaussArrays st{};
@@ -435,8 +480,10 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   if (rc) return rc;
   c->last.single = true;
   if ((rc = launch_blend_bgdev(c, g, bg, out_color, out_invdepth, s))) return rc;
+  if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (out_radii)
     if ((rc = launch_radii(c, out_radii, s))) return rc;
+  if (c->profile) cudaEventRecord(c->stage_evt[8], s);
   return finish_launch(c, s);
 }
 

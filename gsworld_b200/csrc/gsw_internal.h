@@ -15,6 +15,9 @@ constexpr int kSortSmemKeys = 8192; // largest bin sorted in shared memory (64 K
 
 void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
+void count_launches(int n);  // bookkeeping for gsw_kernel_launches()
+
+constexpr int kNumStages = 8;  // preprocess_static, preprocess_dynamic, scan, scatter, sort, merge, blend, radii
 
 #define GSW_CUDA(expr)                                                                   \
   do {                                                                                   \
@@ -121,6 +124,8 @@ struct gsw_ctx {
     const int32_t* frame_view = nullptr;
   } last;
   int64_t* h_status = nullptr;  // pinned: [0]=D, [1]=merged, [2]=overflow flag
+  bool profile = false;         // record an event after every stage (gsw_profile_*)
+  cudaEvent_t stage_evt[gsw::kNumStages + 1] = {};
   cudaEvent_t done_evt = nullptr;
   int64_t launches = 0;
 };

@@ -482,6 +482,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
                                                   w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
                                                   w.bin_count.as<uint32_t>());
   }
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -499,6 +500,7 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
     scatter_kernel<false><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
                                                w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -512,6 +514,7 @@ int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_
       L.N, L.Nm, L.V, frame, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(), L.g, w.recA.as<float4>(),
       w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(), radii, tiles_touched, depth, xy, conic_opacity,
       rgb);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -523,6 +526,7 @@ int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s) {
   dim3 grid((unsigned)((L.N + 255) / 256), (unsigned)L.F);
   radii_kernel<<<grid, 256, 0, s>>>(L.N, L.Nm, L.V, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(),
                                     w.rad.as<int32_t>(), out_radii);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -531,6 +535,7 @@ int launch_mark_visible(int32_t P, const float* means3D, const float* viewmatrix
                         cudaStream_t s) {
   if (P <= 0) return 0;
   mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, near_plane, out);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -541,6 +546,7 @@ int launch_gather_movable(const gsw_ctx* ctx, cudaStream_t s) {
       ctx->Nm, ctx->mov_idx.as<int32_t>(), ctx->scene, ctx->mov_xyz.as<float>(), ctx->mov_scale_act.as<float>(),
       ctx->mov_opacity.as<float>(), ctx->mov_sh.as<float>(), ctx->mov_log_scale.as<float>(),
       ctx->mov_quat_raw.as<float>(), ctx->mov_slot.as<int32_t>());
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

@@ -192,6 +192,20 @@ class Engine:
                                              float(near), _ptr(out), self._stream()))
         return out.bool()
 
+    # -- measurement hooks --
+    STAGES = ("preprocess_static", "preprocess_dynamic", "scan", "scatter", "sort", "merge", "blend", "radii")
+
+    def profile(self, on: bool):
+        _lib.check(self.lib.gsw_profile_enable(self._h, int(bool(on))))
+
+    def stage_ms(self):
+        buf = (C.c_float * 8)()
+        _lib.check(self.lib.gsw_profile_read(self._h, buf, 8))
+        return {k: float(buf[i]) for i, k in enumerate(self.STAGES)}
+
+    def kernel_launches(self) -> int:
+        return int(self.lib.gsw_kernel_launches())
+
     # -- parity taps --
     def debug_frame_attrs(self, frame: int):
         N, d = self._last_N(), self.device

@@ -67,6 +67,9 @@ class GSWorldWrapper(_Base):
         self.log_state = log_state
         self.cam_randomization = cam_randomization
         self.strict_reference = strict_reference
+        # True: wait for each launch and auto-grow the tile-entry workspace on overflow (safe default).
+        # False: fully asynchronous steps; call self._engine.finish() yourself to validate.
+        self.sync_each_step = True
         fam = rt.robot_family(scene_gs_cfg_name)
         self.gs_semantics = dict(rt.LINK_LABELS[fam])
         self.sim2gs_arm_trans = torch.tensor(rt.SIM2GS_ROBOT[fam], dtype=torch.float32, device=self.device)
@@ -192,28 +195,65 @@ class GSWorldWrapper(_Base):
                       image_name=cam_name, uid=0, data_device=device)
 
     def _views(self, cam_names):
-        """Stack the view tensors the engine consumes: strict -> one view per camera, else one per (camera, env)."""
+        """Stack the view tensors the engine consumes and the frame -> view map.
+
+        strict_reference: one view per camera from env 0's parameters through the reference's own numpy
+        path (bit-identical camera matrices).  Otherwise each env's own camera, composed batched on the
+        device in fp32 (no .cpu() round trip); a camera whose parameters are identical for every env
+        (fixed third-person mount) is collapsed to a single view so the static scene is projected once."""
         params = self.base_env.get_sensor_params()
-        envs = [0] if self.strict_reference else list(range(self.num_envs))
-        cams = [[self._camera_for(params[c], c, e, self.device) for e in envs] for c in cam_names]
-        self.gs_cam = {c: cams[i][0] for i, c in enumerate(cam_names)}
-        flat = [cam for per in cams for cam in per]
-        view = torch.stack([c.world_view_transform for c in flat])
-        proj = torch.stack([c.full_proj_transform for c in flat])
-        campos = torch.stack([c.camera_center for c in flat])
-        tanfov = torch.tensor([[math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5)] for c in flat],
-                              dtype=torch.float32, device=self.device)
-        return view.contiguous(), proj.contiguous(), campos.contiguous(), tanfov
+        B = self.num_envs
+        if self.strict_reference:
+            cams = [self._camera_for(params[c], c, 0, self.device) for c in cam_names]
+            self.gs_cam = dict(zip(cam_names, cams))
+            view = torch.stack([c.world_view_transform for c in cams])
+            proj = torch.stack([c.full_proj_transform for c in cams])
+            campos = torch.stack([c.camera_center for c in cams])
+            tanfov = torch.tensor([[math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5)] for c in cams],
+                                  dtype=torch.float32, device=self.device)
+            fv = torch.arange(len(cam_names), dtype=torch.int32, device=self.device).repeat_interleave(B)
+            return view.contiguous(), proj.contiguous(), campos.contiguous(), tanfov, fv
+        views, projs, centers, tans, fvs, base = [], [], [], [], [], 0
+        for c in cam_names:
+            ext = params[c]["extrinsic_cv"].to(self.device, torch.float32)
+            K = params[c]["intrinsic_cv"].to(self.device, torch.float32)
+            shared = bool(((ext == ext[:1]).all() & (K == K[:1]).all()).item())
+            if shared:
+                ext, K = ext[:1], K[:1]
+            H, W = self._sensor_hw(c)
+            v, p, cc, tf = self._camera_batch(ext, K, H, W)
+            views.append(v); projs.append(p); centers.append(cc); tans.append(tf)
+            n = v.shape[0]
+            fvs.append(torch.full((B,), base, dtype=torch.int32, device=self.device) if shared
+                       else base + torch.arange(B, dtype=torch.int32, device=self.device))
+            base += n
+        return (torch.cat(views).contiguous(), torch.cat(projs).contiguous(), torch.cat(centers).contiguous(),
+                torch.cat(tans).contiguous(), torch.cat(fvs).contiguous())
+
+    def _camera_batch(self, ext, K, H, W, znear=0.01, zfar=100.0):
+        """cam_maniskill2gs + Camera.__init__ for n cameras at once, fp32 on the device."""
+        n, dev = ext.shape[0], ext.device
+        bottom = torch.tensor([0.0, 0.0, 0.0, 1.0], device=dev).expand(n, 1, 4)
+        c2w = torch.linalg.inv(torch.cat([ext, bottom], 1))
+        c2w[:, :3, 3] = c2w[:, :3, 3] * self.scale_sim2real
+        w2c = torch.linalg.inv(self.rigid_sim2real @ c2w)  # == getWorld2View2(R, T) for trans=0, scale=1
+        view = w2c.transpose(1, 2).contiguous()
+        tanx = W / (2 * K[:, 0, 0])  # tan(FoVx/2) with FoVx = 2 atan(W / 2fx)
+        tany = H / (2 * K[:, 1, 1])
+        P = torch.zeros((n, 4, 4), device=dev)
+        P[:, 0, 0] = 1.0 / tanx
+        P[:, 1, 1] = 1.0 / tany
+        P[:, 3, 2] = 1.0
+        P[:, 2, 2] = zfar / (zfar - znear)
+        P[:, 2, 3] = -(zfar * znear) / (zfar - znear)
+        proj = view.bmm(P.transpose(1, 2))
+        campos = torch.linalg.inv(view)[:, 3, :3]
+        return view, proj.contiguous(), campos.contiguous(), torch.stack([tanx, tany], 1)
 
     def _maps(self, n_cams):
-        key = (n_cams, self.strict_reference)
-        if key not in self._frame_maps:
-            B = self.num_envs
-            fe = torch.arange(B, dtype=torch.int32).repeat(n_cams)  # frame = cam * B + env
-            cam_of = torch.arange(n_cams, dtype=torch.int32).repeat_interleave(B)
-            fv = cam_of if self.strict_reference else cam_of * B + fe
-            self._frame_maps[key] = (fe.to(self.device), fv.to(self.device).to(torch.int32))
-        return self._frame_maps[key]
+        if n_cams not in self._frame_maps:  # frame = cam * B + env
+            self._frame_maps[n_cams] = torch.arange(self.num_envs, dtype=torch.int32).repeat(n_cams).to(self.device)
+        return self._frame_maps[n_cams]
 
     def _render_gsworld(self, renderer="gaussian-splatting"):
         if renderer != "gaussian-splatting":
@@ -224,11 +264,11 @@ class GSWorldWrapper(_Base):
         gs_renders = {}
         for names in groups:  # one launch set per distinct resolution (the reference sensors share one)
             H, W = self._sensor_hw(names[0])
-            view, proj, campos, tanfov = self._views(names)
-            fe, fv = self._maps(len(names))
+            view, proj, campos, tanfov, fv = self._views(names)
+            fe = self._maps(len(names))
             out = self._engine.render_frames(
                 self._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=self.num_envs, bg=(0.0, 0.0, 0.0),
-                antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True)
+                antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True, finish=self.sync_each_step)
             rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
             for i, c in enumerate(names):
                 gs_renders[c] = rgb[i]

@@ -118,6 +118,15 @@ int gsw_rasterize_forward(gsw_ctx* ctx, int32_t P, int32_t sh_degree, int32_t M,
 int gsw_mark_visible(gsw_ctx* ctx, int32_t P, const float* means3D, const float* viewmatrix, float near_plane,
                      uint8_t* out_visible, gsw_stream stream);
 
+/* ---- measurement hooks (no counterpart in the reference) ---- */
+/* Number of kernels this library has launched in the calling process so far. */
+long long gsw_kernel_launches(void);
+/* With profiling on, every launch records a CUDA event after each stage on the launch stream;
+ * gsw_profile_read waits for the last launch and returns the stage durations in ms, in the order
+ * preprocess_static, preprocess_dynamic, scan, scatter, sort, merge, blend, radii (n >= 8). */
+int gsw_profile_enable(gsw_ctx* ctx, int on);
+int gsw_profile_read(gsw_ctx* ctx, float* stage_ms, int n);
+
 /* ---- parity taps for the LAST gsw_render_frames / gsw_rasterize_forward launch (device outputs) ---- */
 /* Per-Gaussian preprocess results of frame f, indexed by original Gaussian index; any pointer NULL ok. */
 int gsw_debug_frame_attrs(gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,

@@ -38,8 +38,8 @@ def _check_frames(scene, env, wrap, H, W, exact_objects=True):
     params = env.get_sensor_params()
     T = ((H + 15) // 16) * ((W + 15) // 16)
     # second launch with float outputs for the tolerance checks
-    view, proj, campos, tanfov = wrap._views(names)
-    fe, fv = wrap._maps(len(names))
+    view, proj, campos, tanfov, fv = wrap._views(names)
+    fe = wrap._maps(len(names))
     out = eng.render_frames(wrap._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=env.num_envs,
                             want_u8=True, want_color=True, want_invdepth=True, want_radii=True)
     torch.cuda.synchronize()
