@@ -58,6 +58,7 @@ class ReplayEnv:
         self.num_envs = base.num_envs
         self.sensor_hw = base.sensor_hw
         self.cameras = base.cameras
+        self.static_cameras = base.static_cameras
         self._names = [l.name for l in base.agent.robot.get_links()]
         self._states = []
         for _ in range(n_states):
@@ -281,7 +282,8 @@ def run_ours(args):
 
     results = {}
     sampler = None
-    for mode, strict in (("strict", True), ("per_env", False)):
+    modes = (("strict", True),) if args.quick else (("strict", True), ("per_env", False))
+    for mode, strict in modes:
         env, wrap = build(True, strict)
         eng = wrap._engine
         if mode == "strict":
@@ -307,6 +309,10 @@ def run_ours(args):
                              V=int(wrap._views(list(CAMERAS))[0].shape[0]))
         if mode == "strict":
             results[mode].update(clocks=clocks, launches=launches)
+            if args.quick:
+                results["e2e"] = dict(ms=float("nan"), fps=float("nan"), h2d=0, d2h=0)
+                results["per_env"] = results["strict"]
+                continue
             # e2e: host (pinned) inputs every step, uint8 observations read back to pinned host memory
             env_h, wrap_h = build(False, True)
             pinned = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8).pin_memory()
@@ -337,7 +343,7 @@ def run_ours(args):
         }
         ach = alg.get(dom, 0) / (stages[dom] * 1e-3) / 1e9 if stages[dom] > 0 else 0.0
         cpu = None
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and not args.quick:
             fps_c, ms_c, cores = cpu_reference_sample(scene_cpu, 1, 3, 1)
             cpu = {"value": fps_c, "unit": "frames/s", "cores": cores, "kind": "port",
                    "sample": f"1 env x 2 cams per step (of {B}), 3 steps, same 1M-Gaussian scene, oracle/ port"}
@@ -378,6 +384,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quick", action="store_true",
+                    help="profiling aid: strict mode only, no e2e / per-env / cpu legs (line is NOT a bench value)")
     args = ap.parse_args()
     if args.steps is None:
         args.steps = 10 if args.impl == "reference" else 20

@@ -41,6 +41,9 @@ SYMBOLS = {
     "gsw_rasterize_forward": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f, _vp,
                                         _vp, _vp, _vp, _vp, _f, _f, _i32, _i32, _f, _vp, _vp, _vp, _vp]),
     "gsw_mark_visible": (C.c_int, [_vp, _i32, _vp, _vp, _f, _vp, _vp]),
+    "gsw_rig_set": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gsw_compose_poses": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, _vp, _vp]),
+    "gsw_compose_cameras": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, C.c_int, _vp, _f, _vp, _vp, _vp, _vp, _vp]),
     "gsw_kernel_launches": (C.c_longlong, []),
     "gsw_profile_enable": (C.c_int, [_vp, C.c_int]),
     "gsw_profile_read": (C.c_int, [_vp, C.POINTER(C.c_float), C.c_int]),

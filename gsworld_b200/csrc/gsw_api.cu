@@ -219,7 +219,7 @@ int gsw_destroy(gsw_ctx* c) {
   DevBuf* bufs[] = {&w.recA, &w.recB, &w.recC, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
                     &w.keys, &w.splats, &w.tdesc, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
-                    &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos};
+                    &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos, &c->rig.dev};
   for (DevBuf* b : bufs) b->release();
   if (c->h_status) cudaFreeHost(c->h_status);
   if (c->done_evt) cudaEventDestroy(c->done_evt);
@@ -388,6 +388,60 @@ int gsw_finish(gsw_ctx* c, int64_t* needed_entries, int64_t stats[4]) {
     return GSW_E_CAPACITY;
   }
   return GSW_OK;
+}
+
+int gsw_rig_set(gsw_ctx* c, int L, int K, const float* S, const float* S_inv, const float* scan_inv,
+                const float* link_offset, const float* obj_S_inv, const float* obj_offset, const float* obj_scale) {
+  if (!c || L < 0 || K < 0 || L + K <= 0 || L + K > 512 || !S || !S_inv || (L > 0 && !scan_inv) ||
+      (K > 0 && (!obj_S_inv || !obj_offset || !obj_scale))) {
+    set_error("gsw_rig_set: invalid argument");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  memcpy(c->rig.S, S, 64);
+  memcpy(c->rig.S_inv, S_inv, 64);
+  for (int k = 0; k < 3; ++k) c->rig.link_off[k] = link_offset ? link_offset[k] : 0.f;
+  c->rig.L = L;
+  c->rig.K = K;
+  std::vector<float> h((size_t)L * 16 + (size_t)K * 20);
+  if (L) memcpy(h.data(), scan_inv, (size_t)L * 64);
+  if (K) {
+    memcpy(h.data() + (size_t)L * 16, obj_S_inv, (size_t)K * 64);
+    memcpy(h.data() + (size_t)L * 16 + (size_t)K * 16, obj_offset, (size_t)K * 12);
+    memcpy(h.data() + (size_t)L * 16 + (size_t)K * 19, obj_scale, (size_t)K * 4);
+  }
+  int rc = c->rig.dev.reserve(h.size() * 4);
+  if (rc) return rc;
+  GSW_CUDA(cudaMemcpy(c->rig.dev.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
+  c->rig.valid = true;
+  return GSW_OK;
+}
+
+int gsw_compose_poses(gsw_ctx* c, int B, const float* link_mats, const float* obj_pose, int obj_stride,
+                      float* pose_out, gsw_stream stream) {
+  if (!c || !c->rig.valid) {
+    set_error("gsw_compose_poses: call gsw_rig_set first");
+    return GSW_E_STATE;
+  }
+  if (B <= 0 || !pose_out || (c->rig.L > 0 && !link_mats) || (c->rig.K > 0 && (!obj_pose || obj_stride < 7))) {
+    set_error("gsw_compose_poses: invalid argument");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  return launch_compose_poses(c, B, link_mats, obj_pose, obj_stride, pose_out, (cudaStream_t)stream);
+}
+
+int gsw_compose_cameras(gsw_ctx* c, int n, const float* extrinsic_cv, const float* intrinsic_cv, int height,
+                        int width, const float* rigid_sim2real, float scale_sim2real, float* viewmatrix,
+                        float* projmatrix, float* campos, float* tanfov, gsw_stream stream) {
+  if (!c || n < 0 || height <= 0 || width <= 0 || !rigid_sim2real ||
+      (n > 0 && (!extrinsic_cv || !intrinsic_cv || !viewmatrix || !projmatrix || !campos || !tanfov))) {
+    set_error("gsw_compose_cameras: invalid argument");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  return launch_compose_cameras(n, extrinsic_cv, intrinsic_cv, height, width, rigid_sim2real, scale_sim2real,
+                                viewmatrix, projmatrix, campos, tanfov, (cudaStream_t)stream);
 }
 
 long long gsw_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }

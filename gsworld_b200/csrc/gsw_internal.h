@@ -108,6 +108,13 @@ struct gsw_ctx {
   gsw::GaussArrays scene{};
   gsw::DevBuf mov_xyz, mov_scale_act, mov_opacity, mov_sh, mov_log_scale, mov_quat_raw, mov_slot, mov_idx, mov_pos;
   bool have_scene = false;
+  // rig constants (gsw_rig_set): sim->GS similarity, its inverse, per-link scan-pose inverses, objects
+  struct {
+    bool valid = false;
+    int L = 0, K = 0;
+    float S[16] = {}, S_inv[16] = {}, link_off[3] = {};
+    gsw::DevBuf dev;  // [L*16 scan_inv | K*16 obj_S_inv | K*3 obj_off | K obj_scale]
+  } rig;
   // workspace
   gsw::Workspace ws;
   int64_t cap_entries = 0;  // capacity of [sorted lists | merged lists] combined
@@ -155,6 +162,12 @@ int launch_merge(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, c
                  int64_t nbins, int64_t cap, cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                        int64_t cap, cudaStream_t s);
+
+// pose.cu
+int launch_compose_poses(const gsw_ctx* ctx, int B, const float* link_mats, const float* obj_pose, int obj_stride,
+                         float* pose_out, cudaStream_t s);
+int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W, const float* rigid, float scale,
+                           float* view, float* proj, float* campos, float* tanfov, cudaStream_t s);
 
 // blend.cu
 int launch_blend(const gsw_ctx* ctx, int32_t F, const FrameGeom& g, const float bg[3], uint8_t* out_u8,

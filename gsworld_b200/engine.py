@@ -86,6 +86,35 @@ class Engine:
     def reserve_entries(self, n: int):
         _lib.check(self.lib.gsw_reserve_entries(self._h, int(n)))
 
+    # -- per-step pose / camera algebra (one launch each) --
+    def set_rig(self, S, S_inv, scan_inv, link_offset, obj_S_inv, obj_offset, obj_scale):
+        """Host fp32 tensors: S, S_inv (4,4); scan_inv (L,4,4); link_offset (3,) or None;
+        obj_S_inv (K,4,4); obj_offset (K,3); obj_scale (K,)."""
+        h = lambda t: None if t is None else t.detach().to("cpu", torch.float32).contiguous()
+        S, S_inv, scan_inv, link_offset = h(S), h(S_inv), h(scan_inv), h(link_offset)
+        obj_S_inv, obj_offset, obj_scale = h(obj_S_inv), h(obj_offset), h(obj_scale)
+        L = 0 if scan_inv is None else scan_inv.shape[0]
+        K = 0 if obj_S_inv is None else obj_S_inv.shape[0]
+        self._rig_host = (S, S_inv, scan_inv, link_offset, obj_S_inv, obj_offset, obj_scale)
+        p = lambda t: None if t is None or t.numel() == 0 else C.c_void_p(t.data_ptr())
+        _lib.check(self.lib.gsw_rig_set(self._h, L, K, p(S), p(S_inv), p(scan_inv), p(link_offset), p(obj_S_inv),
+                                        p(obj_offset), p(obj_scale)))
+        self.rig_L, self.rig_K = L, K
+
+    def compose_poses(self, link_mats, obj_pose, out):
+        """link_mats (B,L,4,4) fp32 device; obj_pose (B,K,>=7) fp32 device or None; out (B,L+K,20)."""
+        B = out.shape[0]
+        stride = 7 if obj_pose is None else int(obj_pose.shape[-1])
+        _lib.check(self.lib.gsw_compose_poses(self._h, B, _ptr(link_mats), _ptr(obj_pose), stride, _ptr(out),
+                                              self._stream()))
+        return out
+
+    def compose_cameras(self, ext, K, H, W, rigid_sim2real_host, scale_sim2real, view, proj, campos, tanfov):
+        n = ext.shape[0]
+        _lib.check(self.lib.gsw_compose_cameras(self._h, n, _ptr(ext), _ptr(K), int(H), int(W),
+                                                C.c_void_p(rigid_sim2real_host.data_ptr()), float(scale_sim2real),
+                                                _ptr(view), _ptr(proj), _ptr(campos), _ptr(tanfov), self._stream()))
+
     # -- frames --
     def render_frames(self, pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view, H, W, *,
                       num_envs, bg=(0.0, 0.0, 0.0), antialiasing=False, scale_modifier=1.0, near=NEAR_GSWORLD,

@@ -279,6 +279,7 @@ class FakeEnv:
         self.robot_uid = robot
         self.agent = SimpleNamespace(uid=robot, robot=_Robot(robot, self))
         self.cameras = tuple(cameras)
+        self.static_cameras = tuple(c for c in self.cameras if c != "wrist_cam")  # world-fixed mounts
         self.sensor_hw = {c: tuple(hw) for c in self.cameras}
         self.objects = tuple(objects)
         self._rng = np.random.default_rng(seed)

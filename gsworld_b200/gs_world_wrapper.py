@@ -58,7 +58,8 @@ class GSWorldWrapper(_Base):
     def __init__(self, env, robot_pipe, scene_gs_cfg_name: str = "franka_merger",
                  device: Union[str, torch.device] = "cuda", log_state: bool = False,
                  state_log_path: str = "./exp_log", cam_randomization: bool = False, *, merged_model=None,
-                 scan_link_mats=None, strict_reference: bool = True, engine: Optional[Engine] = None):
+                 scan_link_mats=None, strict_reference: bool = True, engine: Optional[Engine] = None,
+                 fused_host: bool = True):
         super().__init__(env)
         self.num_envs = env.num_envs
         self.robot_pipe = robot_pipe
@@ -70,6 +71,9 @@ class GSWorldWrapper(_Base):
         # True: wait for each launch and auto-grow the tile-entry workspace on overflow (safe default).
         # False: fully asynchronous steps; call self._engine.finish() yourself to validate.
         self.sync_each_step = True
+        # True: pose table and camera matrices come from one libgsw launch each (no host sync).
+        # False: the reference's own torch / numpy statements (slow; kept for validation).
+        self.fused_host = fused_host
         fam = rt.robot_family(scene_gs_cfg_name)
         self.gs_semantics = dict(rt.LINK_LABELS[fam])
         self.sim2gs_arm_trans = torch.tensor(rt.SIM2GS_ROBOT[fam], dtype=torch.float32, device=self.device)
@@ -129,6 +133,13 @@ class GSWorldWrapper(_Base):
             f(g._scaling), f(g._rotation), slot.to(dev).contiguous(), self.num_slots)
         self._pose = torch.zeros((self.num_envs, self.num_slots, _lib.POSE_STRIDE), dtype=torch.float32, device=dev)
         self._frame_maps = {}
+        self._engine.set_rig(
+            S, self._S_inv, self._scan_inv, self._xarm_off if self._is_xarm else None,
+            torch.stack(self._obj_S_inv) if K else None, torch.stack(self._obj_off) if K else None,
+            torch.tensor(self._obj_scale) if K else None)
+        self._rigid_host = self.rigid_sim2real.detach().to("cpu", torch.float32).contiguous()
+        self._scale_host = float(self.scale_sim2real)
+        self._cam_bufs = {}
 
     # ------------------------------------------------------------------ per step
     def transform_gs_perlink(self, splats=None, gs_init_qpos=None, target_mat=None, eef_pos=None):
@@ -138,7 +149,17 @@ class GSWorldWrapper(_Base):
         part (gs_utils.transform_gaussians) is fused into the rasterizer's preprocess kernel."""
         be, dev = self.base_env, self.device
         links = be.agent.robot.get_links()
-        M = torch.stack([l.pose.to_transformation_matrix().to(dev, torch.float32) for l in links], 1)  # (B,L,4,4)
+        M = torch.stack([l.pose.to_transformation_matrix() for l in links], 1)  # (B,L,4,4)
+        M = M.to(dev, torch.float32, non_blocking=True).contiguous()
+        if self.fused_host:
+            obj = None
+            if self._obj_names:
+                actors = be.get_state_dict()["actors"]
+                obj = torch.stack([actors[n][:, :7] for n in self._obj_names], 1)
+                obj = obj.to(dev, torch.float32, non_blocking=True).contiguous()
+                for name in self._obj_names:
+                    self.gs_semantics[name] = self.obj_gs_semantics[name]
+            return self._engine.compose_poses(M, obj, self._pose)
         if self._is_xarm:
             M = M.clone()
             M[:, :, :3, 3] += self._xarm_off
@@ -203,6 +224,8 @@ class GSWorldWrapper(_Base):
         (fixed third-person mount) is collapsed to a single view so the static scene is projected once."""
         params = self.base_env.get_sensor_params()
         B = self.num_envs
+        if self.fused_host:
+            return self._views_fused(params, cam_names)
         if self.strict_reference:
             cams = [self._camera_for(params[c], c, 0, self.device) for c in cam_names]
             self.gs_cam = dict(zip(cam_names, cams))
@@ -229,6 +252,35 @@ class GSWorldWrapper(_Base):
             base += n
         return (torch.cat(views).contiguous(), torch.cat(projs).contiguous(), torch.cat(centers).contiguous(),
                 torch.cat(tans).contiguous(), torch.cat(fvs).contiguous())
+
+    def _views_fused(self, params, cam_names):
+        """Camera matrices through gsw_compose_cameras: no host sync.  strict -> env 0's camera for every env;
+        otherwise one view per (camera, env) unless the env exposes `static_cameras` naming world-fixed ones."""
+        B, dev = self.num_envs, self.device
+        static = set(getattr(self.base_env, "static_cameras", ()))
+        key = (tuple(cam_names), self.strict_reference)
+        if key not in self._cam_bufs:
+            counts = [1 if (self.strict_reference or c in static) else B for c in cam_names]
+            V = sum(counts)
+            fv, base = [], 0
+            for n in counts:
+                fv.append(torch.full((B,), base, dtype=torch.int32) if n == 1
+                          else base + torch.arange(B, dtype=torch.int32))
+                base += n
+            z = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+            self._cam_bufs[key] = dict(counts=counts, view=z(V, 16), proj=z(V, 16), campos=z(V, 3), tanfov=z(V, 2),
+                                       fv=torch.cat(fv).to(dev))
+        cb = self._cam_bufs[key]
+        base = 0
+        for c, n in zip(cam_names, cb["counts"]):
+            H, W = self._sensor_hw(c)
+            ext = params[c]["extrinsic_cv"][:n].to(dev, torch.float32, non_blocking=True).contiguous()
+            K = params[c]["intrinsic_cv"][:n].to(dev, torch.float32, non_blocking=True).contiguous()
+            sl = slice(base, base + n)
+            self._engine.compose_cameras(ext, K, H, W, self._rigid_host, self._scale_host, cb["view"][sl],
+                                         cb["proj"][sl], cb["campos"][sl], cb["tanfov"][sl])
+            base += n
+        return cb["view"], cb["proj"], cb["campos"], cb["tanfov"], cb["fv"]
 
     def _camera_batch(self, ext, K, H, W, znear=0.01, zfar=100.0):
         """cam_maniskill2gs + Camera.__init__ for n cameras at once, fp32 on the device."""

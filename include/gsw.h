@@ -25,6 +25,14 @@
  *                             graphdeco-inria/diff-gaussian-rasterization@9c5c2028, near plane 0.05 per
  *                             GSWorld README.md:33).
  *   gsw_mark_visible       <- GaussianRasterizer.markVisible (same absent extension).
+ *   gsw_rig_set / gsw_compose_poses
+ *                          <- the matrix algebra of transform_gs_perlink: link_trans = S @ M_link @
+ *                             inv(M_scan) @ inv(S) (gs_world_wrapper.py:115-120), objects through
+ *                             extract_rigid_transform (gs_world_wrapper.py:139-156, pcd_utils.py:224-252)
+ *                             and matrix_to_quaternion (gs_utils.py:322).
+ *   gsw_compose_cameras    <- GSWorldWrapper.cam_maniskill2gs (gs_world_wrapper.py:277-325) + Camera.__init__
+ *                             (scene/cameras.py:80-89) + getWorld2View2/getProjectionMatrix
+ *                             (utils/graphics_utils.py:38-71), without the .cpu() round trips.
  *   gsw_debug_*            <- no counterpart; parity taps (tiles_touched, sorted keys, tile ranges).
  */
 #ifndef GSW_H_
@@ -117,6 +125,24 @@ int gsw_rasterize_forward(gsw_ctx* ctx, int32_t P, int32_t sh_degree, int32_t M,
 
 int gsw_mark_visible(gsw_ctx* ctx, int32_t P, const float* means3D, const float* viewmatrix, float near_plane,
                      uint8_t* out_visible, gsw_stream stream);
+
+/* Rig constants, HOST pointers, row-major 4x4: S = sim->GS similarity of the robot, S_inv its inverse,
+ * scan_inv[L] = inverse link poses at the scan qpos, link_offset[3] (xarm: 0,0,0.05; NULL = none),
+ * obj_S_inv[K] = inverse object similarities, obj_offset[K,3], obj_scale[K].  Synchronises. */
+int gsw_rig_set(gsw_ctx* ctx, int L, int K, const float* S, const float* S_inv, const float* scan_inv,
+                const float* link_offset, const float* obj_S_inv, const float* obj_offset, const float* obj_scale);
+/* One launch: pose_out[B, L+K, GSW_POSE_STRIDE] from link_mats[B,L,16] (sim-world link poses) and
+ * obj_pose[B,K,obj_stride] (p(3), q_wxyz(4), ...; obj_stride >= 7), all device pointers.
+ * fp32 like the reference; the polar factor of object transforms is computed in fp64. */
+int gsw_compose_poses(gsw_ctx* ctx, int B, const float* link_mats, const float* obj_pose, int obj_stride,
+                      float* pose_out, gsw_stream stream);
+/* One launch: n cameras from OpenCV extrinsics[n,3,4] and intrinsics[n,3,3] (device) to the transposed
+ * view / full-projection matrices, camera centre and tan(fov/2) the rasterizer consumes.
+ * rigid_sim2real: HOST 4x4 row-major.  Evaluated in fp64 and rounded once (the reference mixes fp32
+ * torch and fp64 numpy): agrees with it to ~1 ulp of fp32, not bit-for-bit. */
+int gsw_compose_cameras(gsw_ctx* ctx, int n, const float* extrinsic_cv, const float* intrinsic_cv, int height,
+                        int width, const float* rigid_sim2real, float scale_sim2real, float* viewmatrix,
+                        float* projmatrix, float* campos, float* tanfov, gsw_stream stream);
 
 /* ---- measurement hooks (no counterpart in the reference) ---- */
 /* Number of kernels this library has launched in the calling process so far. */
