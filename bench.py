@@ -282,7 +282,7 @@ def run_ours(args):
 
     results = {}
     sampler = None
-    modes = (("strict", True),) if args.quick else (("strict", True), ("per_env", False))
+    modes = (("strict", not args.quick_per_env),) if args.quick else (("strict", True), ("per_env", False))
     for mode, strict in modes:
         env, wrap = build(True, strict)
         eng = wrap._engine
@@ -327,19 +327,18 @@ def run_ours(args):
         r = results["strict"]
         peak, peak_src = peaks()
         Nm = int((scene_cpu._semantics.reshape(-1) >= 0).sum())
-        D, M = r["stats"]["D"], r["stats"]["merged"]
+        D, R = r["stats"]["D"], r["stats"]["staged"]
         stages = r["stages"]
         dom = max(stages, key=stages.get)
         # algorithmic bytes per launch of each stage: N static reads once per VIEW,
-        # movable Gaussians once per FRAME, D tile entries, M merged entries.
+        # movable Gaussians once per FRAME, D tile entries built, R entries staged by the blend.
         V = r["V"]
         alg = {
             "preprocess_static": V * N_GAUSS * (12 + 12 + 16 + 4 + 4 + 4),
             "preprocess_dynamic": F * Nm * (12 + 12 + 12 + 16 + 4 + 4 + 4 + 4),
             "scatter": (V * N_GAUSS + F * Nm) * 4 + D * 8,
             "sort": D * (8 + 8 + 48 + 48),
-            "merge": M * 2 * 56,
-            "blend": (D + M) * 48 + F * H * W * 3,  # upper bound: early termination reads less
+            "blend": R * 48 + F * H * W * 3,
         }
         ach = alg.get(dom, 0) / (stages[dom] * 1e-3) / 1e9 if stages[dom] > 0 else 0.0
         cpu = None
@@ -364,7 +363,7 @@ def run_ours(args):
                          "kernel_ms": stages[dom]},
             "stages_ms": {k: round(v, 4) for k, v in stages.items()},
             "stage_gbs": {k: round(alg[k] / (stages[k] * 1e-3) / 1e9, 1) for k in alg if stages.get(k, 0) > 0},
-            "counts": {"N": N_GAUSS, "movable": Nm, "D": D, "merged": M},
+            "counts": {"N": N_GAUSS, "movable": Nm, "D": D, "blend_staged": R},
             "per_env_cameras": {"value": results["per_env"]["fps"], "ms_per_step": results["per_env"]["ms"] / args.steps,
                                 "views": results["per_env"]["V"],
                                 "stages_ms": {k: round(v, 4) for k, v in results["per_env"]["stages"].items()},
@@ -384,6 +383,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quick-per-env", action="store_true", help="with --quick: profile the per-env-camera mode")
     ap.add_argument("--quick", action="store_true",
                     help="profiling aid: strict mode only, no e2e / per-env / cpu legs (line is NOT a bench value)")
     args = ap.parse_args()

@@ -144,8 +144,9 @@ __device__ __forceinline__ uint32_t pow2ceil(uint32_t n) {
   return n <= 1 ? 1u : 1u << (32 - __clz(n - 1));
 }
 
-// One CTA per bin.  BIG=false: bins with n <= kSortSmemKeys, sorted in shared memory;
-// BIG=true: larger bins, same network run directly on global memory (L2) by one CTA.
+// BIG=false: one CTA per bin, bins with n <= kSortSmemKeys sorted in shared memory.
+// BIG=true: a small persistent grid strides over all bins and sorts the (rare) larger ones directly in
+// global memory (L2) with the same network, one CTA per bin.
 template <bool BIG>
 __global__ void __launch_bounds__(512)
 sort_bins_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t V, int64_t N, int64_t Nm,
@@ -153,134 +154,84 @@ sort_bins_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t V,
                  const float4* __restrict__ recA, const float4* __restrict__ recB, const float4* __restrict__ recC,
                  Splat* __restrict__ splats, int64_t cap) {
   extern __shared__ unsigned long long skeys[];
-  const int64_t bin = blockIdx.x;
-  const uint32_t start = bin_off[bin];
-  const uint32_t end = bin_off[bin + 1];
-  if (end <= start || (int64_t)end > cap) return;
-  const uint32_t n = end - start;
-  if (BIG != (n > (uint32_t)kSortSmemKeys)) return;
-  const uint32_t n2 = pow2ceil(n);
-  unsigned long long* g = keys + start;
-  if (!BIG) {
-    for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) skeys[t] = g[t];
-    __syncthreads();
-    if (n > 1) bitonic_sort(skeys, n, n2);
-  } else {
-    __syncthreads();
-    bitonic_sort(g, n, n2);
-  }
-  // gather the sorted records into the blend stream
-  const int64_t list = bin / bins_per_list;
-  const bool dyn = list >= V;
-  const int64_t item_base = dyn ? (int64_t)V * N + (list - V) * Nm : list * N;
-  for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) {
-    const unsigned long long key = BIG ? g[t] : skeys[t];
-    if (!BIG) g[t] = key;
-    const uint32_t idx = (uint32_t)(key & 0xffffffffull);
-    const int64_t item = item_base + (dyn ? (int64_t)mov_pos[idx] : (int64_t)idx);
-    const float4 a = recA[item], b = recB[item], c = recC[item];
-    Splat sp;
-    sp.a = a;
-    sp.b = b;
-    sp.c = make_float4(c.x, c.y, c.z, 1 / c.w);
-    splats[start + t] = sp;
+  for (int64_t bin = blockIdx.x; bin < nbins; bin += gridDim.x) {
+    const uint32_t start = bin_off[bin];
+    const uint32_t end = bin_off[bin + 1];
+    if (end <= start || (int64_t)end > cap) continue;
+    const uint32_t n = end - start;
+    if (BIG != (n > (uint32_t)kSortSmemKeys)) continue;
+    const uint32_t n2 = pow2ceil(n);
+    unsigned long long* g = keys + start;
+    if (!BIG) {
+      for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) skeys[t] = g[t];
+      __syncthreads();
+      if (n > 1) bitonic_sort(skeys, n, n2);
+    } else {
+      __syncthreads();
+      bitonic_sort(g, n, n2);
+    }
+    // gather the sorted records into the blend stream.  The conic is pre-scaled so the blend evaluates
+    // alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A, B' = -log2(e) B, C' = -0.5 log2(e) C.
+    const int64_t list = bin / bins_per_list;
+    const bool dyn = list >= V;
+    const int64_t item_base = dyn ? (int64_t)V * N + (list - V) * Nm : list * N;
+    constexpr float kLog2e = 1.4426950408889634f;
+    for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) {
+      const unsigned long long key = BIG ? g[t] : skeys[t];
+      if (!BIG) g[t] = key;
+      const uint32_t idx = (uint32_t)(key & 0xffffffffull);
+      const int64_t item = item_base + (dyn ? (int64_t)mov_pos[idx] : (int64_t)idx);
+      const float4 a = recA[item], b = recB[item], c = recC[item];
+      Splat sp;
+      sp.a = a;
+      sp.b = make_float4(-0.5f * kLog2e * b.x, -kLog2e * b.y, -0.5f * kLog2e * b.z, b.w);
+      sp.c = make_float4(c.x, c.y, c.z, 1 / c.w);
+      splats[start + t] = sp;
+    }
+    __syncthreads();  // skeys is reused by the next bin of this CTA (BIG grid only loops)
   }
 }
 
-// ---- static/dynamic merge ----
-// Pass 1: per (frame, tile): counts, and how many merged entries it needs (0 if one of the lists is empty)
-__global__ void merge_plan_kernel(int32_t V, int32_t F, int32_t T, int32_t NB, const int32_t* __restrict__ frame_view,
-                                  const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ merge_cnt) {
-  const int64_t ft = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (ft >= (int64_t)F * T) return;
-  const int f = (int)(ft / T), tile = (int)(ft % T);
-  const int v = frame_view[f];
-  const int64_t sb = ((int64_t)v * T + tile) * NB, db = ((int64_t)(V + f) * T + tile) * NB;
-  const uint32_t ns = bin_off[sb + NB] - bin_off[sb];
-  const uint32_t nd = bin_off[db + NB] - bin_off[db];
-  merge_cnt[ft] = (ns > 0 && nd > 0) ? ns + nd : 0u;
+// Debug: lists of one frame in blend order (static view list merged with the frame's dynamic list), in the
+// reference's key format (tile << 32 | depth bits) + Gaussian index.
+__global__ void frame_counts_kernel(int32_t V, int32_t T, int32_t NB, int32_t frame, const int32_t* frame_view,
+                                    const uint32_t* bin_off, uint32_t* cnt) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const int v = frame_view ? frame_view[frame] : 0;
+  const int64_t sb = ((int64_t)v * T + t) * NB, db = ((int64_t)(V + frame) * T + t) * NB;
+  cnt[t] = (bin_off[sb + NB] - bin_off[sb]) + (bin_off[db + NB] - bin_off[db]);
 }
-
-// Pass 2: one CTA per (frame, tile): write the tile descriptor; where both lists are non-empty, merge them
-// (rank by binary search in the other list; keys are unique) into the merged region after the D sorted entries.
-__global__ void __launch_bounds__(256)
-merge_kernel(int32_t V, int32_t F, int32_t T, int32_t NB, const int32_t* __restrict__ frame_view,
-             const uint32_t* __restrict__ bin_off, int64_t nbins, const uint32_t* __restrict__ merge_off,
-             unsigned long long* __restrict__ keys, Splat* __restrict__ splats, TileDesc* __restrict__ tdesc,
-             int64_t cap, long long* __restrict__ status) {
-  const int64_t ft = blockIdx.x;
-  const int f = (int)(ft / T), tile = (int)(ft % T);
-  const int v = frame_view[f];
-  const int64_t sb = ((int64_t)v * T + tile) * NB, db = ((int64_t)(V + f) * T + tile) * NB;
+__global__ void frame_lists_kernel(int32_t V, int32_t T, int32_t NB, int32_t frame, const int32_t* frame_view,
+                                   const uint32_t* bin_off, const uint32_t* off, const unsigned long long* keys,
+                                   int32_t* ranges, unsigned long long* okeys, uint32_t* ovals, int64_t cap) {
+  const int tile = blockIdx.x;
+  const int v = frame_view ? frame_view[frame] : 0;
+  const int64_t sb = ((int64_t)v * T + tile) * NB, db = ((int64_t)(V + frame) * T + tile) * NB;
   const uint32_t s0 = bin_off[sb], ns = bin_off[sb + NB] - s0;
   const uint32_t d0 = bin_off[db], nd = bin_off[db + NB] - d0;
-  const uint32_t D = bin_off[nbins];
-  const bool overflow = (int64_t)D > cap;
-  TileDesc td;
-  if (overflow) {
-    td.offset = 0;
-    td.count = 0;
-  } else if (nd == 0) {
-    td.offset = s0;
-    td.count = ns;
-  } else if (ns == 0) {
-    td.offset = d0;
-    td.count = nd;
-  } else {
-    const uint32_t m0 = D + merge_off[ft];
-    td.offset = m0;
-    td.count = ns + nd;
-    if ((int64_t)m0 + ns + nd > cap) {
-      td.count = 0;
-      if (threadIdx.x == 0) status[2] = 1;
-    } else {
-      const unsigned long long* ks = keys + s0;
-      const unsigned long long* kd = keys + d0;
-      for (uint32_t t = threadIdx.x; t < ns + nd; t += blockDim.x) {
-        const bool from_s = t < ns;
-        const uint32_t k = from_s ? t : t - ns;
-        const unsigned long long key = from_s ? ks[k] : kd[k];
-        const unsigned long long* other = from_s ? kd : ks;
-        uint32_t lo = 0, hi = from_s ? nd : ns;
-        while (lo < hi) {  // number of keys in `other` smaller than key
-          const uint32_t mid = (lo + hi) >> 1;
-          if (other[mid] < key) lo = mid + 1; else hi = mid;
-        }
-        const uint32_t dst = m0 + k + lo;
-        keys[dst] = key;
-        splats[dst] = splats[(from_s ? s0 : d0) + k];
-      }
-    }
-  }
-  if (threadIdx.x == 0) tdesc[ft] = td;
-  if (ft == 0 && threadIdx.x == 0) {
-    status[0] = (long long)D;
-    status[1] = (long long)merge_off[(int64_t)F * T];
-    if (overflow) status[2] = 1;
-  }
-}
-
-// Debug: lists of one frame in blend order, in the reference's key format (tile << 32 | depth bits)
-__global__ void frame_ranges_kernel(int32_t T, int32_t frame, const TileDesc* tdesc, uint32_t* cnt) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < T) cnt[t] = tdesc[(int64_t)frame * T + t].count;
-}
-__global__ void frame_lists_kernel(int32_t T, int32_t frame, const TileDesc* tdesc, const uint32_t* off,
-                                   const unsigned long long* keys, int32_t* ranges, unsigned long long* okeys,
-                                   uint32_t* ovals, int64_t cap) {
-  const int tile = blockIdx.x;
-  const TileDesc td = tdesc[(int64_t)frame * T + tile];
-  const uint32_t o = off[tile];
+  const uint32_t o = off[tile], n = ns + nd;
   if (threadIdx.x == 0) {
     // empty tiles keep (0,0) like the reference's memset + identifyTileRanges
-    ranges[2 * tile] = td.count ? (int32_t)o : 0;
-    ranges[2 * tile + 1] = td.count ? (int32_t)(o + td.count) : 0;
+    ranges[2 * tile] = n ? (int32_t)o : 0;
+    ranges[2 * tile + 1] = n ? (int32_t)(o + n) : 0;
   }
-  for (uint32_t t = threadIdx.x; t < td.count; t += blockDim.x) {
-    if ((int64_t)o + t >= cap) break;
-    const unsigned long long k = keys[td.offset + t];
-    okeys[o + t] = ((unsigned long long)tile << 32) | (k >> 32);
-    ovals[o + t] = (uint32_t)(k & 0xffffffffull);
+  const unsigned long long* ks = keys + s0;
+  const unsigned long long* kd = keys + d0;
+  for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) {
+    const bool from_s = t < ns;
+    const uint32_t k = from_s ? t : t - ns;
+    const unsigned long long key = from_s ? ks[k] : kd[k];
+    const unsigned long long* other = from_s ? kd : ks;
+    uint32_t lo = 0, hi = from_s ? nd : ns;
+    while (lo < hi) {  // number of keys in the other list smaller than key (keys are unique)
+      const uint32_t mid = (lo + hi) >> 1;
+      if (other[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    const int64_t dst = (int64_t)o + k + lo;
+    if (dst >= cap) continue;
+    okeys[dst] = ((unsigned long long)tile << 32) | (key >> 32);
+    ovals[dst] = (uint32_t)(key & 0xffffffffull);
   }
 }
 
@@ -323,27 +274,10 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, in
   sort_bins_kernel<false><<<(unsigned)nbins, 512, smem, s>>>(
       w.bin_off.as<uint32_t>(), nbins, V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
       w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>(), cap);
-  sort_bins_kernel<true><<<(unsigned)nbins, 512, 0, s>>>(
+  const unsigned big_grid = (unsigned)(nbins < 296 ? nbins : 296);
+  sort_bins_kernel<true><<<big_grid, 512, 0, s>>>(
       w.bin_off.as<uint32_t>(), nbins, V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
       w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>(), cap);
-  count_launches(2);
-  GSW_CUDA(cudaGetLastError());
-  return 0;
-}
-
-int launch_merge(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, const int32_t* frame_view,
-                 int64_t nbins, int64_t cap, cudaStream_t s) {
-  auto& w = ctx->ws;
-  const int64_t FT = (int64_t)F * g.T;
-  if (FT <= 0) return 0;
-  merge_plan_kernel<<<(unsigned)((FT + 255) / 256), 256, 0, s>>>(V, F, g.T, g.NB, frame_view,
-                                                                 w.bin_off.as<uint32_t>(), w.merge_cnt.as<uint32_t>());
-  int rc = launch_scan_u32(w.merge_cnt.as<uint32_t>(), w.merge_off.as<uint32_t>(), FT, w.scan_tmp.as<uint32_t>(), s);
-  if (rc) return rc;
-  merge_kernel<<<(unsigned)FT, 256, 0, s>>>(V, F, g.T, g.NB, frame_view, w.bin_off.as<uint32_t>(), nbins,
-                                            w.merge_off.as<uint32_t>(), w.keys.as<unsigned long long>(),
-                                            w.splats.as<Splat>(), w.tdesc.as<TileDesc>(), cap,
-                                            w.status.as<long long>());
   count_launches(2);
   GSW_CUDA(cudaGetLastError());
   return 0;
@@ -352,13 +286,15 @@ int launch_merge(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, c
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                        int64_t cap, cudaStream_t s) {
   auto& w = ctx->ws;
-  const int32_t T = ctx->last.g.T;
-  // per-tile counts -> exclusive offsets (reuse merge_cnt/merge_off scratch: both hold >= T+1 elements)
-  frame_ranges_kernel<<<(T + 255) / 256, 256, 0, s>>>(T, frame, w.tdesc.as<TileDesc>(), w.merge_cnt.as<uint32_t>());
+  const auto& L = ctx->last;
+  const int32_t T = L.g.T;
+  // per-tile counts -> exclusive offsets (scratch: merge_cnt / merge_off hold >= T+1 elements)
+  frame_counts_kernel<<<(T + 255) / 256, 256, 0, s>>>(L.V, T, L.g.NB, frame, L.frame_view, w.bin_off.as<uint32_t>(),
+                                                      w.merge_cnt.as<uint32_t>());
   int rc = launch_scan_u32(w.merge_cnt.as<uint32_t>(), w.merge_off.as<uint32_t>(), T, w.scan_tmp.as<uint32_t>(), s);
   if (rc) return rc;
-  frame_lists_kernel<<<T, 256, 0, s>>>(T, frame, w.tdesc.as<TileDesc>(), w.merge_off.as<uint32_t>(),
-                                       w.keys.as<unsigned long long>(), ranges,
+  frame_lists_kernel<<<T, 256, 0, s>>>(L.V, T, L.g.NB, frame, L.frame_view, w.bin_off.as<uint32_t>(),
+                                       w.merge_off.as<uint32_t>(), w.keys.as<unsigned long long>(), ranges,
                                        reinterpret_cast<unsigned long long*>(keys), vals, cap);
   count_launches(2);
   GSW_CUDA(cudaGetLastError());

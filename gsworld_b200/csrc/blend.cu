@@ -1,15 +1,21 @@
-// blend.cu — 16x16-tile front-to-back alpha compositing over the sorted splat stream.  sm_100a.
+// blend.cu — 16x16-tile front-to-back alpha compositing over the sorted splat streams.  sm_100a.
 //
-// One CTA per (frame, tile); 8 warps, each owning an 8x4 pixel block.  A chunk of 256 splat records is
-// staged in shared memory; every warp then culls 32 staged records at a time against its own pixel
-// block (one record per lane, one ballot) and runs the per-pixel blend only for the survivors, in list
-// order.  Skipped records are exactly those whose alpha would be < 1/255 on all 32 pixels, which the
-// reference skips too, so the result is unchanged.  Warps whose 32 pixels have all saturated stop
+// One CTA per (frame, tile); 8 warps, each owning an 8x4 pixel block.  A frame's tile list is the merge
+// of two sorted streams: the STATIC list of the frame's view (shared by every env that looks through
+// that camera) and the frame's own DYNAMIC list (robot links / objects of that env).  Chunks of up to
+// 256 records are staged in shared memory; where both streams are non-empty the chunk is produced by a
+// merge-path step over two 256-key windows (keys = depth bits << 32 | Gaussian index, unique), so the
+// blend order is exactly the reference's single sorted list.  Every warp then culls 32 staged records at
+// a time against its own pixel block (one record per lane, one ballot) and runs the per-pixel blend only
+// for the survivors, in list order.  Skipped records are exactly those whose alpha would be < 1/255 on
+// all 32 pixels, which the reference skips too.  Warps whose 32 pixels have all saturated stop
 // evaluating; the CTA leaves when every warp has.
 //
 // Reference arithmetic: diff-gaussian-rasterization@9c5c2028 forward.cu renderCUDA (absent submodule):
 //   power = -0.5(A dx^2 + C dy^2) - B dx dy; skip if > 0; alpha = min(0.99, o*exp(power)); skip if
 //   < 1/255; stop when T(1-alpha) < 1e-4; C += rgb*alpha*T; invD += alpha*T/depth; out = C + T*bg.
+// Here exp(power) is evaluated as 2^(power*log2 e) with the conic pre-scaled at gather time (binsort.cu);
+// colour / inverse depth are tolerance quantities (max-abs 1e-3).
 // uint8 epilogue: gs_world_wrapper.py:268-270 after render()'s clamp(0,1) (gaussian_renderer/__init__.py:119).
 #include "gsw_internal.h"
 
@@ -18,11 +24,29 @@ namespace {
 
 constexpr int kChunk = 256;
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float2 lds64(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+
 __global__ void __launch_bounds__(256)
-blend_kernel(const TileDesc* __restrict__ tdesc, const Splat* __restrict__ splats, FrameGeom g, float bg0, float bg1,
-             float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8, float* __restrict__ out_color,
-             float* __restrict__ out_invd) {
+blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
+             const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats, int64_t cap, FrameGeom g,
+             float bg0, float bg1, float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8,
+             float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status) {
   __shared__ float4 sA[kChunk], sB[kChunk], sC[kChunk];
+  __shared__ unsigned long long kS[kChunk], kD[kChunk];
   const int64_t ft = blockIdx.x;
   const int f = (int)(ft / g.T), tile = (int)(ft % g.T);
   const int tx = tile % g.gx, ty = tile / g.gx;
@@ -32,47 +56,90 @@ blend_kernel(const TileDesc* __restrict__ tdesc, const Splat* __restrict__ splat
   const bool inside = px < g.W && py < g.H;
   const float pxf = (float)px, pyf = (float)py;
   const float bx0 = (float)wx, bx1 = (float)(wx + 7), by0 = (float)wy, by1 = (float)(wy + 3);
-  const TileDesc td = tdesc[ft];
+
+  const int v = frame_view ? frame_view[f] : 0;
+  const int64_t sb = ((int64_t)v * g.T + tile) * g.NB, db = ((int64_t)(V + f) * g.T + tile) * g.NB;
+  const uint32_t s0 = bin_off[sb], d0 = bin_off[db];
+  uint32_t ns = bin_off[sb + g.NB] - s0, nd = bin_off[db + g.NB] - d0;
+  const uint32_t D = bin_off[nbins];
+  if ((int64_t)D > cap) ns = nd = 0;  // workspace overflow: lists are incomplete; the launch is flagged invalid
+  if (ft == 0 && threadIdx.x == 0) {
+    status[0] = (long long)D;
+    if ((int64_t)D > cap) status[2] = 1;
+  }
+  const uint32_t total = ns + nd;
+  uint32_t i0 = 0, j0 = 0;  // consumed from the static / dynamic stream (block-uniform)
+
+  const uint32_t aA = (uint32_t)__cvta_generic_to_shared(sA), aB = (uint32_t)__cvta_generic_to_shared(sB),
+                 aC = (uint32_t)__cvta_generic_to_shared(sC);
 
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
   bool done = !inside;
-
-  for (uint32_t base = 0; base < td.count; base += kChunk) {
+  uint32_t base = 0;
+  for (; base < total; base += kChunk) {
     if (__syncthreads_and(done)) break;  // also protects the staging buffers of the previous round
-    const uint32_t n = min((uint32_t)kChunk, td.count - base);
-    if (threadIdx.x < n) {
-      const Splat* sp = splats + td.offset + base + threadIdx.x;
-      sA[threadIdx.x] = __ldg(&sp->a);
-      sB[threadIdx.x] = __ldg(&sp->b);
-      sC[threadIdx.x] = __ldg(&sp->c);
+    const uint32_t n = min((uint32_t)kChunk, total - base);
+    const uint32_t rs = ns - i0, rd = nd - j0;
+    if (rs == 0 || rd == 0) {  // single-stream chunk
+      const uint32_t src = rd == 0 ? s0 + i0 : d0 + j0;
+      if (threadIdx.x < n) {
+        const Splat* sp = splats + src + threadIdx.x;
+        sA[threadIdx.x] = __ldg(&sp->a);
+        sB[threadIdx.x] = __ldg(&sp->b);
+        sC[threadIdx.x] = __ldg(&sp->c);
+      }
+      if (rd == 0) i0 += n; else j0 += n;
+    } else {  // merge-path over two key windows
+      const uint32_t ws = min((uint32_t)kChunk, rs), wd = min((uint32_t)kChunk, rd);
+      if (threadIdx.x < ws) kS[threadIdx.x] = keys[s0 + i0 + threadIdx.x];
+      if (threadIdx.x < wd) kD[threadIdx.x] = keys[d0 + j0 + threadIdx.x];
+      __syncthreads();
+      bool take_s = false;
+      if (threadIdx.x < n) {
+        const uint32_t t = threadIdx.x;
+        uint32_t lo = t > wd ? t - wd : 0u, hi = min(t, ws);
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (kS[mid] < kD[t - 1 - mid]) lo = mid + 1; else hi = mid;
+        }
+        const uint32_t a = lo, b = t - lo;
+        take_s = a < ws && (b >= wd || kS[a] < kD[b]);
+        const Splat* sp = splats + (take_s ? s0 + i0 + a : d0 + j0 + b);
+        sA[t] = __ldg(&sp->a);
+        sB[t] = __ldg(&sp->b);
+        sC[t] = __ldg(&sp->c);
+      }
+      const uint32_t cs = (uint32_t)__syncthreads_count(take_s);
+      i0 += cs;
+      j0 += n - cs;
     }
     __syncthreads();
     if (__all_sync(0xffffffffu, done)) continue;
-    for (uint32_t j0 = 0; j0 < n; j0 += 32) {
-      const uint32_t j = j0 + lane;
+    for (uint32_t j0w = 0; j0w < n; j0w += 32) {
+      const uint32_t j = j0w + lane;
       bool hit = false;
       if (j < n) {
-        const float4 a = sA[j];
+        const float4 a = lds128(aA + j * 16);
         hit = a.z >= 0.f && !(a.x + a.z < bx0 || a.x - a.z > bx1 || a.y + a.w < by0 || a.y - a.w > by1);
       }
       uint32_t mask = __ballot_sync(0xffffffffu, hit);
       while (mask) {
-        const uint32_t jj = j0 + (uint32_t)(__ffs(mask) - 1);
+        const uint32_t jj = j0w + (uint32_t)(__ffs(mask) - 1);
         mask &= mask - 1;
         if (done) continue;
-        const float4 a = sA[jj];
-        const float4 b = sB[jj];
-        const float dx = a.x - pxf, dy = a.y - pyf;
-        const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
-        if (power > 0.0f) continue;
-        const float alpha = fminf(0.99f, b.w * __expf(power));
+        const float2 xy = lds64(aA + jj * 16);
+        const float4 b = lds128(aB + jj * 16);
+        const float dx = xy.x - pxf, dy = xy.y - pyf;
+        const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
+        if (p2 > 0.0f) continue;
+        const float alpha = fminf(0.99f, b.w * ex2_approx(p2));
         if (alpha < 1.0f / 255.0f) continue;
         const float test_T = T * (1 - alpha);
         if (test_T < 0.0001f) {
           done = true;
           continue;
         }
-        const float4 c = sC[jj];
+        const float4 c = lds128(aC + jj * 16);
         const float wgt = alpha * T;
         C0 += c.x * wgt;
         C1 += c.y * wgt;
@@ -83,6 +150,7 @@ blend_kernel(const TileDesc* __restrict__ tdesc, const Splat* __restrict__ splat
       if (__all_sync(0xffffffffu, done)) break;
     }
   }
+  if (threadIdx.x == 0) atomicAdd((unsigned long long*)&status[3], (unsigned long long)min(base, total));
 
   if (inside) {
     if (bg_dev) {
@@ -110,23 +178,16 @@ blend_kernel(const TileDesc* __restrict__ tdesc, const Splat* __restrict__ splat
 
 }  // namespace
 
-int launch_blend(const gsw_ctx* ctx, int32_t F, const FrameGeom& g, const float bg[3], uint8_t* out_u8,
-                 float* out_color, float* out_invdepth, cudaStream_t s) {
+int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
+                 const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
+                 float* out_invdepth, cudaStream_t s) {
   const int64_t FT = (int64_t)F * g.T;
   if (FT <= 0) return 0;
   auto& w = ctx->ws;
-  blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.tdesc.as<TileDesc>(), w.splats.as<Splat>(), g, bg[0], bg[1], bg[2],
-                                            nullptr, out_u8, out_color, out_invdepth);
-  count_launches(1);
-  GSW_CUDA(cudaGetLastError());
-  return 0;
-}
-
-int launch_blend_bgdev(const gsw_ctx* ctx, const FrameGeom& g, const float* bg_dev, float* out_color,
-                       float* out_invdepth, cudaStream_t s) {
-  auto& w = ctx->ws;
-  blend_kernel<<<(unsigned)g.T, 256, 0, s>>>(w.tdesc.as<TileDesc>(), w.splats.as<Splat>(), g, 0.f, 0.f, 0.f, bg_dev,
-                                             nullptr, out_color, out_invdepth);
+  blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, frame_view, V,
+                                            w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g,
+                                            bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8,
+                                            out_color, out_invdepth, w.status.as<long long>());
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

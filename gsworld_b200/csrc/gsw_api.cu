@@ -50,9 +50,6 @@ void DevBuf::release() {
   bytes = 0;
 }
 
-int launch_blend_bgdev(const gsw_ctx* ctx, const FrameGeom& g, const float* bg_dev, float* out_color,
-                       float* out_invdepth, cudaStream_t s);
-
 namespace {
 
 int ilog2(int v) {
@@ -114,12 +111,11 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   if ((rc = w.bin_count.reserve((size_t)(nbins + 1) * 4)) || (rc = w.bin_off.reserve((size_t)(nbins + 1) * 4)) ||
       (rc = w.bin_cursor.reserve((size_t)(nbins + 1) * 4)))
     return rc;
-  const int64_t scan_n = nbins > FT ? nbins : FT;
+  const int64_t scan_n = nbins;
+  (void)FT;
   if ((rc = w.scan_tmp.reserve(scan_tmp_elems(scan_n) * 4))) return rc;
-  const int64_t mc = (FT > g.T ? FT : g.T) + 1;
-  if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4)) ||
-      (rc = w.tdesc.reserve((size_t)(FT > 0 ? FT : 1) * sizeof(TileDesc))))
-    return rc;
+  const int64_t mc = (int64_t)g.T + 1;
+  if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(64))) return rc;
 
@@ -150,7 +146,6 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   mark(4);
   if ((rc = launch_sort_bins(ctx, nbins, V, N, Nm, g, cap, s))) return rc;
   mark(5);
-  if ((rc = launch_merge(ctx, V, F, g, frame_view, nbins, cap, s))) return rc;
   mark(6);
 
   ctx->last.valid = true;
@@ -162,11 +157,13 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   ctx->last.stat = stat;
   ctx->last.frame_env = frame_env;
   ctx->last.frame_view = frame_view;
+  ctx->last.nbins = nbins;
+  ctx->last.cap = cap;
   return 0;
 }
 
 int finish_launch(gsw_ctx* ctx, cudaStream_t s) {
-  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 3 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
   GSW_CUDA(cudaEventRecord(ctx->done_evt, s));
   ctx->launches++;
   return 0;
@@ -217,7 +214,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.recA, &w.recB, &w.recC, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.tdesc, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos, &c->rig.dev};
   for (DevBuf* b : bufs) b->release();
@@ -359,7 +356,9 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                         d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s);
   if (rc) return rc;
   c->last.single = false;
-  if ((rc = launch_blend(c, d->num_frames, g, d->bg, d->out_rgb_u8, d->out_color, d->out_invdepth, s))) return rc;
+  if ((rc = launch_blend(c, d->num_views, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg, nullptr,
+                         d->out_rgb_u8, d->out_color, d->out_invdepth, s)))
+    return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (d->out_radii)
     if ((rc = launch_radii(c, d->out_radii, s))) return rc;
@@ -374,11 +373,11 @@ int gsw_finish(gsw_ctx* c, int64_t* needed_entries, int64_t stats[4]) {
   }
   Guard gd(c->device);
   GSW_CUDA(cudaEventSynchronize(c->done_evt));
-  const int64_t D = c->h_status[0], M = c->h_status[1], ovf = c->h_status[2];
+  const int64_t D = c->h_status[0], M = 0, ovf = c->h_status[2];
   if (needed_entries) *needed_entries = D + M;
   if (stats) {
     stats[0] = D;
-    stats[1] = M;
+    stats[1] = c->h_status[3];
     stats[2] = c->cap_entries;
     stats[3] = c->launches;
   }
@@ -533,7 +532,8 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   rc = run_pipeline(c, st, P, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv, nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend_bgdev(c, g, bg, out_color, out_invdepth, s))) return rc;
+  if ((rc = launch_blend(c, 1, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
+    return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (out_radii)
     if ((rc = launch_radii(c, out_radii, s))) return rc;

@@ -17,7 +17,7 @@ void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
 void count_launches(int n);  // bookkeeping for gsw_kernel_launches()
 
-constexpr int kNumStages = 8;  // preprocess_static, preprocess_dynamic, scan, scatter, sort, merge, blend, radii
+constexpr int kNumStages = 8;  // preprocess_static, preprocess_dynamic, scan, scatter, sort, (unused), blend, radii
 
 #define GSW_CUDA(expr)                                                                   \
   do {                                                                                   \
@@ -44,12 +44,6 @@ struct DevBuf {
 //   c = {r, g, b, 1/depth}
 struct Splat {
   float4 a, b, c;
-};
-
-// Where a (frame, tile) list lives inside the stream buffers.
-struct TileDesc {
-  uint32_t offset;
-  uint32_t count;
 };
 
 // Inputs of one preprocess "layer" launch.
@@ -89,10 +83,9 @@ struct Workspace {
   // bins: (list, tile, bucket); lists = [V static | F dynamic]
   DevBuf bin_count, bin_off, bin_cursor, scan_tmp;
   // tile entries
-  DevBuf keys;    // u64 [(cap_entries + cap_merged)]
-  DevBuf splats;  // Splat [(cap_entries + cap_merged)]
-  DevBuf tdesc;   // TileDesc [F*T]
-  DevBuf merge_cnt, merge_off;  // u32 [F*T + 1]
+  DevBuf keys;    // u64 [cap_entries]   sorted (depth bits << 32 | index) per bin
+  DevBuf splats;  // Splat [cap_entries] blend records in the same order
+  DevBuf merge_cnt, merge_off;  // u32 [T + 1] scratch of the debug list dump
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -129,8 +122,9 @@ struct gsw_ctx {
     gsw::GaussArrays stat{};
     const int32_t* frame_env = nullptr;
     const int32_t* frame_view = nullptr;
+    int64_t nbins = 0, cap = 0;
   } last;
-  int64_t* h_status = nullptr;  // pinned: [0]=D, [1]=merged, [2]=overflow flag
+  int64_t* h_status = nullptr;  // pinned: [0]=D, [1]=unused, [2]=overflow flag, [3]=entries staged by the blend
   bool profile = false;         // record an event after every stage (gsw_profile_*)
   cudaEvent_t stage_evt[gsw::kNumStages + 1] = {};
   cudaEvent_t done_evt = nullptr;
@@ -158,8 +152,6 @@ int launch_gather_movable(const gsw_ctx* ctx, cudaStream_t s);
 int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s);
 int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, int64_t Nm, const FrameGeom& g,
                      int64_t cap, cudaStream_t s);
-int launch_merge(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, const int32_t* frame_view,
-                 int64_t nbins, int64_t cap, cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                        int64_t cap, cudaStream_t s);
 
@@ -170,8 +162,9 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
                            float* view, float* proj, float* campos, float* tanfov, cudaStream_t s);
 
 // blend.cu
-int launch_blend(const gsw_ctx* ctx, int32_t F, const FrameGeom& g, const float bg[3], uint8_t* out_u8,
-                 float* out_color, float* out_invdepth, cudaStream_t s);
+int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
+                 const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
+                 float* out_invdepth, cudaStream_t s);
 
 size_t scan_tmp_elems(int64_t n);
 

@@ -101,43 +101,18 @@ __device__ __forceinline__ float sh_channel(int deg, float x, float y, float z, 
   return fmaxf(res, 0.0f);
 }
 
-// grid: (ceil(n_items/256), n_lists); list = view (static layer) or frame (dynamic layer)
-template <bool DYN>
-__global__ void __launch_bounds__(256)
-preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
-                  const float* __restrict__ views, const float* __restrict__ projs,
-                  const float* __restrict__ campos, const float* __restrict__ tanfov,
-                  const int32_t* __restrict__ frame_env, const int32_t* __restrict__ frame_view,
-                  const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
-                  float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
-                  uint32_t* __restrict__ bin_count) {
-  __shared__ ViewSmem vs;
-  extern __shared__ float pose_s[];  // DYN: [num_slots][GSW_POSE_STRIDE]
-  const int list = blockIdx.y;
-  int view = list, env = 0;
-  if (DYN) {
-    view = frame_view[list];
-    env = frame_env[list];
-  }
-  if (threadIdx.x < 16) {
-    vs.V[threadIdx.x] = views[view * 16 + threadIdx.x];
-    vs.P[threadIdx.x] = projs[view * 16 + threadIdx.x];
-  } else if (threadIdx.x < 19) {
-    vs.cam[threadIdx.x - 16] = campos[view * 3 + threadIdx.x - 16];
-  } else if (threadIdx.x == 19) {
-    vs.tanx = tanfov[view * 2];
-  } else if (threadIdx.x == 20) {
-    vs.tany = tanfov[view * 2 + 1];
-  }
-  if (DYN) {
-    for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
-      pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
-  }
-  __syncthreads();
+constexpr int kItemsPerThread = 8;                   // each CTA walks 256 * 8 consecutive items of one list
+constexpr int kItemsPerBlock = 256 * kItemsPerThread;
+constexpr size_t kMaxHistBytes = 160 * 1024;         // per-CTA shared histogram budget; above it: global atomics
 
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_items) return;
-  const int64_t item = item_base + (int64_t)list * n_items + i;
+// Per-item body.  `hist` (shared, one counter per (tile, bucket) of this list) may be null, in which case
+// the global bin counters are hit directly.
+template <bool DYN>
+__device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i, int64_t item, int list_global,
+                                                const FrameGeom& g, const ViewSmem& vs, const float* pose_s,
+                                                float4* __restrict__ recA, float4* __restrict__ recB,
+                                                float4* __restrict__ recC, int32_t* __restrict__ rad,
+                                                uint32_t* __restrict__ bin_count, uint32_t* hist) {
   if (!DYN && ga.slot != nullptr && ga.slot[i] >= 0) {  // movable: handled by the dynamic layer
     rad[item] = 0;
     return;
@@ -346,40 +321,141 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
 
   // ---- count this Gaussian into every (tile, depth bucket) bin it touches ----
   const uint32_t bk = depth_bucket(pvz, g);
-  const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)g.T;
-  for (int y = rc.y0; y < rc.y1; ++y)
-    for (int x = rc.x0; x < rc.x1; ++x)
-      atomicAdd(&bin_count[(lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk], 1u);
+  if (hist != nullptr) {
+    for (int y = rc.y0; y < rc.y1; ++y)
+      for (int x = rc.x0; x < rc.x1; ++x) atomicAdd(&hist[(uint32_t)(y * g.gx + x) * (uint32_t)g.NB + bk], 1u);
+  } else {
+    const uint32_t lbase = (uint32_t)list_global * (uint32_t)g.T;
+    for (int y = rc.y0; y < rc.y1; ++y)
+      for (int x = rc.x0; x < rc.x1; ++x)
+        atomicAdd(&bin_count[(lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk], 1u);
+  }
+}
+
+// grid: (ceil(n_items / kItemsPerBlock), n_lists); list = view (static layer) or frame (dynamic layer).
+// Dynamic shared memory: [hist: T*NB u32 (if use_hist)] [pose table of the frame's env (DYN)].
+template <bool DYN>
+__global__ void __launch_bounds__(256)
+preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
+                  const float* __restrict__ views, const float* __restrict__ projs,
+                  const float* __restrict__ campos, const float* __restrict__ tanfov,
+                  const int32_t* __restrict__ frame_env, const int32_t* __restrict__ frame_view,
+                  const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
+                  float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
+                  uint32_t* __restrict__ bin_count, int use_hist) {
+  __shared__ ViewSmem vs;
+  extern __shared__ uint32_t dsm[];
+  const int nbl = g.T * g.NB;
+  uint32_t* hist = use_hist ? dsm : nullptr;
+  float* pose_s = reinterpret_cast<float*>(dsm + (use_hist ? nbl : 0));
+  const int list = blockIdx.y;
+  int view = list, env = 0;
+  if (DYN) {
+    view = frame_view[list];
+    env = frame_env[list];
+  }
+  if (threadIdx.x < 16) {
+    vs.V[threadIdx.x] = views[view * 16 + threadIdx.x];
+    vs.P[threadIdx.x] = projs[view * 16 + threadIdx.x];
+  } else if (threadIdx.x < 19) {
+    vs.cam[threadIdx.x - 16] = campos[view * 3 + threadIdx.x - 16];
+  } else if (threadIdx.x == 19) {
+    vs.tanx = tanfov[view * 2];
+  } else if (threadIdx.x == 20) {
+    vs.tany = tanfov[view * 2 + 1];
+  }
+  if (use_hist)
+    for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
+  if (DYN) {
+    for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
+      pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
+  }
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
+#pragma unroll 1
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    const int64_t i = base + (int64_t)it * 256 + threadIdx.x;
+    if (i < n_items)
+      preprocess_item<DYN>(ga, i, item_base + (int64_t)list * n_items + i, list_base + list, g, vs, pose_s, recA, recB,
+                           recC, rad, bin_count, hist);
+  }
+  if (use_hist) {
+    __syncthreads();
+    const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
+    for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
+      const uint32_t c = hist[k];
+      if (c) atomicAdd(&bin_count[gb + k], c);
+    }
+  }
 }
 
 // Second pass: write (depth bits << 32 | original index) into the bin's slice.  Order inside a bin is
 // arbitrary here; the per-bin sort orders by the full 64-bit key, which reproduces the reference's
 // stable (tile, depth) radix sort exactly (ties on depth fall back to ascending Gaussian index).
+// With use_hist the CTA first counts its own entries per bin in shared memory, reserves one contiguous
+// range per non-empty bin with a single global atomic, then hands out slots with shared-memory atomics.
 template <bool DYN>
 __global__ void __launch_bounds__(256)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                const float4* __restrict__ recA, const float4* __restrict__ recC, const int32_t* __restrict__ rad,
                const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
-               unsigned long long* __restrict__ keys, int64_t cap) {
+               unsigned long long* __restrict__ keys, int64_t cap, int use_hist) {
+  extern __shared__ uint32_t dsm[];
+  const int nbl = g.T * g.NB;
+  uint32_t* hist = dsm;         // counts, then running slot counters
+  uint32_t* hbase = dsm + nbl;  // absolute start of this CTA's range in each bin
   const int list = blockIdx.y;
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_items) return;
-  const int64_t item = item_base + (int64_t)list * n_items + i;
-  const int radius = rad[item];
-  if (radius <= 0) return;
-  const float4 a = recA[item];
-  const float depth = recC[item].w;
-  const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
-  const uint32_t idx = DYN ? (uint32_t)ga.mov_idx[i] : (uint32_t)i;
-  const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | idx;
-  const uint32_t bk = depth_bucket(depth, g);
-  const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)g.T;
-  for (int y = rc.y0; y < rc.y1; ++y)
-    for (int x = rc.x0; x < rc.x1; ++x) {
-      const uint32_t bin = (lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk;
-      const uint32_t pos = bin_off[bin] + atomicAdd(&bin_cursor[bin], 1u);
-      if ((int64_t)pos < cap) keys[pos] = key;
+  const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
+  const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
+  if (use_hist) {
+    for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
+    __syncthreads();
+#pragma unroll 1
+    for (int it = 0; it < kItemsPerThread; ++it) {
+      const int64_t i = base + (int64_t)it * 256 + threadIdx.x;
+      if (i >= n_items) continue;
+      const int64_t item = item_base + (int64_t)list * n_items + i;
+      const int radius = rad[item];
+      if (radius <= 0) continue;
+      const float4 a = recA[item];
+      const float depth = recC[item].w;
+      const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
+      const uint32_t bk = depth_bucket(depth, g);
+      for (int y = rc.y0; y < rc.y1; ++y)
+        for (int x = rc.x0; x < rc.x1; ++x) atomicAdd(&hist[(uint32_t)(y * g.gx + x) * (uint32_t)g.NB + bk], 1u);
     }
+    __syncthreads();
+    for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
+      const uint32_t c = hist[k];
+      if (c) hbase[k] = bin_off[gb + k] + atomicAdd(&bin_cursor[gb + k], c);
+      hist[k] = 0u;
+    }
+    __syncthreads();
+  }
+#pragma unroll 1
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    const int64_t i = base + (int64_t)it * 256 + threadIdx.x;
+    if (i >= n_items) continue;
+    const int64_t item = item_base + (int64_t)list * n_items + i;
+    const int radius = rad[item];
+    if (radius <= 0) continue;
+    const float4 a = recA[item];
+    const float depth = recC[item].w;
+    const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
+    const uint32_t idx = DYN ? (uint32_t)ga.mov_idx[i] : (uint32_t)i;
+    const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | idx;
+    const uint32_t bk = depth_bucket(depth, g);
+    for (int y = rc.y0; y < rc.y1; ++y)
+      for (int x = rc.x0; x < rc.x1; ++x) {
+        const uint32_t b = (uint32_t)(y * g.gx + x) * (uint32_t)g.NB + bk;
+        uint32_t pos;
+        if (use_hist)
+          pos = hbase[b] + atomicAdd(&hist[b], 1u);
+        else
+          pos = bin_off[gb + b] + atomicAdd(&bin_cursor[gb + b], 1u);
+        if ((int64_t)pos < cap) keys[pos] = key;
+      }
+  }
 }
 
 // Per-Gaussian taps of one frame, addressed by original index (parity tests / radii output).
@@ -463,24 +539,38 @@ __global__ void gather_movable_kernel(int64_t Nm, const int32_t* mov_idx, GaussA
 
 }  // namespace
 
+namespace {
+template <typename K>
+int ensure_smem(K kernel, size_t bytes) {
+  if (bytes > 48 * 1024) GSW_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+}  // namespace
+
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
                       const float* pose, int32_t num_slots, cudaStream_t s) {
   if (n_items <= 0 || n_lists <= 0) return 0;
-  dim3 grid((unsigned)((n_items + 255) / 256), (unsigned)n_lists);
+  dim3 grid((unsigned)((n_items + kItemsPerBlock - 1) / kItemsPerBlock), (unsigned)n_lists);
   auto& w = ctx->ws;
+  const size_t hist_b = (size_t)g.T * g.NB * 4;
+  const int use_hist = hist_b <= kMaxHistBytes;
+  size_t sm = use_hist ? hist_b : 0;
+  int rc;
   if (dynamic) {
-    const size_t sm = (size_t)num_slots * GSW_POSE_STRIDE * sizeof(float);
+    sm += (size_t)num_slots * GSW_POSE_STRIDE * sizeof(float);
+    if ((rc = ensure_smem(preprocess_kernel<true>, sm))) return rc;
     preprocess_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
                                                   frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
                                                   w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
-                                                  w.bin_count.as<uint32_t>());
+                                                  w.bin_count.as<uint32_t>(), use_hist);
   } else {
-    preprocess_kernel<false><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
-                                                  frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
-                                                  w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
-                                                  w.bin_count.as<uint32_t>());
+    if ((rc = ensure_smem(preprocess_kernel<false>, sm))) return rc;
+    preprocess_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
+                                                   frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
+                                                   w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
+                                                   w.bin_count.as<uint32_t>(), use_hist);
   }
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
@@ -490,16 +580,25 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, cudaStream_t s) {
   if (n_items <= 0 || n_lists <= 0) return 0;
-  dim3 grid((unsigned)((n_items + 255) / 256), (unsigned)n_lists);
+  dim3 grid((unsigned)((n_items + kItemsPerBlock - 1) / kItemsPerBlock), (unsigned)n_lists);
   auto& w = ctx->ws;
-  if (dynamic)
-    scatter_kernel<true><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
-                                              w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
-                                              w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap);
-  else
-    scatter_kernel<false><<<grid, 256, 0, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
+  const size_t hist_b = (size_t)g.T * g.NB * 8;
+  const int use_hist = hist_b <= kMaxHistBytes;
+  const size_t sm = use_hist ? hist_b : 0;
+  int rc;
+  if (dynamic) {
+    if ((rc = ensure_smem(scatter_kernel<true>, sm))) return rc;
+    scatter_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
                                                w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
-                                               w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap);
+                                               w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
+                                               use_hist);
+  } else {
+    if ((rc = ensure_smem(scatter_kernel<false>, sm))) return rc;
+    scatter_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
+                                                w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
+                                                w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
+                                                use_hist);
+  }
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

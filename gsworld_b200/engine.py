@@ -174,7 +174,7 @@ class Engine:
         need = C.c_int64(0)
         stats = (C.c_int64 * 4)()
         rc = self.lib.gsw_finish(self._h, C.byref(need), C.byref(stats))
-        self.last_stats = dict(D=stats[0], merged=stats[1], cap=stats[2], launches=stats[3])
+        self.last_stats = dict(D=stats[0], staged=stats[1], cap=stats[2], launches=stats[3])
         if rc == _lib.GSW_E_CAPACITY:
             self.reserve_entries(int(need.value * 1.25) + 1024)
             if raise_on_overflow:
@@ -222,7 +222,7 @@ class Engine:
         return out.bool()
 
     # -- measurement hooks --
-    STAGES = ("preprocess_static", "preprocess_dynamic", "scan", "scatter", "sort", "merge", "blend", "radii")
+    STAGES = ("preprocess_static", "preprocess_dynamic", "scan", "scatter", "sort", "reserved", "blend", "radii")
 
     def profile(self, on: bool):
         _lib.check(self.lib.gsw_profile_enable(self._h, int(bool(on))))

@@ -105,7 +105,8 @@ int gsw_render_frames(gsw_ctx* ctx, const gsw_frames_desc* desc, gsw_stream stre
 /* Wait for the last launch on this context and report it.  Returns GSW_E_CAPACITY if the tile-entry
  * workspace overflowed (outputs are then invalid); *needed_entries (may be NULL) receives the entry
  * count that launch needed.  Call gsw_reserve_entries() and launch again.  stats (may be NULL):
- * [0] = D tile entries written, [1] = merged entries written, [2] = entry capacity, [3] = launches. */
+ * [0] = D tile entries written (static per view + dynamic per frame), [1] = entries the blend staged
+ * (<= sum of per-frame list lengths; early termination reads less), [2] = entry capacity, [3] = launches. */
 int gsw_finish(gsw_ctx* ctx, int64_t* needed_entries, int64_t stats[4]);
 int gsw_reserve_entries(gsw_ctx* ctx, int64_t entries);
 /* depth sub-buckets per tile list (power of two, 1..64); 0 = automatic */
@@ -149,7 +150,7 @@ int gsw_compose_cameras(gsw_ctx* ctx, int n, const float* extrinsic_cv, const fl
 long long gsw_kernel_launches(void);
 /* With profiling on, every launch records a CUDA event after each stage on the launch stream;
  * gsw_profile_read waits for the last launch and returns the stage durations in ms, in the order
- * preprocess_static, preprocess_dynamic, scan, scatter, sort, merge, blend, radii (n >= 8). */
+ * preprocess_static, preprocess_dynamic, scan, scatter, sort, (reserved), blend, radii (n >= 8). */
 int gsw_profile_enable(gsw_ctx* ctx, int on);
 int gsw_profile_read(gsw_ctx* ctx, float* stage_ms, int n);
 
