@@ -144,51 +144,334 @@ __device__ __forceinline__ uint32_t pow2ceil(uint32_t n) {
   return n <= 1 ? 1u : 1u << (32 - __clz(n - 1));
 }
 
-// BIG=false: one CTA per bin, bins with n <= kSortSmemKeys sorted in shared memory.
-// BIG=true: a small persistent grid strides over all bins and sorts the (rare) larger ones directly in
-// global memory (L2) with the same network, one CTA per bin.
-template <bool BIG>
+// ---- shared-memory merge sort of one segment (n <= kSortSmemKeys), 8 keys per thread step ----
+typedef unsigned long long u64;
+
+__device__ __forceinline__ void cswap(u64& a, u64& b) {
+  const u64 lo = a < b ? a : b, hi = a < b ? b : a;
+  a = lo;
+  b = hi;
+}
+
+// Batcher odd-even merge sort network for 8 keys (19 comparators)
+__device__ __forceinline__ void sort8(u64 (&k)[8]) {
+  cswap(k[0], k[1]); cswap(k[2], k[3]); cswap(k[4], k[5]); cswap(k[6], k[7]);
+  cswap(k[0], k[2]); cswap(k[1], k[3]); cswap(k[4], k[6]); cswap(k[5], k[7]);
+  cswap(k[1], k[2]); cswap(k[5], k[6]);
+  cswap(k[0], k[4]); cswap(k[1], k[5]); cswap(k[2], k[6]); cswap(k[3], k[7]);
+  cswap(k[2], k[4]); cswap(k[3], k[5]);
+  cswap(k[1], k[2]); cswap(k[3], k[4]); cswap(k[5], k[6]);
+}
+
+// Sorts buf0[0..n) (padded to n8 = roundup(n,8) with +inf); returns the buffer holding the result.
+__device__ __forceinline__ u64* smem_merge_sort(u64* buf0, u64* buf1, uint32_t n) {
+  const uint32_t n8 = (n + 7u) & ~7u;
+  const uint32_t chunks = n8 >> 3;
+  for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) {
+    u64 k[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) k[i] = (8 * c + i < n) ? buf0[8 * c + i] : ~0ull;
+    sort8(k);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) buf0[8 * c + i] = k[i];
+  }
+  __syncthreads();
+  u64* src = buf0;
+  u64* dst = buf1;
+  for (uint32_t L = 8; L < n8; L <<= 1) {
+    for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) {
+      const uint32_t o = 8 * c;
+      const uint32_t pbase = (o / (2 * L)) * (2 * L);
+      const uint32_t lenA = min(L, n8 - pbase);
+      const uint32_t lenB = (n8 - pbase > L) ? min(L, n8 - pbase - L) : 0u;
+      const u64* A = src + pbase;
+      const u64* B = A + L;
+      const uint32_t d = o - pbase;
+      uint32_t lo = d > lenB ? d - lenB : 0u, hi = min(d, lenA);
+      while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (A[mid] < B[d - 1 - mid]) lo = mid + 1; else hi = mid;
+      }
+      uint32_t a = lo, b = d - lo;
+      u64 ka = a < lenA ? A[a] : ~0ull, kb = b < lenB ? B[b] : ~0ull;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const bool ta = (b >= lenB) || (a < lenA && ka <= kb);
+        dst[o + i] = ta ? ka : kb;
+        if (ta) {
+          ++a;
+          ka = a < lenA ? A[a] : ~0ull;
+        } else {
+          ++b;
+          kb = b < lenB ? B[b] : ~0ull;
+        }
+      }
+    }
+    __syncthreads();
+    u64* t = src;
+    src = dst;
+    dst = t;
+  }
+  return src;
+}
+
+struct Segment {  // a slice of the key array that is sorted independently (a whole bin or a depth sub-range of one)
+  uint32_t start, count, bin, pad;
+};
+
+// gather the sorted records into the blend stream.  The conic is pre-scaled so the blend evaluates
+// alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A, B' = -log2(e) B, C' = -0.5 log2(e) C.
+// Four records per thread are in flight at once: the reads are random 16-byte gathers from L2/HBM.
+__device__ __forceinline__ void gather_splats(const u64* sorted, bool to_global_keys, u64* gkeys, uint32_t start,
+                                              uint32_t n, int64_t bin, int32_t V, int64_t N, int64_t Nm,
+                                              int32_t bins_per_list, const int32_t* __restrict__ mov_pos,
+                                              const float4* __restrict__ recA, const float4* __restrict__ recB,
+                                              const float4* __restrict__ recC, Splat* __restrict__ splats) {
+  const int64_t list = bin / bins_per_list;
+  const bool dyn = list >= V;
+  const int64_t item_base = dyn ? (int64_t)V * N + (list - V) * Nm : list * N;
+  constexpr float kLog2e = 1.4426950408889634f;
+  constexpr int U = 4;
+  for (uint32_t t0 = threadIdx.x; t0 < n; t0 += blockDim.x * U) {
+    u64 key[U];
+    int64_t item[U];
+    float4 a[U], b[U], c[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t t = t0 + u * blockDim.x;
+      key[u] = t < n ? sorted[t] : 0ull;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t t = t0 + u * blockDim.x;
+      const uint32_t idx = (uint32_t)(key[u] & 0xffffffffull);
+      item[u] = item_base + ((dyn && t < n) ? (int64_t)mov_pos[idx] : (int64_t)idx);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t t = t0 + u * blockDim.x;
+      if (t < n) {
+        a[u] = recA[item[u]];
+        b[u] = recB[item[u]];
+        c[u] = recC[item[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t t = t0 + u * blockDim.x;
+      if (t < n) {
+        if (to_global_keys) gkeys[start + t] = key[u];
+        Splat sp;
+        sp.a = a[u];
+        sp.b = make_float4(-0.5f * kLog2e * b[u].x, -kLog2e * b[u].y, -0.5f * kLog2e * b[u].z, b[u].w);
+        sp.c = make_float4(c[u].x, c[u].y, c[u].z, 1 / c[u].w);
+        splats[start + t] = sp;
+      }
+    }
+  }
+}
+
+// Work classification: every non-empty bin goes to one of three queues by size, so that the sort CTAs
+// are sized for their segments and no CTA is launched for an empty bin.
+//   queue 0 (small):  n <= kSmallKeys          -> 128-thread CTAs, 16 KB shared memory
+//   queue 1 (medium): n <= kSortSmemKeys       -> 256-thread CTAs, 64 KB
+//   queue 2 (huge):   larger                   -> refine_big_bins_kernel splits by depth into medium segments
+constexpr int kSmallKeys = 1024;
+struct Queues {
+  Segment* q[3];
+  uint32_t* count;  // [3]
+  uint32_t cap[3];
+};
+
+__global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int64_t cap, Queues Q,
+                                     long long* __restrict__ status) {
+  const int64_t bin = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (bin >= nbins) return;
+  const uint32_t start = bin_off[bin], end = bin_off[bin + 1];
+  if (end <= start || (int64_t)end > cap) return;
+  const uint32_t n = end - start;
+  const int k = n <= (uint32_t)kSmallKeys ? 0 : (n <= (uint32_t)kSortSmemKeys ? 1 : 2);
+  const uint32_t slot = atomicAdd(&Q.count[k], 1u);
+  if (slot < Q.cap[k]) {
+    Segment sg;
+    sg.start = start;
+    sg.count = n;
+    sg.bin = (uint32_t)bin;
+    sg.pad = 0;
+    Q.q[k][slot] = sg;
+  } else {
+    status[2] = 3;
+  }
+}
+
+// Persistent CTAs pull segments of one size class and sort them in shared memory.
+template <int CAP, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+sort_segments_kernel(const Segment* __restrict__ queue, const uint32_t* __restrict__ queue_count, uint32_t queue_cap,
+                     int32_t V, int64_t N, int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ mov_pos,
+                     u64* __restrict__ keys, const float4* __restrict__ recA, const float4* __restrict__ recB,
+                     const float4* __restrict__ recC, Splat* __restrict__ splats) {
+  extern __shared__ u64 sbuf[];
+  u64* buf0 = sbuf;
+  u64* buf1 = sbuf + CAP;
+  const uint32_t nseg = min(*queue_count, queue_cap);
+  for (uint32_t sidx = blockIdx.x; sidx < nseg; sidx += gridDim.x) {
+    const Segment sg = queue[sidx];
+    const uint32_t start = sg.start, n = sg.count;
+    for (uint32_t t = threadIdx.x; t < n; t += THREADS) buf0[t] = keys[start + t];
+    __syncthreads();
+    const u64* sorted = smem_merge_sort(buf0, buf1, n);
+    gather_splats(sorted, true, keys, start, n, sg.bin, V, N, Nm, bins_per_list, mov_pos, recA, recB, recC, splats);
+    __syncthreads();  // buffers are reused by the next segment of this CTA
+  }
+}
+
+// Bins larger than kSortSmemKeys: partition the bin by depth into sub-segments that fit shared memory.
+// One CTA per huge bin.  256 buckets linear in the depth bits between the bin's min and max; keys are
+// moved bucket by bucket through scratch space (the bin's own, not yet written, splat slice), then
+// consecutive buckets are grouped greedily into segments <= kSortSmemKeys and appended to the medium
+// queue.  A single bucket that is still too large (many equal depths) is sorted in place with the
+// global-memory bitonic network.
+constexpr int kRefineBuckets = 256;
 __global__ void __launch_bounds__(512)
-sort_bins_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t V, int64_t N, int64_t Nm,
-                 int32_t bins_per_list, const int32_t* __restrict__ mov_pos, unsigned long long* __restrict__ keys,
-                 const float4* __restrict__ recA, const float4* __restrict__ recB, const float4* __restrict__ recC,
-                 Splat* __restrict__ splats, int64_t cap) {
-  extern __shared__ unsigned long long skeys[];
-  for (int64_t bin = blockIdx.x; bin < nbins; bin += gridDim.x) {
-    const uint32_t start = bin_off[bin];
-    const uint32_t end = bin_off[bin + 1];
-    if (end <= start || (int64_t)end > cap) continue;
-    const uint32_t n = end - start;
-    if (BIG != (n > (uint32_t)kSortSmemKeys)) continue;
-    const uint32_t n2 = pow2ceil(n);
-    unsigned long long* g = keys + start;
-    if (!BIG) {
-      for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) skeys[t] = g[t];
-      __syncthreads();
-      if (n > 1) bitonic_sort(skeys, n, n2);
-    } else {
-      __syncthreads();
-      bitonic_sort(g, n, n2);
-    }
-    // gather the sorted records into the blend stream.  The conic is pre-scaled so the blend evaluates
-    // alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A, B' = -log2(e) B, C' = -0.5 log2(e) C.
-    const int64_t list = bin / bins_per_list;
-    const bool dyn = list >= V;
-    const int64_t item_base = dyn ? (int64_t)V * N + (list - V) * Nm : list * N;
-    constexpr float kLog2e = 1.4426950408889634f;
+refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ splats, int32_t V, int64_t N, int64_t Nm,
+                       int32_t bins_per_list, const int32_t* __restrict__ mov_pos, const float4* __restrict__ recA,
+                       const float4* __restrict__ recB, const float4* __restrict__ recC,
+                       long long* __restrict__ status) {
+  __shared__ uint32_t hist[kRefineBuckets + 1];
+  __shared__ uint32_t cursor[kRefineBuckets];
+  __shared__ uint32_t red_min[16], red_max[16];
+  __shared__ uint32_t s_min, s_max;
+  __shared__ uint32_t big_lo[8], big_n[8];
+  __shared__ uint32_t n_big;
+  const uint32_t nh = min(Q.count[2], Q.cap[2]);
+  for (uint32_t h = blockIdx.x; h < nh; h += gridDim.x) {
+    const Segment hs = Q.q[2][h];
+    const uint32_t start = hs.start, n = hs.count;
+    const int64_t bin = hs.bin;
+    u64* K = keys + start;
+    u64* S = reinterpret_cast<u64*>(splats + start);  // scratch: 48 B per entry available, 8 used
+    // 1. depth range
+    uint32_t mn = 0xffffffffu, mx = 0u;
+#pragma unroll 4
     for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) {
-      const unsigned long long key = BIG ? g[t] : skeys[t];
-      if (!BIG) g[t] = key;
-      const uint32_t idx = (uint32_t)(key & 0xffffffffull);
-      const int64_t item = item_base + (dyn ? (int64_t)mov_pos[idx] : (int64_t)idx);
-      const float4 a = recA[item], b = recB[item], c = recC[item];
-      Splat sp;
-      sp.a = a;
-      sp.b = make_float4(-0.5f * kLog2e * b.x, -kLog2e * b.y, -0.5f * kLog2e * b.z, b.w);
-      sp.c = make_float4(c.x, c.y, c.z, 1 / c.w);
-      splats[start + t] = sp;
+      const uint32_t d = (uint32_t)(K[t] >> 32);
+      mn = min(mn, d);
+      mx = max(mx, d);
     }
-    __syncthreads();  // skeys is reused by the next bin of this CTA (BIG grid only loops)
+    for (int o = 16; o > 0; o >>= 1) {
+      mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      red_min[threadIdx.x >> 5] = mn;
+      red_max[threadIdx.x >> 5] = mx;
+    }
+    for (int k = threadIdx.x; k <= kRefineBuckets; k += blockDim.x) hist[k] = 0u;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t a = 0xffffffffu, b = 0u;
+      for (int k = 0; k < (int)(blockDim.x >> 5); ++k) {
+        a = min(a, red_min[k]);
+        b = max(b, red_max[k]);
+      }
+      s_min = a;
+      s_max = b;
+    }
+    __syncthreads();
+    const uint32_t dmin = s_min;
+    const u64 range = (u64)(s_max - dmin) + 1ull;
+    auto bucket_of = [&](u64 key) -> uint32_t {
+      return (uint32_t)((((key >> 32) - dmin) * (u64)kRefineBuckets) / range);
+    };
+    // 2. histogram
+#pragma unroll 4
+    for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) atomicAdd(&hist[bucket_of(K[t])], 1u);
+    __syncthreads();
+    // 3. exclusive scan of 256 counters by warp 0 (8 per lane)
+    if (threadIdx.x < 32) {
+      uint32_t v[8], sum = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        v[k] = hist[threadIdx.x * 8 + k];
+        sum += v[k];
+      }
+      uint32_t incl = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((int)threadIdx.x >= d) incl += t;
+      }
+      uint32_t run = incl - sum;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        hist[threadIdx.x * 8 + k] = run;
+        cursor[threadIdx.x * 8 + k] = run;
+        run += v[k];
+      }
+      if (threadIdx.x == 31) hist[kRefineBuckets] = run;
+    }
+    __syncthreads();
+    // 4. scatter to scratch, copy back
+#pragma unroll 4
+    for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) {
+      const u64 key = K[t];
+      S[atomicAdd(&cursor[bucket_of(key)], 1u)] = key;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (uint32_t t = threadIdx.x; t < n; t += blockDim.x) K[t] = S[t];
+    __syncthreads();
+    // 5. group buckets into segments (thread 0), oversize buckets sorted here
+    if (threadIdx.x == 0) {
+      n_big = 0;
+      uint32_t seg_lo = 0;
+      auto emit = [&](uint32_t lo, uint32_t hi) {
+        if (hi <= lo) return;
+        if (hi - lo > (uint32_t)kSortSmemKeys) {  // one bucket, still too large
+          if (n_big < 8) {
+            big_lo[n_big] = lo;
+            big_n[n_big] = hi - lo;
+            ++n_big;
+          } else {
+            status[2] = 2;
+          }
+          return;
+        }
+        const uint32_t q = atomicAdd(&Q.count[1], 1u);
+        if (q < Q.cap[1]) {
+          Segment sg;
+          sg.start = start + lo;
+          sg.count = hi - lo;
+          sg.bin = (uint32_t)bin;
+          sg.pad = 0;
+          Q.q[1][q] = sg;
+        } else {
+          status[2] = 3;
+        }
+      };
+      for (int k = 0; k < kRefineBuckets; ++k) {
+        const uint32_t b_hi = hist[k + 1];
+        if (b_hi - seg_lo > (uint32_t)kSortSmemKeys) {
+          emit(seg_lo, hist[k]);  // close the segment before bucket k
+          seg_lo = hist[k];
+          if (b_hi - seg_lo > (uint32_t)kSortSmemKeys) {  // bucket k alone is oversize
+            emit(seg_lo, b_hi);
+            seg_lo = b_hi;
+          }
+        }
+      }
+      emit(seg_lo, n);
+    }
+    __syncthreads();
+    for (uint32_t k = 0; k < n_big; ++k) {
+      const uint32_t lo = big_lo[k], m = big_n[k];
+      bitonic_sort(K + lo, m, pow2ceil(m));
+      gather_splats(K + lo, false, keys, start + lo, m, bin, V, N, Nm, bins_per_list, mov_pos, recA, recB, recC,
+                    splats);
+      __syncthreads();
+    }
+    __syncthreads();
   }
 }
 
@@ -265,20 +548,37 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, in
   if (nbins <= 0) return 0;
   auto& w = ctx->ws;
   static bool attr_set = false;
-  const size_t smem = (size_t)kSortSmemKeys * sizeof(unsigned long long);
+  constexpr size_t smem_m = (size_t)2 * kSortSmemKeys * sizeof(unsigned long long);
+  constexpr size_t smem_s = (size_t)2 * kSmallKeys * sizeof(unsigned long long);
   if (!attr_set) {
-    GSW_CUDA(cudaFuncSetAttribute(sort_bins_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    GSW_CUDA(cudaFuncSetAttribute(sort_segments_kernel<kSortSmemKeys, 256>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_m));
     attr_set = true;
   }
   const int32_t bpl = g.T * g.NB;
-  sort_bins_kernel<false><<<(unsigned)nbins, 512, smem, s>>>(
-      w.bin_off.as<uint32_t>(), nbins, V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
-      w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>(), cap);
-  const unsigned big_grid = (unsigned)(nbins < 296 ? nbins : 296);
-  sort_bins_kernel<true><<<big_grid, 512, 0, s>>>(
-      w.bin_off.as<uint32_t>(), nbins, V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
-      w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>(), cap);
-  count_launches(2);
+  // queue storage: [small: nbins][huge: nbins][medium: the rest]
+  Queues Q;
+  Segment* base = w.seg_queue.as<Segment>();
+  const uint32_t total = (uint32_t)(w.seg_queue.bytes / sizeof(Segment));
+  Q.q[0] = base;
+  Q.cap[0] = (uint32_t)nbins;
+  Q.q[2] = base + nbins;
+  Q.cap[2] = (uint32_t)nbins;
+  Q.q[1] = base + 2 * nbins;
+  Q.cap[1] = total - 2 * (uint32_t)nbins;
+  Q.count = w.status.as<uint32_t>() + 12;  // three words of the status block (zeroed every launch)
+  classify_bins_kernel<<<(unsigned)((nbins + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, cap, Q,
+                                                                      w.status.as<long long>());
+  refine_big_bins_kernel<<<296, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), V, N, Nm, bpl,
+                                             ctx->mov_pos.as<int32_t>(), w.recA.as<float4>(), w.recB.as<float4>(),
+                                             w.recC.as<float4>(), w.status.as<long long>());
+  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 3, 256, smem_m, s>>>(
+      Q.q[1], Q.count + 1, Q.cap[1], V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
+      w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>());
+  sort_segments_kernel<kSmallKeys, 128><<<148 * 8, 128, smem_s, s>>>(
+      Q.q[0], Q.count, Q.cap[0], V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
+      w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>());
+  count_launches(4);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

@@ -118,6 +118,8 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(64))) return rc;
+  // every queued sub-segment but the last of a bin pairs with a neighbour to more than kSortSmemKeys entries
+  if ((rc = w.seg_queue.reserve((size_t)(2 * (cap / kSortSmemKeys) + 3 * nbins + 16) * 16))) return rc;
 
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
@@ -214,7 +216,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.recA, &w.recB, &w.recC, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos, &c->rig.dev};
   for (DevBuf* b : bufs) b->release();

@@ -11,7 +11,7 @@
 namespace gsw {
 
 constexpr int kTile = 16;           // 16x16 pixel tiles, as the reference rasterizer (BLOCK_X/BLOCK_Y)
-constexpr int kSortSmemKeys = 8192; // largest bin sorted in shared memory (64 KB of u64 keys)
+constexpr int kSortSmemKeys = 4096; // largest segment sorted in shared memory (2 x 32 KB ping-pong of u64 keys)
 
 void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
@@ -86,6 +86,7 @@ struct Workspace {
   DevBuf keys;    // u64 [cap_entries]   sorted (depth bits << 32 | index) per bin
   DevBuf splats;  // Splat [cap_entries] blend records in the same order
   DevBuf merge_cnt, merge_off;  // u32 [T + 1] scratch of the debug list dump
+  DevBuf seg_queue;             // Segment[]: depth sub-ranges of bins too large for one shared-memory sort
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
