@@ -163,111 +163,111 @@ __device__ __forceinline__ void sort8(u64 (&k)[8]) {
   cswap(k[1], k[2]); cswap(k[3], k[4]); cswap(k[5], k[6]);
 }
 
-// Sorts buf0[0..n) (padded to n8 = roundup(n,8) with +inf); returns the buffer holding the result.
-__device__ __forceinline__ u64* smem_merge_sort(u64* buf0, u64* buf1, uint32_t n) {
+// Sorts buf[0..n) in place (padded to n8 = roundup(n,8) with +inf).  Each merge round computes a thread's
+// output chunks into registers, then all threads write back after a barrier, so one buffer suffices.
+// CPT = max chunks (of 8 keys) per thread = capacity / (8 * THREADS).
+template <int THREADS, int CPT>
+__device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
   const uint32_t n8 = (n + 7u) & ~7u;
   const uint32_t chunks = n8 >> 3;
-  for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) {
-    u64 k[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) k[i] = (8 * c + i < n) ? buf0[8 * c + i] : ~0ull;
-    sort8(k);
+  for (int q = 0; q < CPT; ++q) {
+    const uint32_t c = threadIdx.x + q * THREADS;
+    if (c < chunks) {
+      u64 k[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) buf0[8 * c + i] = k[i];
+      for (int i = 0; i < 8; ++i) k[i] = (8 * c + i < n) ? buf[8 * c + i] : ~0ull;
+      sort8(k);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) buf[8 * c + i] = k[i];
+    }
   }
   __syncthreads();
-  u64* src = buf0;
-  u64* dst = buf1;
   for (uint32_t L = 8; L < n8; L <<= 1) {
-    for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) {
-      const uint32_t o = 8 * c;
-      const uint32_t pbase = (o / (2 * L)) * (2 * L);
-      const uint32_t lenA = min(L, n8 - pbase);
-      const uint32_t lenB = (n8 - pbase > L) ? min(L, n8 - pbase - L) : 0u;
-      const u64* A = src + pbase;
-      const u64* B = A + L;
-      const uint32_t d = o - pbase;
-      uint32_t lo = d > lenB ? d - lenB : 0u, hi = min(d, lenA);
-      while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (A[mid] < B[d - 1 - mid]) lo = mid + 1; else hi = mid;
-      }
-      uint32_t a = lo, b = d - lo;
-      u64 ka = a < lenA ? A[a] : ~0ull, kb = b < lenB ? B[b] : ~0ull;
+    u64 out[CPT][8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const bool ta = (b >= lenB) || (a < lenA && ka <= kb);
-        dst[o + i] = ta ? ka : kb;
-        if (ta) {
-          ++a;
-          ka = a < lenA ? A[a] : ~0ull;
-        } else {
-          ++b;
-          kb = b < lenB ? B[b] : ~0ull;
+    for (int q = 0; q < CPT; ++q) {
+      const uint32_t c = threadIdx.x + q * THREADS;
+      if (c < chunks) {
+        const uint32_t o = 8 * c;
+        const uint32_t pbase = (o / (2 * L)) * (2 * L);
+        const uint32_t lenA = min(L, n8 - pbase);
+        const uint32_t lenB = (n8 - pbase > L) ? min(L, n8 - pbase - L) : 0u;
+        const u64* A = buf + pbase;
+        const u64* B = A + L;
+        const uint32_t d = o - pbase;
+        uint32_t lo = d > lenB ? d - lenB : 0u, hi = min(d, lenA);
+        while (lo < hi) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (A[mid] < B[d - 1 - mid]) lo = mid + 1; else hi = mid;
+        }
+        uint32_t a = lo, b = d - lo;
+        u64 ka = a < lenA ? A[a] : ~0ull, kb = b < lenB ? B[b] : ~0ull;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const bool ta = (b >= lenB) || (a < lenA && ka <= kb);
+          out[q][i] = ta ? ka : kb;
+          if (ta) {
+            ++a;
+            ka = a < lenA ? A[a] : ~0ull;
+          } else {
+            ++b;
+            kb = b < lenB ? B[b] : ~0ull;
+          }
         }
       }
     }
     __syncthreads();
-    u64* t = src;
-    src = dst;
-    dst = t;
+#pragma unroll
+    for (int q = 0; q < CPT; ++q) {
+      const uint32_t c = threadIdx.x + q * THREADS;
+      if (c < chunks) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) buf[8 * c + i] = out[q][i];
+      }
+    }
+    __syncthreads();
   }
-  return src;
 }
 
 struct Segment {  // a slice of the key array that is sorted independently (a whole bin or a depth sub-range of one)
   uint32_t start, count, bin, pad;
 };
 
-// gather the sorted records into the blend stream.  The conic is pre-scaled so the blend evaluates
-// alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A, B' = -log2(e) B, C' = -0.5 log2(e) C.
-// Four records per thread are in flight at once: the reads are random 16-byte gathers from L2/HBM.
-__device__ __forceinline__ void gather_splats(const u64* sorted, bool to_global_keys, u64* gkeys, uint32_t start,
-                                              uint32_t n, int64_t bin, int32_t V, int64_t N, int64_t Nm,
-                                              int32_t bins_per_list, const int32_t* __restrict__ mov_pos,
-                                              const float4* __restrict__ recA, const float4* __restrict__ recB,
-                                              const float4* __restrict__ recC, Splat* __restrict__ splats) {
-  const int64_t list = bin / bins_per_list;
-  const bool dyn = list >= V;
-  const int64_t item_base = dyn ? (int64_t)V * N + (list - V) * Nm : list * N;
+// Record gather for one entry: key -> per-item record (64 B slot) -> blend record.  The conic is pre-scaled
+// so the blend evaluates alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A,
+// B' = -log2(e) B, C' = -0.5 log2(e) C.
+__device__ __forceinline__ Splat make_splat(const float4* __restrict__ rec, int64_t item) {
   constexpr float kLog2e = 1.4426950408889634f;
-  constexpr int U = 4;
-  for (uint32_t t0 = threadIdx.x; t0 < n; t0 += blockDim.x * U) {
-    u64 key[U];
-    int64_t item[U];
-    float4 a[U], b[U], c[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t t = t0 + u * blockDim.x;
-      key[u] = t < n ? sorted[t] : 0ull;
+  const float4 a = rec[4 * item], b = rec[4 * item + 1], c = rec[4 * item + 2];
+  Splat sp;
+  sp.a = a;
+  sp.b = make_float4(-0.5f * kLog2e * b.x, -kLog2e * b.y, -0.5f * kLog2e * b.z, b.w);
+  sp.c = make_float4(c.x, c.y, c.z, 1 / c.w);
+  return sp;
+}
+
+// One thread per tile entry, over the whole sorted key array: fully parallel random gather (two aligned
+// 32 B sectors per entry), coalesced key reads and splat writes.  The list an entry belongs to is found
+// by binary search over the V+F list boundaries (bin_off at multiples of bins_per_list).
+__global__ void __launch_bounds__(256)
+gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t N,
+                     int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ mov_pos,
+                     const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
+                     int64_t cap) {
+  const uint32_t D = bin_off[nbins];
+  if ((int64_t)D > cap) return;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < D; p += gridDim.x * blockDim.x) {
+    int lo = 0, hi = n_lists - 1;  // last list whose start is <= p
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (bin_off[(int64_t)mid * bins_per_list] <= p) lo = mid; else hi = mid - 1;
     }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t t = t0 + u * blockDim.x;
-      const uint32_t idx = (uint32_t)(key[u] & 0xffffffffull);
-      item[u] = item_base + ((dyn && t < n) ? (int64_t)mov_pos[idx] : (int64_t)idx);
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t t = t0 + u * blockDim.x;
-      if (t < n) {
-        a[u] = recA[item[u]];
-        b[u] = recB[item[u]];
-        c[u] = recC[item[u]];
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t t = t0 + u * blockDim.x;
-      if (t < n) {
-        if (to_global_keys) gkeys[start + t] = key[u];
-        Splat sp;
-        sp.a = a[u];
-        sp.b = make_float4(-0.5f * kLog2e * b[u].x, -kLog2e * b[u].y, -0.5f * kLog2e * b[u].z, b[u].w);
-        sp.c = make_float4(c[u].x, c[u].y, c[u].z, 1 / c[u].w);
-        splats[start + t] = sp;
-      }
-    }
+    const u64 key = keys[p];
+    const uint32_t idx = (uint32_t)(key & 0xffffffffull);
+    const bool dyn = lo >= V;
+    const int64_t item = dyn ? (int64_t)V * N + (int64_t)(lo - V) * Nm + mov_pos[idx] : (int64_t)lo * N + idx;
+    splats[p] = make_splat(rec, item);
   }
 }
 
@@ -304,25 +304,21 @@ __global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64
   }
 }
 
-// Persistent CTAs pull segments of one size class and sort them in shared memory.
+// Persistent CTAs pull segments of one size class and sort their keys in shared memory.
 template <int CAP, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 sort_segments_kernel(const Segment* __restrict__ queue, const uint32_t* __restrict__ queue_count, uint32_t queue_cap,
-                     int32_t V, int64_t N, int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ mov_pos,
-                     u64* __restrict__ keys, const float4* __restrict__ recA, const float4* __restrict__ recB,
-                     const float4* __restrict__ recC, Splat* __restrict__ splats) {
+                     u64* __restrict__ keys) {
   extern __shared__ u64 sbuf[];
-  u64* buf0 = sbuf;
-  u64* buf1 = sbuf + CAP;
   const uint32_t nseg = min(*queue_count, queue_cap);
   for (uint32_t sidx = blockIdx.x; sidx < nseg; sidx += gridDim.x) {
     const Segment sg = queue[sidx];
     const uint32_t start = sg.start, n = sg.count;
-    for (uint32_t t = threadIdx.x; t < n; t += THREADS) buf0[t] = keys[start + t];
+    for (uint32_t t = threadIdx.x; t < n; t += THREADS) sbuf[t] = keys[start + t];
     __syncthreads();
-    const u64* sorted = smem_merge_sort(buf0, buf1, n);
-    gather_splats(sorted, true, keys, start, n, sg.bin, V, N, Nm, bins_per_list, mov_pos, recA, recB, recC, splats);
-    __syncthreads();  // buffers are reused by the next segment of this CTA
+    smem_merge_sort<THREADS, CAP / (8 * THREADS)>(sbuf, n);
+    for (uint32_t t = threadIdx.x; t < n; t += THREADS) keys[start + t] = sbuf[t];
+    __syncthreads();  // buffer is reused by the next segment of this CTA
   }
 }
 
@@ -334,9 +330,7 @@ sort_segments_kernel(const Segment* __restrict__ queue, const uint32_t* __restri
 // global-memory bitonic network.
 constexpr int kRefineBuckets = 256;
 __global__ void __launch_bounds__(512)
-refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ splats, int32_t V, int64_t N, int64_t Nm,
-                       int32_t bins_per_list, const int32_t* __restrict__ mov_pos, const float4* __restrict__ recA,
-                       const float4* __restrict__ recB, const float4* __restrict__ recC,
+refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ splats,
                        long long* __restrict__ status) {
   __shared__ uint32_t hist[kRefineBuckets + 1];
   __shared__ uint32_t cursor[kRefineBuckets];
@@ -348,7 +342,7 @@ refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ spl
   for (uint32_t h = blockIdx.x; h < nh; h += gridDim.x) {
     const Segment hs = Q.q[2][h];
     const uint32_t start = hs.start, n = hs.count;
-    const int64_t bin = hs.bin;
+    const uint32_t bin = hs.bin;
     u64* K = keys + start;
     u64* S = reinterpret_cast<u64*>(splats + start);  // scratch: 48 B per entry available, 8 used
     // 1. depth range
@@ -443,7 +437,7 @@ refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ spl
           Segment sg;
           sg.start = start + lo;
           sg.count = hi - lo;
-          sg.bin = (uint32_t)bin;
+          sg.bin = bin;
           sg.pad = 0;
           Q.q[1][q] = sg;
         } else {
@@ -467,8 +461,6 @@ refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ spl
     for (uint32_t k = 0; k < n_big; ++k) {
       const uint32_t lo = big_lo[k], m = big_n[k];
       bitonic_sort(K + lo, m, pow2ceil(m));
-      gather_splats(K + lo, false, keys, start + lo, m, bin, V, N, Nm, bins_per_list, mov_pos, recA, recB, recC,
-                    splats);
       __syncthreads();
     }
     __syncthreads();
@@ -547,15 +539,10 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, in
                      int64_t cap, cudaStream_t s) {
   if (nbins <= 0) return 0;
   auto& w = ctx->ws;
-  static bool attr_set = false;
-  constexpr size_t smem_m = (size_t)2 * kSortSmemKeys * sizeof(unsigned long long);
-  constexpr size_t smem_s = (size_t)2 * kSmallKeys * sizeof(unsigned long long);
-  if (!attr_set) {
-    GSW_CUDA(cudaFuncSetAttribute(sort_segments_kernel<kSortSmemKeys, 256>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_m));
-    attr_set = true;
-  }
+  constexpr size_t smem_m = (size_t)kSortSmemKeys * sizeof(unsigned long long);  // 32 KB
+  constexpr size_t smem_s = (size_t)kSmallKeys * sizeof(unsigned long long);     // 8 KB
   const int32_t bpl = g.T * g.NB;
+  const int32_t n_lists = (int32_t)(nbins / bpl);
   // queue storage: [small: nbins][huge: nbins][medium: the rest]
   Queues Q;
   Segment* base = w.seg_queue.as<Segment>();
@@ -569,16 +556,16 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, in
   Q.count = w.status.as<uint32_t>() + 12;  // three words of the status block (zeroed every launch)
   classify_bins_kernel<<<(unsigned)((nbins + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, cap, Q,
                                                                       w.status.as<long long>());
-  refine_big_bins_kernel<<<296, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), V, N, Nm, bpl,
-                                             ctx->mov_pos.as<int32_t>(), w.recA.as<float4>(), w.recB.as<float4>(),
-                                             w.recC.as<float4>(), w.status.as<long long>());
-  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 3, 256, smem_m, s>>>(
-      Q.q[1], Q.count + 1, Q.cap[1], V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
-      w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>());
-  sort_segments_kernel<kSmallKeys, 128><<<148 * 8, 128, smem_s, s>>>(
-      Q.q[0], Q.count, Q.cap[0], V, N, Nm, bpl, ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
-      w.recA.as<float4>(), w.recB.as<float4>(), w.recC.as<float4>(), w.splats.as<Splat>());
-  count_launches(4);
+  refine_big_bins_kernel<<<148 * 2, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
+                                                 w.status.as<long long>());
+  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 6, 256, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
+                                                                        w.keys.as<unsigned long long>());
+  sort_segments_kernel<kSmallKeys, 128><<<148 * 12, 128, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
+                                                                      w.keys.as<unsigned long long>());
+  gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, N, Nm, bpl,
+                                                ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
+                                                w.rec.as<float4>(), w.splats.as<Splat>(), cap);
+  count_launches(5);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

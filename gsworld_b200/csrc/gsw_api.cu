@@ -105,9 +105,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   const int64_t cap = ctx->cap_entries;
   int rc;
   const size_t it = (size_t)(items > 0 ? items : 1);
-  if ((rc = w.recA.reserve(it * 16)) || (rc = w.recB.reserve(it * 16)) || (rc = w.recC.reserve(it * 16)) ||
-      (rc = w.rad.reserve(it * 4)))
-    return rc;
+  if ((rc = w.rec.reserve(it * 64)) || (rc = w.rad.reserve(it * 4))) return rc;
   if ((rc = w.bin_count.reserve((size_t)(nbins + 1) * 4)) || (rc = w.bin_off.reserve((size_t)(nbins + 1) * 4)) ||
       (rc = w.bin_cursor.reserve((size_t)(nbins + 1) * 4)))
     return rc;
@@ -215,7 +213,7 @@ int gsw_destroy(gsw_ctx* c) {
   Guard gd(c->device);
   cudaDeviceSynchronize();
   auto& w = c->ws;
-  DevBuf* bufs[] = {&w.recA, &w.recB, &w.recC, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
+  DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
                     &w.keys, &w.splats, &w.seg_queue, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos, &c->rig.dev};

@@ -78,8 +78,9 @@ constexpr uint32_t kDepthLo = 0x3D000000u;  // 2^-5; sub-buckets span [2^-5, 2^3
 constexpr int kDepthSpanLog2 = 26;
 
 struct Workspace {
-  // per-item preprocess results; items = [V*N static | F*Nm dynamic]
-  DevBuf recA, recB, recC, rad;
+  // per-item preprocess results; items = [V*N static | F*Nm dynamic].  rec: 64 B per item =
+  // {px,py,hx,hy | conic.xyz,opacity | r,g,b,depth | pad} so a gather touches two aligned 32 B sectors.
+  DevBuf rec, rad;
   // bins: (list, tile, bucket); lists = [V static | F dynamic]
   DevBuf bin_count, bin_off, bin_cursor, scan_tmp;
   // tile entries

@@ -314,9 +314,9 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i
     hy = sqrtf(2.f * tau * cz) * 1.001f + 0.01f;
   }
 
-  recA[item] = make_float4(px, py, hx, hy);
-  recB[item] = make_float4(conx, cony, conz, opac);
-  recC[item] = make_float4(rgb[0], rgb[1], rgb[2], pvz);
+  recA[4 * item] = make_float4(px, py, hx, hy);
+  recB[4 * item] = make_float4(conx, cony, conz, opac);
+  recC[4 * item] = make_float4(rgb[0], rgb[1], rgb[2], pvz);
   rad[item] = radius;
 
   // ---- count this Gaussian into every (tile, depth bucket) bin it touches ----
@@ -417,8 +417,8 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
       const int64_t item = item_base + (int64_t)list * n_items + i;
       const int radius = rad[item];
       if (radius <= 0) continue;
-      const float4 a = recA[item];
-      const float depth = recC[item].w;
+      const float4 a = recA[4 * item];
+      const float depth = recC[4 * item].w;
       const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
       const uint32_t bk = depth_bucket(depth, g);
       for (int y = rc.y0; y < rc.y1; ++y)
@@ -439,8 +439,8 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     const int64_t item = item_base + (int64_t)list * n_items + i;
     const int radius = rad[item];
     if (radius <= 0) continue;
-    const float4 a = recA[item];
-    const float depth = recC[item].w;
+    const float4 a = recA[4 * item];
+    const float depth = recC[4 * item].w;
     const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
     const uint32_t idx = DYN ? (uint32_t)ga.mov_idx[i] : (uint32_t)i;
     const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | idx;
@@ -476,9 +476,9 @@ __global__ void frame_attrs_kernel(int64_t N, int64_t Nm, int32_t V, int32_t fra
   float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
   int tt = 0;
   if (r > 0) {
-    a = recA[item];
-    b = recB[item];
-    c = recC[item];
+    a = recA[4 * item];
+    b = recB[4 * item];
+    c = recC[4 * item];
     const Rect rc = tile_rect(a.x, a.y, r, g.gx, g.gy);
     tt = (rc.y1 - rc.y0) * (rc.x1 - rc.x0);
   }
@@ -562,14 +562,14 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     sm += (size_t)num_slots * GSW_POSE_STRIDE * sizeof(float);
     if ((rc = ensure_smem(preprocess_kernel<true>, sm))) return rc;
     preprocess_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
-                                                  frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
-                                                  w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
+                                                  frame_env, frame_view, pose, num_slots, w.rec.as<float4>(),
+                                                  w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),
                                                   w.bin_count.as<uint32_t>(), use_hist);
   } else {
     if ((rc = ensure_smem(preprocess_kernel<false>, sm))) return rc;
     preprocess_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
-                                                   frame_env, frame_view, pose, num_slots, w.recA.as<float4>(),
-                                                   w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(),
+                                                   frame_env, frame_view, pose, num_slots, w.rec.as<float4>(),
+                                                   w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),
                                                    w.bin_count.as<uint32_t>(), use_hist);
   }
   count_launches(1);
@@ -588,14 +588,14 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   int rc;
   if (dynamic) {
     if ((rc = ensure_smem(scatter_kernel<true>, sm))) return rc;
-    scatter_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
-                                               w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
+    scatter_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
+                                               w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
                                                use_hist);
   } else {
     if ((rc = ensure_smem(scatter_kernel<false>, sm))) return rc;
-    scatter_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.recA.as<float4>(),
-                                                w.recC.as<float4>(), w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
+    scatter_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
+                                                w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                 w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
                                                 use_hist);
   }
@@ -610,8 +610,8 @@ int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_
   auto& w = ctx->ws;
   if (L.N <= 0) return 0;
   frame_attrs_kernel<<<(unsigned)((L.N + 255) / 256), 256, 0, s>>>(
-      L.N, L.Nm, L.V, frame, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(), L.g, w.recA.as<float4>(),
-      w.recB.as<float4>(), w.recC.as<float4>(), w.rad.as<int32_t>(), radii, tiles_touched, depth, xy, conic_opacity,
+      L.N, L.Nm, L.V, frame, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(), L.g, w.rec.as<float4>(),
+      w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(), radii, tiles_touched, depth, xy, conic_opacity,
       rgb);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
