@@ -40,13 +40,28 @@ __device__ __forceinline__ float2 lds64(uint32_t addr) {
   return v;
 }
 
+// keeps a shared-memory byte address in a register (the compiler otherwise re-derives it every use)
+__device__ __forceinline__ uint32_t pin(uint32_t x) {
+  asm volatile("" : "+r"(x));
+  return x;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v));
+}
+
 __global__ void __launch_bounds__(256)
 blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
              const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats, int64_t cap, FrameGeom g,
              float bg0, float bg1, float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8,
              float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status) {
-  __shared__ float4 sA[kChunk], sB[kChunk], sC[kChunk];
-  __shared__ unsigned long long kS[kChunk], kD[kChunk];
+  __shared__ float4 sRec[kChunk * 3];                  // staged records, 48 B each: {a, b, c}
+  __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
+  __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
   const int64_t ft = blockIdx.x;
   const int f = (int)(ft / g.T), tile = (int)(ft % g.T);
   const int tx = tile % g.gx, ty = tile / g.gx;
@@ -70,23 +85,24 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   const uint32_t total = ns + nd;
   uint32_t i0 = 0, j0 = 0;  // consumed from the static / dynamic stream (block-uniform)
 
-  const uint32_t aA = (uint32_t)__cvta_generic_to_shared(sA), aB = (uint32_t)__cvta_generic_to_shared(sB),
-                 aC = (uint32_t)__cvta_generic_to_shared(sC);
+  const uint32_t aRec = pin((uint32_t)__cvta_generic_to_shared(sRec));
+  const uint32_t aQ = pin((uint32_t)__cvta_generic_to_shared(&sQ[w][0]));
 
-  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
-  bool done = !inside;
+  // Tacc is the transmittance used for accumulation; it is forced to 0 once the pixel has saturated so
+  // that every later record fails the T test at once.  Tout keeps the value the reference writes out.
+  float Tacc = inside ? 1.0f : 0.0f, Tout = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
   uint32_t base = 0;
   for (; base < total; base += kChunk) {
-    if (__syncthreads_and(done)) break;  // also protects the staging buffers of the previous round
+    if (__syncthreads_and(Tacc == 0.0f)) break;  // also protects the staging buffers of the previous round
     const uint32_t n = min((uint32_t)kChunk, total - base);
     const uint32_t rs = ns - i0, rd = nd - j0;
     if (rs == 0 || rd == 0) {  // single-stream chunk
       const uint32_t src = rd == 0 ? s0 + i0 : d0 + j0;
       if (threadIdx.x < n) {
         const Splat* sp = splats + src + threadIdx.x;
-        sA[threadIdx.x] = __ldg(&sp->a);
-        sB[threadIdx.x] = __ldg(&sp->b);
-        sC[threadIdx.x] = __ldg(&sp->c);
+        sRec[3 * threadIdx.x] = __ldg(&sp->a);
+        sRec[3 * threadIdx.x + 1] = __ldg(&sp->b);
+        sRec[3 * threadIdx.x + 2] = __ldg(&sp->c);
       }
       if (rd == 0) i0 += n; else j0 += n;
     } else {  // merge-path over two key windows
@@ -105,49 +121,56 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         const uint32_t a = lo, b = t - lo;
         take_s = a < ws && (b >= wd || kS[a] < kD[b]);
         const Splat* sp = splats + (take_s ? s0 + i0 + a : d0 + j0 + b);
-        sA[t] = __ldg(&sp->a);
-        sB[t] = __ldg(&sp->b);
-        sC[t] = __ldg(&sp->c);
+        sRec[3 * t] = __ldg(&sp->a);
+        sRec[3 * t + 1] = __ldg(&sp->b);
+        sRec[3 * t + 2] = __ldg(&sp->c);
       }
       const uint32_t cs = (uint32_t)__syncthreads_count(take_s);
       i0 += cs;
       j0 += n - cs;
     }
     __syncthreads();
-    if (__all_sync(0xffffffffu, done)) continue;
+    if (__all_sync(0xffffffffu, Tacc == 0.0f)) continue;
+
+    // ---- cull: one staged record per lane against this warp's 8x4 pixel block; hits go to the warp's queue ----
+    uint32_t cnt = 0;
     for (uint32_t j0w = 0; j0w < n; j0w += 32) {
       const uint32_t j = j0w + lane;
       bool hit = false;
       if (j < n) {
-        const float4 a = lds128(aA + j * 16);
+        const float4 a = lds128(aRec + j * 48);
         hit = a.z >= 0.f && !(a.x + a.z < bx0 || a.x - a.z > bx1 || a.y + a.w < by0 || a.y - a.w > by1);
       }
-      uint32_t mask = __ballot_sync(0xffffffffu, hit);
-      while (mask) {
-        const uint32_t jj = j0w + (uint32_t)(__ffs(mask) - 1);
-        mask &= mask - 1;
-        if (done) continue;
-        const float2 xy = lds64(aA + jj * 16);
-        const float4 b = lds128(aB + jj * 16);
-        const float dx = xy.x - pxf, dy = xy.y - pyf;
-        const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
-        if (p2 > 0.0f) continue;
-        const float alpha = fminf(0.99f, b.w * ex2_approx(p2));
-        if (alpha < 1.0f / 255.0f) continue;
-        const float test_T = T * (1 - alpha);
-        if (test_T < 0.0001f) {
-          done = true;
-          continue;
-        }
-        const float4 c = lds128(aC + jj * 16);
-        const float wgt = alpha * T;
-        C0 += c.x * wgt;
-        C1 += c.y * wgt;
-        C2 += c.z * wgt;
-        invd += c.w * wgt;
-        T = test_T;
+      const uint32_t mask = __ballot_sync(0xffffffffu, hit);
+      if (hit) sts_u8(aQ + cnt + __popc(mask & ((1u << lane) - 1u)), j);
+      cnt += __popc(mask);
+    }
+    __syncwarp();
+
+    // ---- blend the queued records in list order ----
+    for (uint32_t k = 0; k < cnt; ++k) {
+      if ((k & 15u) == 15u && __all_sync(0xffffffffu, Tacc == 0.0f)) break;
+      const uint32_t ra = aRec + lds_u8(aQ + k) * 48;
+      const float2 xy = lds64(ra);
+      const float4 b = lds128(ra + 16);
+      const float dx = xy.x - pxf, dy = xy.y - pyf;
+      const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
+      if (p2 > 0.0f) continue;
+      const float alpha = fminf(0.99f, b.w * ex2_approx(p2));
+      if (alpha < 1.0f / 255.0f) continue;
+      const float test_T = Tacc * (1 - alpha);
+      if (test_T < 0.0001f) {  // saturated (or already saturated: Tacc == 0)
+        Tacc = 0.0f;
+        continue;
       }
-      if (__all_sync(0xffffffffu, done)) break;
+      const float4 c = lds128(ra + 32);
+      const float wgt = alpha * Tacc;
+      C0 += c.x * wgt;
+      C1 += c.y * wgt;
+      C2 += c.z * wgt;
+      invd += c.w * wgt;
+      Tacc = test_T;
+      Tout = test_T;
     }
   }
   if (threadIdx.x == 0) atomicAdd((unsigned long long*)&status[3], (unsigned long long)min(base, total));
@@ -158,6 +181,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
       bg1 = bg_dev[1];
       bg2 = bg_dev[2];
     }
+    const float T = Tout;
     const float r = C0 + T * bg0, gr = C1 + T * bg1, b = C2 + T * bg2;
     const size_t HW = (size_t)g.H * g.W, pid = (size_t)py * g.W + px;
     if (out_color) {
