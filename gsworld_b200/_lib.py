@@ -40,6 +40,8 @@ SYMBOLS = {
     "gsw_set_depth_buckets": (C.c_int, [_vp, C.c_int]),
     "gsw_rasterize_forward": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f, _vp,
                                         _vp, _vp, _vp, _vp, _f, _f, _i32, _i32, _f, _vp, _vp, _vp, _vp]),
+    "gsw_rasterize_forward_static": (C.c_int, [_i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp,
+                                               _vp, _vp, _vp, _f, _f, _i32, _f, _vp, _vp, _vp, _vp, _vp]),
     "gsw_mark_visible": (C.c_int, [_vp, _i32, _vp, _vp, _f, _vp, _vp]),
     "gsw_rig_set": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gsw_compose_poses": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, _vp, _vp]),

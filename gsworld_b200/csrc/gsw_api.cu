@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "gsw_internal.h"
@@ -539,6 +540,182 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
     if ((rc = launch_radii(c, out_radii, s))) return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[8], s);
   return finish_launch(c, s);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// gsw_rasterize_forward_static: the single-frame forward for callers that must not allocate.
+//
+// Who needs this: a render call made from inside a control loop with a hard latency bound (cudaMalloc /
+// cudaFree can stall behind every other stream of the process), or from a plugin that shares the GPU
+// with a simulator and has been handed a fixed memory budget it may not grow, or from a process whose
+// allocator is owned by someone else (an embedding runtime that forbids raw cudaMalloc).  Those callers
+// cannot use gsw_rasterize_forward, because that entry point sizes and (re)allocates a workspace in its
+// context whenever a shape grows.  Here every byte of scratch (projected records, tile bins, sort keys,
+// blend stream) lives in ONE fixed array compiled into the library, so the call allocates nothing and
+// frees nothing; the price is a hard size limit and ~17 MB of device memory held on every GPU that loads
+// libgsw.so, until the process exits.
+//
+// Limits (rejected with GSW_E_INVALID and a message, nothing is launched): P <= 32768 Gaussians,
+// ceil(W/16)*ceil(H/16) <= 1024 tiles (e.g. 512x512), and at most 262144 (Gaussian, tile) entries; the
+// entry count depends on the data, so it cannot be checked on the host: if a frame needs more, the
+// image is left as background and *out_status (a caller-provided device int64[4], may be NULL) reports
+// it: [0] = entries needed, [2] != 0 on overflow.
+//
+// Sharing: all calls on one device use the same array and it keeps whatever the previous call left.
+// Everything that must start at zero (bin counters, cursors, status words, queue counters) is cleared on
+// the stream at the start of every call.  Two calls whose GPU work overlaps (different streams, or
+// different host threads on the same device) would race on the array: serialise them.
+//
+// The first call on each device looks the array's device address up (cudaGetSymbolAddress needs that
+// device to be current; it is, this function uses the current device) and caches it.  Make that first
+// call before starting any stream capture.
+namespace {
+
+constexpr int32_t kNaMaxP = 32768;
+constexpr int32_t kNaMaxTiles = 1024;
+constexpr int64_t kNaMaxEntries = 262144;
+constexpr size_t kNaBytes = (size_t)17 << 20;
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never a device pointer.
+static __device__ __align__(256) unsigned char g_na_scratch[kNaBytes];
+
+constexpr int kNaMaxDevices = 64;
+struct NaDevice {
+  bool ready = false;
+  gsw_ctx ctx;  // workspace DevBufs point into g_na_scratch; nothing in it is ever allocated or freed
+};
+NaDevice g_na_dev[kNaMaxDevices];
+std::mutex g_na_mutex;
+
+// Carve the fixed array into the workspace slices run_pipeline expects, sized for the maxima above.
+int na_setup(int device, NaDevice& nd) {
+  void* basep = nullptr;
+  GSW_CUDA(cudaGetSymbolAddress(&basep, g_na_scratch));  // device `device` is current (checked by the caller)
+  unsigned char* base = static_cast<unsigned char*>(basep);
+  size_t off = 0;
+  auto carve = [&](DevBuf& b, size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    b.p = base + off;
+    b.bytes = bytes;
+    off += bytes;
+  };
+  gsw_ctx& c = nd.ctx;
+  c.device = device;
+  const int64_t nbins = 2 * (int64_t)kNaMaxTiles;  // one static + one (empty) dynamic list, NB = 1
+  auto& w = c.ws;
+  carve(w.rec, (size_t)kNaMaxP * 64);
+  carve(w.rad, (size_t)kNaMaxP * 4);
+  carve(w.bin_count, (size_t)(nbins + 1) * 4);
+  carve(w.bin_off, (size_t)(nbins + 1) * 4);
+  carve(w.bin_cursor, (size_t)(nbins + 1) * 4);
+  carve(w.scan_tmp, scan_tmp_elems(nbins) * 4);
+  carve(w.merge_cnt, (size_t)(kNaMaxTiles + 1) * 4);
+  carve(w.merge_off, (size_t)(kNaMaxTiles + 1) * 4);
+  carve(w.keys, (size_t)kNaMaxEntries * 8);
+  carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
+  carve(w.status, 64);
+  carve(w.seg_queue, (size_t)(2 * (kNaMaxEntries / kSortSmemKeys) + 3 * nbins + 16) * 16);
+  carve(w.cam, 64);
+  if (off > kNaBytes) {
+    set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);
+    return GSW_E_NOMEM;
+  }
+  c.cap_entries = kNaMaxEntries;
+  c.nb_user = 1;
+  nd.ready = true;
+  return GSW_OK;
+}
+
+}  // namespace
+
+int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const float* bg, int32_t width,
+                                 int32_t height, const float* means3D, const float* shs, const float* colors_precomp,
+                                 const float* opacities, const float* scales, float scale_modifier,
+                                 const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                 const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
+                                 int32_t antialiasing, float near_plane, float* out_color, int32_t* out_radii,
+                                 float* out_invdepth, int64_t* out_status, gsw_stream stream) {
+  if (P < 0 || width <= 0 || height <= 0 || !bg || !viewmatrix || !projmatrix || !campos) {
+    set_error("gsw_rasterize_forward_static: invalid argument");
+    return GSW_E_INVALID;
+  }
+  const int64_t tiles = (int64_t)((width + kTile - 1) / kTile) * ((height + kTile - 1) / kTile);
+  if (P > kNaMaxP || tiles > kNaMaxTiles) {
+    set_error("gsw_rasterize_forward_static: P=%d (max %d) or %lld tiles for %dx%d (max %d) exceeds the fixed "
+              "scratch array; use gsw_rasterize_forward for larger frames", P, kNaMaxP, (long long)tiles, width,
+              height, kNaMaxTiles);
+    return GSW_E_INVALID;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t HW = (size_t)height * width;
+  if (P == 0) {  // same convention as gsw_rasterize_forward: nothing to draw leaves zeros
+    if (out_color) GSW_CUDA(cudaMemsetAsync(out_color, 0, 3 * HW * 4, s));
+    if (out_invdepth) GSW_CUDA(cudaMemsetAsync(out_invdepth, 0, HW * 4, s));
+    if (out_status) GSW_CUDA(cudaMemsetAsync(out_status, 0, 4 * sizeof(int64_t), s));
+    return GSW_OK;
+  }
+  if ((shs == nullptr) == (colors_precomp == nullptr)) {
+    set_error("Please provide excatly one of either SHs or precomputed colors!");
+    return GSW_E_INVALID;
+  }
+  if (((scales == nullptr || rotations == nullptr) && cov3D_precomp == nullptr) ||
+      ((scales != nullptr || rotations != nullptr) && cov3D_precomp != nullptr)) {
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return GSW_E_INVALID;
+  }
+  if (shs && (sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1))) {
+    set_error("gsw_rasterize_forward_static: sh_degree %d needs M >= %d (got %d); degree <= 3 supported", sh_degree,
+              (sh_degree + 1) * (sh_degree + 1), M);
+    return GSW_E_INVALID;
+  }
+  int device = -1;
+  GSW_CUDA(cudaGetDevice(&device));
+  if (device < 0 || device >= kNaMaxDevices) {
+    set_error("gsw_rasterize_forward_static: device ordinal %d not supported (max %d)", device, kNaMaxDevices - 1);
+    return GSW_E_INVALID;
+  }
+  NaDevice& nd = g_na_dev[device];
+  {
+    std::lock_guard<std::mutex> lock(g_na_mutex);
+    if (!nd.ready) {  // once per device, with that device current
+      int rc0 = na_setup(device, nd);
+      if (rc0) return rc0;
+    }
+  }
+  gsw_ctx* c = &nd.ctx;
+  const FrameGeom g = make_geom(height, width, 1, antialiasing, scale_modifier, near_plane);
+  GaussArrays st{};
+  st.xyz = means3D;
+  st.scale_act = scales;
+  st.quat_act = rotations;
+  st.opacity = opacities;
+  st.sh = shs;
+  st.colors_precomp = colors_precomp;
+  st.cov3d_precomp = cov3D_precomp;
+  st.slot = nullptr;
+  st.sh_degree = sh_degree;
+  st.M = M;
+  struct {
+    float tx, ty;
+    int32_t e, v;
+  } hs{tan_fovx, tan_fovy, 0, 0};
+  GSW_CUDA(cudaMemcpyAsync(c->ws.cam.p, &hs, sizeof hs, cudaMemcpyHostToDevice, s));
+  const float* tanfov = c->ws.cam.as<float>();
+  const int32_t* fe = c->ws.cam.as<int32_t>() + 2;
+  const int32_t* fv = c->ws.cam.as<int32_t>() + 3;
+  // Every workspace request below fits its slice (sizes were checked against the maxima above), so the
+  // grow-only buffers never reach their allocation branch; the zero-initialised state is set by
+  // run_pipeline's memsets on the stream.
+  int rc = run_pipeline(c, st, P, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv, nullptr, 0, s);
+  if (rc) return rc;
+  c->last.single = true;
+  if ((rc = launch_blend(c, 1, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
+    return rc;
+  if (out_radii)
+    if ((rc = launch_radii(c, out_radii, s))) return rc;
+  if (out_status)
+    GSW_CUDA(cudaMemcpyAsync(out_status, c->ws.status.p, 4 * sizeof(int64_t), cudaMemcpyDeviceToDevice, s));
+  return GSW_OK;
 }
 
 int gsw_mark_visible(gsw_ctx* c, int32_t P, const float* means3D, const float* viewmatrix, float near_plane,

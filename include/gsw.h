@@ -124,6 +124,26 @@ int gsw_rasterize_forward(gsw_ctx* ctx, int32_t P, int32_t sh_degree, int32_t M,
                           int32_t antialiasing, float near_plane, float* out_color, int32_t* out_radii,
                           float* out_invdepth, gsw_stream stream);
 
+/* Single-frame forward that allocates nothing.  No counterpart in the reference (its rasterizer grows
+ * torch buffers on demand); it exists for callers that cannot call cudaMalloc at render time: a
+ * hard-real-time control loop, a plugin confined to a fixed GPU memory budget next to a simulator, or a
+ * host runtime that owns the allocator.  Same arguments and results as gsw_rasterize_forward, minus the
+ * context: all scratch lives in one fixed ~17 MB array inside libgsw.so (held on every GPU that loads the
+ * library until exit), so sizes are capped: P <= 32768 Gaussians, ceil(W/16)*ceil(H/16) <= 1024 tiles,
+ * <= 262144 (Gaussian, tile) entries.  Larger P / image: GSW_E_INVALID with a message, nothing launched.
+ * Too many entries (data dependent): the frame is left as background and out_status says so.
+ *   out_status: device int64[4] or NULL; [0] = entries the frame needed, [2] != 0 if they did not fit.
+ * Runs on the CURRENT device.  The first call on a device also looks up the array's address; make it
+ * before any stream capture.  All calls on a device share the array (cleared as needed at the start of
+ * each call): calls whose GPU work overlaps race, so keep them on one stream or otherwise serialised. */
+int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const float* bg, int32_t width,
+                                 int32_t height, const float* means3D, const float* shs, const float* colors_precomp,
+                                 const float* opacities, const float* scales, float scale_modifier,
+                                 const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                                 const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
+                                 int32_t antialiasing, float near_plane, float* out_color, int32_t* out_radii,
+                                 float* out_invdepth, int64_t* out_status, gsw_stream stream);
+
 int gsw_mark_visible(gsw_ctx* ctx, int32_t P, const float* means3D, const float* viewmatrix, float near_plane,
                      uint8_t* out_visible, gsw_stream stream);
 
