@@ -244,7 +244,7 @@ def run_ours(args):
         if world > 1:
             for i, c in enumerate(CAMERAS):
                 local_obs[i].copy_(out[c])
-            dist.all_gather_into_tensor(gathered.view(world, -1), local_obs.view(-1))
+            dist.all_gather_into_tensor(gathered.view(-1), local_obs.view(-1))
         return out
 
     def barrier():
@@ -261,6 +261,9 @@ def run_ours(args):
                     d2h[i].copy_(out[c], non_blocking=True)
         wrap.sync_each_step = d2h is not None  # resident-input runs are fully asynchronous
         barrier()
+        prof = steps > 0 and os.environ.get("GSW_PROFILE_RANGE") == "1"  # ncu --profile-from-start off
+        if prof:
+            torch.cuda.profiler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
@@ -271,6 +274,8 @@ def run_ours(args):
                 torch.cuda.current_stream().synchronize()  # the caller reads the observation every step
         e1.record()
         barrier()
+        if prof:
+            torch.cuda.profiler.stop()
         if not wrap._engine.finish(raise_on_overflow=False):
             raise RuntimeError("tile-entry workspace overflowed inside the timed region: number invalid")
         ms = e0.elapsed_time(e1)
