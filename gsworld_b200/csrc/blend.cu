@@ -132,7 +132,10 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     __syncthreads();
     if (__all_sync(0xffffffffu, Tacc == 0.0f)) continue;
 
-    // ---- cull: one staged record per lane against this warp's 8x4 pixel block; hits go to the warp's queue ----
+    // ---- cull: one staged record per lane against this warp's 8x4 pixel block; hits go to the warp's queue.
+    // Stage 1: bounding box of the alpha >= 1/255 footprint.  Stage 2 (box hits only): the exact maximum of
+    // the (concave) exponent over the pixel block, reached either at the splat centre or on one of the two
+    // block edges facing it; the record is dropped when even that maximum gives alpha < 1/255.
     uint32_t cnt = 0;
     for (uint32_t j0w = 0; j0w < n; j0w += 32) {
       const uint32_t j = j0w + lane;
@@ -140,6 +143,17 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
       if (j < n) {
         const float4 a = lds128(aRec + j * 48);
         hit = a.z >= 0.f && !(a.x + a.z < bx0 || a.x - a.z > bx1 || a.y + a.w < by0 || a.y - a.w > by1);
+        if (hit && a.z < 1.0e30f) {
+          const float4 b = lds128(aRec + j * 48 + 16);
+          const float x0 = bx0 - a.x, x1 = bx1 - a.x, y0 = by0 - a.y, y1 = by1 - a.y;
+          const float xe = fminf(fmaxf(0.f, x0), x1), ye = fminf(fmaxf(0.f, y0), y1);
+          const float ys = fminf(fmaxf(__fdividef(-0.5f * b.y * xe, b.z), y0), y1);
+          const float xs = fminf(fmaxf(__fdividef(-0.5f * b.y * ye, b.x), x0), x1);
+          const float p1 = xe * (b.x * xe + b.y * ys) + b.z * ys * ys;
+          const float p2 = xs * (b.x * xs + b.y * ye) + b.z * ye * ye;
+          const float t2 = __log2f(255.0f * b.w) * 1.002f + 0.02f;  // log2 of the largest useful attenuation
+          hit = fmaxf(p1, p2) >= -t2;
+        }
       }
       const uint32_t mask = __ballot_sync(0xffffffffu, hit);
       if (hit) sts_u8(aQ + cnt + __popc(mask & ((1u << lane) - 1u)), j);
@@ -148,29 +162,33 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     __syncwarp();
 
     // ---- blend the queued records in list order ----
-    for (uint32_t k = 0; k < cnt; ++k) {
-      if ((k & 15u) == 15u && __all_sync(0xffffffffu, Tacc == 0.0f)) break;
-      const uint32_t ra = aRec + lds_u8(aQ + k) * 48;
-      const float2 xy = lds64(ra);
-      const float4 b = lds128(ra + 16);
-      const float dx = xy.x - pxf, dy = xy.y - pyf;
-      const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
-      if (p2 > 0.0f) continue;
-      const float alpha = fminf(0.99f, b.w * ex2_approx(p2));
-      if (alpha < 1.0f / 255.0f) continue;
-      const float test_T = Tacc * (1 - alpha);
-      if (test_T < 0.0001f) {  // saturated (or already saturated: Tacc == 0)
-        Tacc = 0.0f;
-        continue;
+    for (uint32_t k0 = 0; k0 < cnt; k0 += 16) {
+      if (k0 && __all_sync(0xffffffffu, Tacc == 0.0f)) break;
+      const uint32_t kend = min(cnt, k0 + 16);
+#pragma unroll 4
+      for (uint32_t k = k0; k < kend; ++k) {
+        const uint32_t ra = aRec + lds_u8(aQ + k) * 48;
+        const float2 xy = lds64(ra);
+        const float4 b = lds128(ra + 16);
+        const float dx = xy.x - pxf, dy = xy.y - pyf;
+        const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
+        if (p2 > 0.0f) continue;
+        const float alpha = fminf(0.99f, b.w * ex2_approx(p2));
+        if (alpha < 1.0f / 255.0f) continue;
+        const float test_T = Tacc * (1 - alpha);
+        if (test_T < 0.0001f) {  // saturated (or already saturated: Tacc == 0)
+          Tacc = 0.0f;
+          continue;
+        }
+        const float4 c = lds128(ra + 32);
+        const float wgt = alpha * Tacc;
+        C0 += c.x * wgt;
+        C1 += c.y * wgt;
+        C2 += c.z * wgt;
+        invd += c.w * wgt;
+        Tacc = test_T;
+        Tout = test_T;
       }
-      const float4 c = lds128(ra + 32);
-      const float wgt = alpha * Tacc;
-      C0 += c.x * wgt;
-      C1 += c.y * wgt;
-      C2 += c.z * wgt;
-      invd += c.w * wgt;
-      Tacc = test_T;
-      Tout = test_T;
     }
   }
   if (threadIdx.x == 0) atomicAdd((unsigned long long*)&status[3], (unsigned long long)min(base, total));
