@@ -75,6 +75,7 @@ __device__ __forceinline__ uint32_t depth_bucket(float depth, const FrameGeom& g
 
 struct ViewSmem {
   float V[16], P[16], cam[3], tanx, tany;
+  float wnorm;  // upper bound on the squared spectral norm of the view matrix's 3x3 block (1 for a rigid camera)
 };
 
 // One colour channel of the degree<=3 SH polynomial, same association as the published kernel.
@@ -108,42 +109,42 @@ constexpr size_t kMaxHistBytes = 160 * 1024;         // per-CTA shared histogram
 // Per-item body.  `hist` (shared, one counter per (tile, bucket) of this list) may be null, in which case
 // the global bin counters are hit directly.
 template <bool DYN>
-__device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i, int64_t item, int list_global,
+__device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const GaussArrays& la, int64_t i, int64_t il, int64_t item, int list_global,
                                                 const FrameGeom& g, const ViewSmem& vs, const float* pose_s,
                                                 float4* __restrict__ recA, float4* __restrict__ recB,
                                                 float4* __restrict__ recC, int32_t* __restrict__ rad,
                                                 uint32_t* __restrict__ bin_count, uint32_t* hist) {
-  if (!DYN && ga.slot != nullptr && ga.slot[i] >= 0) {  // movable: handled by the dynamic layer
+  if (!DYN && la.slot != nullptr && la.slot[il] >= 0) {  // movable: handled by the dynamic layer
     rad[item] = 0;
     return;
   }
 
-  float p[3] = {ga.xyz[3 * i], ga.xyz[3 * i + 1], ga.xyz[3 * i + 2]};
+  float p[3] = {la.xyz[3 * il], la.xyz[3 * il + 1], la.xyz[3 * il + 2]};
   float sc[3] = {0.f, 0.f, 0.f};
   float q[4] = {1.f, 0.f, 0.f, 0.f};
   const bool have_cov = (!DYN) && ga.cov3d_precomp != nullptr;
 
   if (DYN) {
     // ---- rigid transform of a movable Gaussian (gs_utils.py:283-385 order: scale, rotate, translate) ----
-    const float* ps = pose_s + ga.mov_slot[i] * GSW_POSE_STRIDE;
+    const float* ps = pose_s + la.mov_slot[il] * GSW_POSE_STRIDE;
     const float kappa = ps[16];
     const bool has_scale = ps[17] != 0.f;
     if (has_scale) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         p[k] = p[k] * kappa;
-        const float u = expf(ga.log_scale_raw[3 * i + k]) * kappa;
+        const float u = expf(la.log_scale_raw[3 * il + k]) * kappa;
         const float ls = logf(u / (1.0f - u));  // inverse_sigmoid, the reference behaviour (gs_utils.py:310)
         sc[k] = expf(ls);
       }
     } else {
 #pragma unroll
-      for (int k = 0; k < 3; ++k) sc[k] = ga.scale_act[3 * i + k];
+      for (int k = 0; k < 3; ++k) sc[k] = la.scale_act[3 * il + k];
     }
     float rp[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r) rp[r] = ps[3 * r] * p[0] + ps[3 * r + 1] * p[1] + ps[3 * r + 2] * p[2];
-    const float4 qr = reinterpret_cast<const float4*>(ga.quat_raw)[i];
+    const float4 qr = reinterpret_cast<const float4*>(la.quat_raw)[il];
     const float nrm = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
     const float bw = qr.x / nrm, bx = qr.y / nrm, by = qr.z / nrm, bz = qr.w / nrm;
     const float aw = ps[12], ax = ps[13], ay = ps[14], az = ps[15];
@@ -178,18 +179,38 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i
   const float phw = P[3] * p[0] + P[7] * p[1] + P[11] * p[2] + P[15];
   const float pw = 1.0f / (phw + 0.0000001f);
   const float ppx = phx * pw, ppy = phy * pw;
+  const float px = ndc2pix(ppx, g.W), py = ndc2pix(ppy, g.H);
 
-  // ---- 3D covariance ----
+  // ---- Jacobian of the projection (EWA) ----
+  const float focal_y = (float)g.H / (2.0f * vs.tany);
+  const float focal_x = (float)g.W / (2.0f * vs.tanx);
+  float tx = pvx, ty = pvy;
+  const float tz = pvz;
+  {
+    const float limx = 1.3f * vs.tanx, limy = 1.3f * vs.tany;
+    const float txtz = tx / tz, tytz = ty / tz;
+    tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+    ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+  }
+  M3 J;
+  J.m[0][0] = focal_x / tz;  J.m[0][1] = 0.f;            J.m[0][2] = -(focal_x * tx) / (tz * tz);
+  J.m[1][0] = 0.f;           J.m[1][1] = focal_y / tz;   J.m[1][2] = -(focal_y * ty) / (tz * tz);
+  J.m[2][0] = 0.f;           J.m[2][1] = 0.f;            J.m[2][2] = 0.f;
+
+  // ---- 3D covariance: M = S*R first, so that an upper bound on the screen radius is available early ----
   float c3[6];
+  M3 M;
+  float tr_sigma;  // trace of the 3D covariance >= its largest eigenvalue
   if (have_cov) {
 #pragma unroll
     for (int k = 0; k < 6; ++k) c3[k] = ga.cov3d_precomp[6 * i + k];
+    tr_sigma = c3[0] + c3[3] + c3[5];
   } else {
     if (!DYN) {
-      sc[0] = ga.scale_act[3 * i];
-      sc[1] = ga.scale_act[3 * i + 1];
-      sc[2] = ga.scale_act[3 * i + 2];
-      const float4 qq = reinterpret_cast<const float4*>(ga.quat_act)[i];
+      sc[0] = la.scale_act[3 * il];
+      sc[1] = la.scale_act[3 * il + 1];
+      sc[2] = la.scale_act[3 * il + 2];
+      const float4 qq = reinterpret_cast<const float4*>(la.quat_act)[il];
       q[0] = qq.x; q[1] = qq.y; q[2] = qq.z; q[3] = qq.w;
     }
     M3 S;
@@ -211,27 +232,36 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i
     R.m[2][0] = 2.f * (x * z - r * y);
     R.m[2][1] = 2.f * (y * z + r * x);
     R.m[2][2] = 1.f - 2.f * (x * x + y * y);
-    const M3 M = mul3(S, R);
+    M = mul3(S, R);
+    tr_sigma = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int rr = 0; rr < 3; ++rr) tr_sigma += M.m[c][rr] * M.m[c][rr];
+  }
+
+  // ---- conservative frustum cull (not in the reference; it only skips work whose result is "no tile") ----
+  // trace(cov2D) <= lambda_max(Sigma) * |J|_F^2 * |W|_2^2 and lambda_1 <= trace(cov2D) + 0.92, so the true
+  // radius ceil(3 sqrt(lambda_1)) is <= r_b; if even a splat of radius r_b around (px,py) cannot reach the
+  // tile grid, the exact path below would end in the same empty tile rectangle.  NaNs fail every test.
+  {
+    const float jf2 = J.m[0][0] * J.m[0][0] + J.m[0][2] * J.m[0][2] + J.m[1][1] * J.m[1][1] + J.m[1][2] * J.m[1][2];
+    const float lam_b = tr_sigma * jf2 * vs.wnorm * 1.02f + 1.0f;
+    const float r_b = 3.0f * sqrtf(lam_b) + 2.0f;
+    if (tr_sigma >= 0.f &&
+        (px + r_b < 0.5f || px - r_b > (float)(g.gx * kTile) + 0.5f || py + r_b < 0.5f ||
+         py - r_b > (float)(g.gy * kTile) + 0.5f)) {
+      rad[item] = 0;
+      return;
+    }
+  }
+  if (!have_cov) {
     const M3 Sig = mul3(tr3(M), M);
     c3[0] = Sig.m[0][0]; c3[1] = Sig.m[0][1]; c3[2] = Sig.m[0][2];
     c3[3] = Sig.m[1][1]; c3[4] = Sig.m[1][2]; c3[5] = Sig.m[2][2];
   }
 
   // ---- EWA 2D covariance ----
-  const float focal_y = (float)g.H / (2.0f * vs.tany);
-  const float focal_x = (float)g.W / (2.0f * vs.tanx);
-  float tx = pvx, ty = pvy;
-  const float tz = pvz;
-  {
-    const float limx = 1.3f * vs.tanx, limy = 1.3f * vs.tany;
-    const float txtz = tx / tz, tytz = ty / tz;
-    tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
-    ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
-  }
-  M3 J;
-  J.m[0][0] = focal_x / tz;  J.m[0][1] = 0.f;            J.m[0][2] = -(focal_x * tx) / (tz * tz);
-  J.m[1][0] = 0.f;           J.m[1][1] = focal_y / tz;   J.m[1][2] = -(focal_y * ty) / (tz * tz);
-  J.m[2][0] = 0.f;           J.m[2][1] = 0.f;            J.m[2][2] = 0.f;
   M3 Wm;
   Wm.m[0][0] = V[0]; Wm.m[0][1] = V[4]; Wm.m[0][2] = V[8];
   Wm.m[1][0] = V[1]; Wm.m[1][1] = V[5]; Wm.m[1][2] = V[9];
@@ -262,7 +292,6 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i
   const float lam1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
   const float lam2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
   const float my_radius = ceilf(3.f * sqrtf(fmaxf(lam1, lam2)));
-  const float px = ndc2pix(ppx, g.W), py = ndc2pix(ppy, g.H);
   const int radius = (int)my_radius;
   const Rect rc = tile_rect(px, py, radius, g.gx, g.gy);
   if ((rc.x1 - rc.x0) * (rc.y1 - rc.y0) == 0) {
@@ -302,7 +331,7 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i
   }
 
   // ---- footprint of alpha >= 1/255 (cull box for the blend; conservative, not a parity quantity) ----
-  const float opac = ga.opacity[i] * h_scale;
+  const float opac = la.opacity[il] * h_scale;
   float hx, hy;
   if (!(opac * 255.0f >= 0.999f)) {
     hx = hy = -1.0f;  // can never reach alpha 1/255
@@ -332,9 +361,35 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, int64_t i
   }
 }
 
-// grid: (ceil(n_items / kItemsPerBlock), n_lists); list = view (static layer) or frame (dynamic layer).
-// Dynamic shared memory: [hist: T*NB u32 (if use_hist)] [pose table of the frame's env (DYN)].
-template <bool DYN>
+// ---- TMA bulk staging (cp.async.bulk + mbarrier): one elected thread pulls the CTA's contiguous slices of
+// the small per-Gaussian arrays into shared memory in a few large asynchronous copies, so the per-item
+// code never waits on a dependent global load for them (the kernel was latency-bound on exactly those).
+__device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(mbar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+        : "=r"(ok)
+        : "r"(mbar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+
+// grid: (ceil(n_items / IPB), n_lists); list = view (static layer) or frame (dynamic layer).
+// Dynamic shared memory: [staged arrays (if use_tma)] [hist: T*NB u32 (if use_hist)] [pose table (DYN)].
+template <bool DYN, int IPB, bool TMA>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                   const float* __restrict__ views, const float* __restrict__ projs,
@@ -343,16 +398,52 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
                   const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
                   float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
                   uint32_t* __restrict__ bin_count, int use_hist) {
+  constexpr int use_tma = TMA ? 1 : 0;
   __shared__ ViewSmem vs;
-  extern __shared__ uint32_t dsm[];
+  __shared__ __align__(8) unsigned long long mbar_s;
+  extern __shared__ __align__(128) unsigned char dsm_raw[];
+  constexpr int IPT = IPB / 256;
   const int nbl = g.T * g.NB;
-  uint32_t* hist = use_hist ? dsm : nullptr;
-  float* pose_s = reinterpret_cast<float*>(dsm + (use_hist ? nbl : 0));
+  // staged layout (bytes per item): static 12 xyz + 12 scale + 16 quat + 4 opacity + 4 slot = 48;
+  //                                 dynamic 12 xyz + 12 scale + 12 log-scale + 16 quat_raw + 4 opacity + 4 slot = 60
+  constexpr size_t kStage = (size_t)IPB * (DYN ? 60 : 48);
+  unsigned char* stage = dsm_raw;
+  uint32_t* hist_base = reinterpret_cast<uint32_t*>(dsm_raw + (use_tma ? kStage : 0));
+  uint32_t* hist = use_hist ? hist_base : nullptr;
+  float* pose_s = reinterpret_cast<float*>(hist_base + (use_hist ? nbl : 0));
   const int list = blockIdx.y;
   int view = list, env = 0;
   if (DYN) {
     view = frame_view[list];
     env = frame_env[list];
+  }
+  const int64_t base = (int64_t)blockIdx.x * IPB;
+  const bool full = base + IPB <= n_items;
+  const bool staged = use_tma && full;  // partial tail chunk: plain global loads
+  float* xyz_s = reinterpret_cast<float*>(stage);
+  float* sc_s = xyz_s + 3 * IPB;
+  float* ls_s = sc_s + 3 * IPB;                                // DYN only
+  float* q_s = DYN ? ls_s + 3 * IPB : sc_s + 3 * IPB;         // 16 B aligned: IPB multiple of 4
+  float* op_s = q_s + 4 * IPB;
+  int32_t* slot_s = reinterpret_cast<int32_t*>(op_s + IPB);
+  if (staged && threadIdx.x == 0) {
+    const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar_s);
+    mbar_init(mb, 1);
+    const bool want_slot = DYN || ga.slot != nullptr;
+    const uint32_t bytes = (uint32_t)IPB * ((DYN ? 56u : 44u) + (want_slot ? 4u : 0u));
+    mbar_expect_tx(mb, bytes);
+    auto sa = [](const void* p) { return (uint32_t)__cvta_generic_to_shared(p); };
+    bulk_g2s(sa(xyz_s), ga.xyz + 3 * base, IPB * 12, mb);
+    bulk_g2s(sa(sc_s), ga.scale_act + 3 * base, IPB * 12, mb);
+    if (DYN) {
+      bulk_g2s(sa(ls_s), ga.log_scale_raw + 3 * base, IPB * 12, mb);
+      bulk_g2s(sa(q_s), ga.quat_raw + 4 * base, IPB * 16, mb);
+      bulk_g2s(sa(slot_s), ga.mov_slot + base, IPB * 4, mb);
+    } else {
+      bulk_g2s(sa(q_s), ga.quat_act + 4 * base, IPB * 16, mb);
+      if (want_slot) bulk_g2s(sa(slot_s), ga.slot + base, IPB * 4, mb);
+    }
+    bulk_g2s(sa(op_s), ga.opacity + base, IPB * 4, mb);
   }
   if (threadIdx.x < 16) {
     vs.V[threadIdx.x] = views[view * 16 + threadIdx.x];
@@ -363,6 +454,18 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     vs.tanx = tanfov[view * 2];
   } else if (threadIdx.x == 20) {
     vs.tany = tanfov[view * 2 + 1];
+  } else if (threadIdx.x == 32) {  // Gershgorin bound on the largest eigenvalue of W^T W (W = view 3x3 block)
+    const float* Vg = views + view * 16;
+    float w[3][3];
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) w[r][c] = Vg[4 * c + r];
+    float best = 0.f;
+    for (int a = 0; a < 3; ++a) {
+      float row = 0.f;
+      for (int b = 0; b < 3; ++b) row += fabsf(w[0][a] * w[0][b] + w[1][a] * w[1][b] + w[2][a] * w[2][b]);
+      best = fmaxf(best, row);
+    }
+    vs.wnorm = best * 1.001f;
   }
   if (use_hist)
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
@@ -370,14 +473,34 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
       pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
   }
-  __syncthreads();
-  const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
+  __syncthreads();  // mbarrier initialised, view / pose / histogram ready
+  GaussArrays la = ga;
+  if (staged) {
+    mbar_wait((uint32_t)__cvta_generic_to_shared(&mbar_s), 0);
+    la.xyz = xyz_s;
+    la.scale_act = sc_s;
+    la.opacity = op_s;
+    if (DYN) {
+      la.log_scale_raw = ls_s;
+      la.quat_raw = q_s;
+      la.mov_slot = slot_s;
+    } else {
+      la.quat_act = q_s;
+      if (ga.slot != nullptr) la.slot = slot_s;
+    }
+  }
 #pragma unroll 1
-  for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + (int64_t)it * 256 + threadIdx.x;
-    if (i < n_items)
-      preprocess_item<DYN>(ga, i, item_base + (int64_t)list * n_items + i, list_base + list, g, vs, pose_s, recA, recB,
-                           recC, rad, bin_count, hist);
+  for (int it = 0; it < IPT; ++it) {
+    const int il = it * 256 + threadIdx.x;
+    const int64_t i = base + il;
+    if (i < n_items) {
+      if (TMA)
+        preprocess_item<DYN>(ga, la, i, staged ? (int64_t)il : i, item_base + (int64_t)list * n_items + i,
+                             list_base + list, g, vs, pose_s, recA, recB, recC, rad, bin_count, hist);
+      else  // same object for both roles: every load stays a read-only global load
+        preprocess_item<DYN>(ga, ga, i, i, item_base + (int64_t)list * n_items + i, list_base + list, g, vs, pose_s,
+                             recA, recB, recC, rad, bin_count, hist);
+    }
   }
   if (use_hist) {
     __syncthreads();
@@ -547,31 +670,51 @@ int ensure_smem(K kernel, size_t bytes) {
 }
 }  // namespace
 
+// The dynamic layer is arithmetic-bound (transform + SH for nearly every item), not load-latency-bound: it
+// keeps plain loads and the larger chunk; only the static layer stages through TMA.
+constexpr int kIpbStatic = 2048, kIpbDynamic = 2048;
+
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
                       const float* pose, int32_t num_slots, cudaStream_t s) {
   if (n_items <= 0 || n_lists <= 0) return 0;
-  dim3 grid((unsigned)((n_items + kItemsPerBlock - 1) / kItemsPerBlock), (unsigned)n_lists);
   auto& w = ctx->ws;
   const size_t hist_b = (size_t)g.T * g.NB * 4;
-  const int use_hist = hist_b <= kMaxHistBytes;
-  size_t sm = use_hist ? hist_b : 0;
-  int rc;
-  if (dynamic) {
-    sm += (size_t)num_slots * GSW_POSE_STRIDE * sizeof(float);
-    if ((rc = ensure_smem(preprocess_kernel<true>, sm))) return rc;
-    preprocess_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
-                                                  frame_env, frame_view, pose, num_slots, w.rec.as<float4>(),
-                                                  w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),
-                                                  w.bin_count.as<uint32_t>(), use_hist);
-  } else {
-    if ((rc = ensure_smem(preprocess_kernel<false>, sm))) return rc;
-    preprocess_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, view, proj, campos, tanfov,
-                                                   frame_env, frame_view, pose, num_slots, w.rec.as<float4>(),
-                                                   w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),
-                                                   w.bin_count.as<uint32_t>(), use_hist);
+  const size_t pose_b = dynamic ? (size_t)num_slots * GSW_POSE_STRIDE * sizeof(float) : 0;
+  auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  // TMA staging needs 16 B aligned sources and the scale/rotation input form
+  bool tma_ok = aligned16(ga.xyz) && aligned16(ga.scale_act) && aligned16(ga.opacity) && ga.scale_act != nullptr;
+  if (dynamic)
+    tma_ok = tma_ok && aligned16(ga.log_scale_raw) && aligned16(ga.quat_raw) && aligned16(ga.mov_slot);
+  else
+    tma_ok = tma_ok && ga.quat_act != nullptr && aligned16(ga.quat_act) && (ga.slot == nullptr || aligned16(ga.slot));
+  const size_t stage_b = dynamic ? (size_t)kIpbDynamic * 60 : (size_t)kIpbStatic * 48;
+  const size_t budget = 200 * 1024;
+  int use_tma = !dynamic && tma_ok && stage_b + pose_b + 1024 <= budget;
+  int use_hist = hist_b <= kMaxHistBytes && (use_tma ? stage_b : 0) + hist_b + pose_b <= budget;
+  if (!use_hist && use_tma && hist_b <= kMaxHistBytes) {  // prefer the histogram over staging when both do not fit
+    use_tma = 0;
+    use_hist = 1;
   }
+  const size_t sm = (use_tma ? stage_b : 0) + (use_hist ? hist_b : 0) + pose_b;
+  int rc;
+#define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_)                                                                          \
+  do {                                                                                                            \
+    dim3 grid((unsigned)((n_items + IPB_ - 1) / IPB_), (unsigned)n_lists);                                        \
+    if ((rc = ensure_smem(preprocess_kernel<DYN_, IPB_, TMA_>, sm))) return rc;                                   \
+    preprocess_kernel<DYN_, IPB_, TMA_><<<grid, 256, sm, s>>>(                                                    \
+        ga, n_items, list_base, item_base, g, view, proj, campos, tanfov, frame_env, frame_view, pose, num_slots, \
+        w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
+        w.bin_count.as<uint32_t>(), use_hist);                                                                    \
+  } while (0)
+  if (dynamic)
+    GSW_LAUNCH_PRE(true, kIpbDynamic, false);
+  else if (use_tma)
+    GSW_LAUNCH_PRE(false, kIpbStatic, true);
+  else
+    GSW_LAUNCH_PRE(false, kIpbStatic, false);
+#undef GSW_LAUNCH_PRE
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
