@@ -112,41 +112,61 @@ class ReplayEnv:
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
-
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons sampled (NVML, every 5 ms) while the timed region runs."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
 
-    def run(self):
-        while not self._stop_evt.is_set():
+    @staticmethod
+    def _physical_index(index):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
+                return int(vis.split(",")[index])
             except Exception:
                 pass
-            self._stop_evt.wait(0.2)
+        return index
+
+    def run(self):
+        nv = self.nv
+        while not self._stop_evt.is_set():
+            try:
+                if nv is not None:
+                    sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
+                        nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    self.rows.append((float(sm), int(r)))
+                else:
+                    out = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                    a, b = [float(x) for x in out.strip().split(",")]
+                    self.max_sm = b
+                    self.rows.append((a, 0))
+            except Exception:
+                pass
+            self._stop_evt.wait(0.005)
 
     def stop(self):
         self._stop_evt.set()
         self.join(timeout=3)
-        sm, mx, reasons = [], 0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx = max(mx, float(r[1]))
-                for n, v in zip(names, r[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                continue
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        reasons = set()
+        for _, r in self.rows:
+            for bit, n in names.items():
+                if r & bit:
+                    reasons.add(n)
+        sm = [a for a, _ in self.rows]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(getattr(self, "max_sm", 0)) or None,
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
@@ -234,21 +254,39 @@ def run_ours(args):
                               scan_link_mats=list(scan), strict_reference=strict)
         return env, wrap
 
-    gathered = torch.empty((world, len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev) if world > 1 else None
-    local_obs = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev)
+    # Multi-GPU: every step ends with ONE all-gather of the uint8 observations.  It is issued asynchronously
+    # into one of two buffers, so the exchange of step k overlaps the rendering of step k+1; a buffer is
+    # only reused after the collective that read/wrote it has completed.
+    nbuf = 2
+    gathered = [torch.empty((world, len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(nbuf)] \
+        if world > 1 else None
+    pending = [None] * nbuf
+    counter = [0]
 
     def step(env, wrap):
         env.advance()
         wrap.transform_gs_perlink(None)
         out = wrap._render_gsworld()
         if world > 1:
+            k = counter[0] % nbuf
+            counter[0] += 1
+            if pending[k] is not None:
+                pending[k].wait()
+            mine = gathered[k][rank]
             for i, c in enumerate(CAMERAS):
-                local_obs[i].copy_(out[c])
-            dist.all_gather_into_tensor(gathered.view(-1), local_obs.view(-1))
+                mine[i].copy_(out[c])
+            pending[k] = dist.all_gather_into_tensor(gathered[k].view(-1), mine.view(-1), async_op=True)
         return out
+
+    def drain():
+        for k in range(nbuf):
+            if pending[k] is not None:
+                pending[k].wait()
+                pending[k] = None
 
     def barrier():
         if world > 1:
+            drain()
             dist.barrier()
         torch.cuda.synchronize(dev)
 
@@ -272,6 +310,8 @@ def run_ours(args):
                 for i, c in enumerate(CAMERAS):
                     d2h[i].copy_(out[c], non_blocking=True)
                 torch.cuda.current_stream().synchronize()  # the caller reads the observation every step
+        if world > 1:
+            drain()  # the last exchanges belong to the timed steps
         e1.record()
         barrier()
         if prof:
