@@ -331,6 +331,8 @@ def run_ours(args):
     for mode, strict in modes:
         env, wrap = build(True, strict)
         eng = wrap._engine
+        if os.environ.get("GSW_NB"):
+            eng.set_depth_buckets(int(os.environ["GSW_NB"]))
         if mode == "strict":
             sampler = ClockSampler(local)
             timed(env, wrap, 0, args.warmup)

@@ -664,11 +664,12 @@ __global__ void gather_movable_kernel(int64_t Nm, const int32_t* mov_idx, GaussA
 
 namespace {
 template <auto Kernel>
-int ensure_smem(size_t bytes) {
-  static size_t granted = 48 * 1024;  // per kernel: raise the opt-in shared-memory limit only when it grows
-  if (bytes > granted) {
+int ensure_smem(size_t bytes, int device) {
+  static size_t granted[64] = {};  // per kernel and device: raise the opt-in shared-memory limit only when it grows
+  size_t& g = granted[device & 63];
+  if (bytes > 48 * 1024 && bytes > g) {
     GSW_CUDA(cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    granted = bytes;
+    g = bytes;
   }
   return 0;
 }
@@ -706,7 +707,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 #define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_)                                                                          \
   do {                                                                                                            \
     dim3 grid((unsigned)((n_items + IPB_ - 1) / IPB_), (unsigned)n_lists);                                        \
-    if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_>>(sm))) return rc;                                   \
+    if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_>>(sm, ctx->device))) return rc;                                   \
     preprocess_kernel<DYN_, IPB_, TMA_><<<grid, 256, sm, s>>>(                                                    \
         ga, n_items, list_base, item_base, g, view, proj, campos, tanfov, frame_env, frame_view, pose, num_slots, \
         w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
@@ -734,13 +735,13 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   const size_t sm = use_hist ? hist_b : 0;
   int rc;
   if (dynamic) {
-    if ((rc = ensure_smem<scatter_kernel<true>>(sm))) return rc;
+    if ((rc = ensure_smem<scatter_kernel<true>>(sm, ctx->device))) return rc;
     scatter_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
                                                w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
                                                use_hist);
   } else {
-    if ((rc = ensure_smem<scatter_kernel<false>>(sm))) return rc;
+    if ((rc = ensure_smem<scatter_kernel<false>>(sm, ctx->device))) return rc;
     scatter_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
                                                 w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                 w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
