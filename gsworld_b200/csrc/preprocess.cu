@@ -390,7 +390,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
 // grid: (ceil(n_items / IPB), n_lists); list = view (static layer) or frame (dynamic layer).
 // Dynamic shared memory: [staged arrays (if use_tma)] [hist: T*NB u32 (if use_hist)] [pose table (DYN)].
 template <bool DYN, int IPB, bool TMA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, TMA ? 2 : 3)
 preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                   const float* __restrict__ views, const float* __restrict__ projs,
                   const float* __restrict__ campos, const float* __restrict__ tanfov,
