@@ -1,0 +1,127 @@
+"""Parity and size-independent properties at BASELINE.json's full scene size (1M Gaussians, 256x256,
+fr3_umi + 2 objects, wrist + third-person camera), with a few envs so the CPU oracle finishes in seconds.
+
+* one frame per camera against the CPU oracle: radii, tile lists and order exact, colour within 1e-3;
+* idempotence: the same step rendered twice is byte-identical;
+* sharing the static tile lists between envs (strict mode, V = 2 views) gives byte-identical images to
+  rendering each env through its own copy of the same camera (V = 1 + B views);
+* checksum of checksums: the entry count the pipeline reports equals the sum of tiles touched over the
+  static Gaussians of every view plus the movable Gaussians of every frame;
+* sortedness: every tile list is strictly increasing in (depth bits, index) and the ranges tile [0, D_f).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as orc
+from tests.helpers import assert_image_close, oracle_frame_inputs
+
+pytestmark = pytest.mark.gpu
+
+H = W = 256
+B = 3
+
+
+@pytest.fixture(scope="module")
+def rig():
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200.gaussian_renderer import PipelineParams
+    from gsworld_b200.gs_world_wrapper import GSWorldWrapper
+    dev = torch.device("cuda:0")
+    objects = ("006_mustard_bottle", "snack_box")
+    scene = fx.make_scene(fx.SceneSpec(robot="fr3_umi", n_total=1_000_000, per_link=4000, objects=objects,
+                                       per_object=7000, seed=1237))
+    env = fx.FakeEnv("fr3_umi", num_envs=B, hw=(H, W), objects=objects, seed=21, device=dev)
+    scan = fx.forward_kinematics("fr3_umi", fx.rt.ROBOT_SCAN_QPOS["fr3_umi"][None])[0]
+    scene_dev = scene.to(dev)
+    mk = lambda strict: GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene_dev,
+                                       scan_link_mats=list(scan), strict_reference=strict)
+    return scene, env, mk
+
+
+def _render(wrap, **kw):
+    names = list(wrap.base_env.cameras)
+    wrap.transform_gs_perlink(None)
+    view, proj, campos, tanfov, fv = wrap._views(names)
+    fe = wrap._maps(len(names))
+    out = wrap._engine.render_frames(wrap._pose, view, proj, campos, tanfov, fe, fv, H, W,
+                                     num_envs=wrap.num_envs, **kw)
+    torch.cuda.synchronize()
+    return out, (view, proj, campos, tanfov, fv)
+
+
+def test_full_size_frames_match_oracle(rig):
+    scene, env, mk = rig
+    wrap = mk(True)
+    out, (view, proj, campos, tanfov, fv) = _render(wrap, want_u8=True, want_color=True, want_radii=True)
+    eng = wrap._engine
+    pose = wrap._pose.cpu().numpy()
+    slot = eng._keep["slot"].cpu().numpy()
+    T = (H // 16) * (W // 16)
+    for f in (1, B + 2):  # env 1 through the third-person camera, env 2 through the wrist camera
+        e, v = f % B, int(fv[f])
+        fin = oracle_frame_inputs(scene, slot, pose[e], 14)
+        want = orc.rasterize_forward(fin["xyz"], fin["opacities"], view[v].cpu().numpy(), proj[v].cpu().numpy(),
+                                     campos[v].cpu().numpy(), float(tanfov[v, 0]), float(tanfov[v, 1]), H, W,
+                                     shs=fin["shs"], scales=fin["scales"], rotations=fin["rotations"], debug=True)
+        radii = out["radii"][f].cpu().numpy()
+        is_obj = slot >= 14
+        np.testing.assert_array_equal(radii[~is_obj], want["radii"][~is_obj])
+        assert int((radii[is_obj] != want["radii"][is_obj]).sum()) <= 1
+        if (radii == want["radii"]).all():
+            lists = eng.debug_frame_lists(f, T)
+            assert lists["D"] == want["D"]
+            np.testing.assert_array_equal(lists["keys"].cpu().numpy().view(np.uint64), want["keys"])
+            np.testing.assert_array_equal(lists["vals"].cpu().numpy().view(np.uint32), want["vals"])
+            np.testing.assert_array_equal(lists["ranges"].cpu().numpy(), want["ranges"])
+        assert_image_close(out["color"][f].cpu().numpy(), want["color"], want["fragile"].astype(bool))
+
+
+def test_idempotent_and_shared_static_lists_change_nothing(rig):
+    scene, env, mk = rig
+    # give every env the same joint state so that all wrist cameras coincide
+    env._q[:] = env._q[0]
+    env._refresh()
+    strict = mk(True)
+    a, _ = _render(strict, want_u8=True, want_radii=True)
+    b, _ = _render(strict, want_u8=True, want_radii=True)
+    assert torch.equal(a["rgb_u8"], b["rgb_u8"]) and torch.equal(a["radii"], b["radii"])
+    per_env = mk(False)
+    c, (view, *_rest, fv) = _render(per_env, want_u8=True, want_radii=True)
+    assert view.shape[0] == 1 + B  # third-person camera collapsed to one view, wrist camera one view per env
+    assert torch.equal(a["rgb_u8"], c["rgb_u8"]) and torch.equal(a["radii"], c["radii"])
+
+
+def test_entry_checksum_and_sorted_lists(rig):
+    scene, env, mk = rig
+    wrap = mk(True)
+    out, (view, proj, campos, tanfov, fv) = _render(wrap, want_u8=True, want_radii=True)
+    eng = wrap._engine
+    D = eng.last_stats["D"]
+    slot = eng._keep["slot"]
+    static = slot < 0
+    total = 0
+    seen_views = set()
+    T = (H // 16) * (W // 16)
+    for f in range(out["radii"].shape[0]):
+        attrs = eng.debug_frame_attrs(f)
+        tt = attrs["tiles_touched"].long()
+        total += int(tt[~static].sum())
+        v = int(fv[f])
+        if v not in seen_views:
+            seen_views.add(v)
+            total += int(tt[static].sum())
+        if f in (0, out["radii"].shape[0] - 1):
+            lists = eng.debug_frame_lists(f, T)
+            assert lists["D"] == int(tt.sum())
+            keys = lists["keys"].cpu().numpy().view(np.uint64)
+            vals = lists["vals"].cpu().numpy().view(np.uint32).astype(np.uint64)
+            full = ((keys & np.uint64(0xFFFFFFFF)) << np.uint64(32)) | vals  # (depth bits, index) within a tile
+            tiles = keys >> np.uint64(32)
+            assert (np.diff(tiles.astype(np.int64)) >= 0).all()
+            same = tiles[1:] == tiles[:-1]
+            assert (full[1:][same] > full[:-1][same]).all()
+            r = lists["ranges"].cpu().numpy()
+            nz = r[r[:, 1] > r[:, 0]]
+            assert nz[0, 0] == 0 and nz[-1, 1] == lists["D"] and (nz[1:, 0] == nz[:-1, 1]).all()
+    assert total == D
