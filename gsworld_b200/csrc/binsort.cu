@@ -251,8 +251,8 @@ __device__ __forceinline__ Splat make_splat(const float4* __restrict__ rec, int6
 // 32 B sectors per entry), coalesced key reads and splat writes.  The list an entry belongs to is found
 // by binary search over the V+F list boundaries (bin_off at multiples of bins_per_list).
 __global__ void __launch_bounds__(256)
-gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t N,
-                     int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ mov_pos,
+gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t Ns,
+                     int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ pos_of,
                      const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
                      int64_t cap) {
   const uint32_t D = bin_off[nbins];
@@ -266,7 +266,8 @@ gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_
     const u64 key = keys[p];
     const uint32_t idx = (uint32_t)(key & 0xffffffffull);
     const bool dyn = lo >= V;
-    const int64_t item = dyn ? (int64_t)V * N + (int64_t)(lo - V) * Nm + mov_pos[idx] : (int64_t)lo * N + idx;
+    const int64_t pos = pos_of ? (int64_t)pos_of[idx] : (int64_t)idx;  // position inside the Gaussian's layer
+    const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)(lo - V) * Nm + pos : (int64_t)lo * Ns + pos;
     splats[p] = make_splat(rec, item);
   }
 }
@@ -535,7 +536,7 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t*
   return 0;
 }
 
-int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, int64_t Nm, const FrameGeom& g,
+int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g,
                      int64_t cap, cudaStream_t s) {
   if (nbins <= 0) return 0;
   auto& w = ctx->ws;
@@ -562,8 +563,8 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, in
                                                                         w.keys.as<unsigned long long>());
   sort_segments_kernel<kSmallKeys, 128><<<148 * 12, 128, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
                                                                       w.keys.as<unsigned long long>());
-  gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, N, Nm, bpl,
-                                                ctx->mov_pos.as<int32_t>(), w.keys.as<unsigned long long>(),
+  gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, Ns, Nm, bpl,
+                                                ctx->last.pos_of, w.keys.as<unsigned long long>(),
                                                 w.rec.as<float4>(), w.splats.as<Splat>(), cap);
   count_launches(5);
   GSW_CUDA(cudaGetLastError());

@@ -1,4 +1,5 @@
 // gsw_api.cu — extern "C" entry points of libgsw.so and launch orchestration.  See include/gsw.h.
+#include <algorithm>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -88,12 +89,12 @@ struct Guard {  // make ctx->device current for the duration of a call
 };
 
 // Shared body of gsw_render_frames / gsw_rasterize_forward once the layer inputs are known.
-int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussArrays* dyn, int64_t Nm, int32_t V,
-                 int32_t F, const FrameGeom& g, const float* view, const float* proj, const float* campos,
+int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, const int32_t* slot_orig,
+                 const int32_t* pos_of, const GaussArrays* dyn, int64_t Nm, int32_t V, int32_t F, const FrameGeom& g, const float* view, const float* proj, const float* campos,
                  const float* tanfov, const int32_t* frame_env, const int32_t* frame_view, const float* pose,
                  int32_t num_slots, cudaStream_t s) {
   auto& w = ctx->ws;
-  const int64_t items = (int64_t)V * N + (int64_t)F * Nm;
+  const int64_t items = (int64_t)V * Ns + (int64_t)F * Nm;  // N = original count (outputs), Ns = static-layer items
   const int64_t nbins = (int64_t)(V + F) * g.T * g.NB;
   const int64_t FT = (int64_t)F * g.T;
   if (nbins >= (int64_t)1 << 31 || items >= (int64_t)1 << 40) {
@@ -128,12 +129,12 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   };
 
   mark(0);
-  if ((rc = launch_preprocess(ctx, false, stat, N, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
+  if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
                               pose, num_slots, s)))
     return rc;
   mark(1);
   if (dyn && Nm > 0)
-    if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * N, g, view, proj, campos, tanfov, frame_env,
+    if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, view, proj, campos, tanfov, frame_env,
                                 frame_view, pose, num_slots, s)))
       return rc;
   mark(2);
@@ -141,11 +142,12 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
                             s)))
     return rc;
   mark(3);
-  if ((rc = launch_scatter(ctx, false, stat, N, V, 0, 0, g, cap, s))) return rc;
+  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, s))) return rc;
   if (dyn && Nm > 0)
-    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * N, g, cap, s))) return rc;
+    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, s))) return rc;
   mark(4);
-  if ((rc = launch_sort_bins(ctx, nbins, V, N, Nm, g, cap, s))) return rc;
+  ctx->last.pos_of = pos_of;  // the gather reads it
+  if ((rc = launch_sort_bins(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
   mark(5);
   mark(6);
 
@@ -153,7 +155,9 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, const GaussAr
   ctx->last.V = V;
   ctx->last.F = F;
   ctx->last.N = N;
+  ctx->last.Ns = Ns;
   ctx->last.Nm = Nm;
+  ctx->last.slot_orig = slot_orig;
   ctx->last.g = g;
   ctx->last.stat = stat;
   ctx->last.frame_env = frame_env;
@@ -217,7 +221,8 @@ int gsw_destroy(gsw_ctx* c) {
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
                     &w.keys, &w.splats, &w.seg_queue, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
-                    &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_pos, &c->rig.dev};
+                    &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
+                    &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
   for (DevBuf* b : bufs) b->release();
   if (c->h_status) cudaFreeHost(c->h_status);
   if (c->done_evt) cudaEventDestroy(c->done_evt);
@@ -238,6 +243,10 @@ int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_ac
     set_error("gsw_scene_set: num_slots %d out of range [0,512]", num_slots);
     return GSW_E_INVALID;
   }
+  if (slot && num_slots > 0 && N > 0 && (!log_scale_raw || !quat_raw)) {
+    set_error("gsw_scene_set: log_scale_raw/quat_raw are required when slots are given");
+    return GSW_E_INVALID;
+  }
   Guard gd(c->device);
   cudaStream_t s = (cudaStream_t)stream;
   c->have_scene = false;
@@ -252,48 +261,118 @@ int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_ac
   c->scene.sh = sh;
   c->scene.log_scale_raw = log_scale_raw;
   c->scene.quat_raw = quat_raw;
-  c->scene.slot = slot;
+  c->scene.slot = (slot && num_slots > 0) ? slot : nullptr;
   c->scene.sh_degree = 3;
   c->scene.M = 16;
+  c->slot_orig = c->scene.slot;
   c->Nm = 0;
-  if (slot && num_slots > 0 && N > 0) {
-    if (!log_scale_raw || !quat_raw) {
-      set_error("gsw_scene_set: log_scale_raw/quat_raw are required when slots are given");
+  c->Ns = 0;
+  if (N == 0) {
+    c->stat_layer = c->scene;
+    c->have_scene = true;
+    return GSW_OK;
+  }
+  // ---- host side, once per scene: split into layers and order each along a Morton curve ----
+  std::vector<int32_t> hslot;
+  if (c->scene.slot) {
+    hslot.resize((size_t)N);
+    GSW_CUDA(cudaMemcpyAsync(hslot.data(), slot, (size_t)N * 4, cudaMemcpyDeviceToHost, s));
+  }
+  std::vector<float> hxyz((size_t)N * 3);
+  GSW_CUDA(cudaMemcpyAsync(hxyz.data(), xyz, (size_t)N * 12, cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaStreamSynchronize(s));
+  float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+  for (int64_t i = 0; i < N; ++i) {
+    if (c->scene.slot && hslot[i] >= num_slots) {
+      set_error("gsw_scene_set: slot[%lld] = %d >= num_slots %d", (long long)i, hslot[i], num_slots);
       return GSW_E_INVALID;
     }
-    std::vector<int32_t> h((size_t)N);
-    GSW_CUDA(cudaMemcpyAsync(h.data(), slot, (size_t)N * 4, cudaMemcpyDeviceToHost, s));
-    GSW_CUDA(cudaStreamSynchronize(s));
-    std::vector<int32_t> idx, pos((size_t)N, -1);
-    for (int64_t i = 0; i < N; ++i) {
-      if (h[i] >= num_slots) {
-        set_error("gsw_scene_set: slot[%lld] = %d >= num_slots %d", (long long)i, h[i], num_slots);
-        return GSW_E_INVALID;
-      }
-      if (h[i] >= 0) {
-        pos[i] = (int32_t)idx.size();
-        idx.push_back((int32_t)i);
+    for (int k = 0; k < 3; ++k) {
+      const float v = hxyz[3 * i + k];
+      if (v == v) {
+        lo[k] = v < lo[k] ? v : lo[k];
+        hi[k] = v > hi[k] ? v : hi[k];
       }
     }
-    const int64_t Nm = (int64_t)idx.size();
-    int rc;
-    if ((rc = c->mov_pos.reserve((size_t)N * 4))) return rc;
-    GSW_CUDA(cudaMemcpyAsync(c->mov_pos.p, pos.data(), (size_t)N * 4, cudaMemcpyHostToDevice, s));
-    if (Nm > 0) {
-      const size_t m = (size_t)Nm;
-      if ((rc = c->mov_idx.reserve(m * 4)) || (rc = c->mov_xyz.reserve(m * 12)) ||
-          (rc = c->mov_scale_act.reserve(m * 12)) || (rc = c->mov_opacity.reserve(m * 4)) ||
-          (rc = c->mov_sh.reserve(m * 192)) || (rc = c->mov_log_scale.reserve(m * 12)) ||
-          (rc = c->mov_quat_raw.reserve(m * 16)) || (rc = c->mov_slot.reserve(m * 4)))
-        return rc;
-      GSW_CUDA(cudaMemcpyAsync(c->mov_idx.p, idx.data(), m * 4, cudaMemcpyHostToDevice, s));
-      c->Nm = Nm;
-      if ((rc = launch_gather_movable(c, s))) return rc;
-    }
-    GSW_CUDA(cudaStreamSynchronize(s));  // host staging vectors go out of scope
-  } else {
-    c->scene.slot = nullptr;
   }
+  auto spread = [](uint32_t v) {  // 10 bits -> every third bit
+    v &= 1023u;
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+  };
+  auto morton = [&](int64_t i) -> uint32_t {
+    uint32_t q[3];
+    for (int k = 0; k < 3; ++k) {
+      const float ext = hi[k] - lo[k];
+      float t = ext > 0.f ? (hxyz[3 * i + k] - lo[k]) / ext : 0.f;
+      if (!(t >= 0.f)) t = 0.f;
+      if (t > 1.f) t = 1.f;
+      q[k] = (uint32_t)(t * 1023.0f);
+    }
+    return spread(q[0]) | (spread(q[1]) << 1) | (spread(q[2]) << 2);
+  };
+  std::vector<std::pair<uint64_t, int32_t>> ks, km;  // (sort key, original index)
+  ks.reserve((size_t)N);
+  for (int64_t i = 0; i < N; ++i) {
+    const int32_t sl = c->scene.slot ? hslot[i] : -1;
+    if (sl < 0)
+      ks.emplace_back((uint64_t)morton(i), (int32_t)i);
+    else
+      km.emplace_back(((uint64_t)(uint32_t)sl << 32) | morton(i), (int32_t)i);  // by link first, then by position
+  }
+  std::sort(ks.begin(), ks.end());
+  std::sort(km.begin(), km.end());
+  const int64_t Ns = (int64_t)ks.size(), Nm = (int64_t)km.size();
+  std::vector<int32_t> sidx((size_t)Ns), midx((size_t)Nm), pos((size_t)N);
+  for (int64_t j = 0; j < Ns; ++j) {
+    sidx[j] = ks[j].second;
+    pos[ks[j].second] = (int32_t)j;
+  }
+  for (int64_t m = 0; m < Nm; ++m) {
+    midx[m] = km[m].second;
+    pos[km[m].second] = (int32_t)m;
+  }
+  int rc;
+  if ((rc = c->pos_of.reserve((size_t)N * 4))) return rc;
+  GSW_CUDA(cudaMemcpyAsync(c->pos_of.p, pos.data(), (size_t)N * 4, cudaMemcpyHostToDevice, s));
+  if (Ns > 0) {
+    const size_t n = (size_t)Ns, ng = (size_t)((Ns + 255) / 256);
+    if ((rc = c->st_idx.reserve(n * 4)) || (rc = c->st_xyz.reserve(n * 12)) || (rc = c->st_scale.reserve(n * 12)) ||
+        (rc = c->st_quat.reserve(n * 16)) || (rc = c->st_opacity.reserve(n * 4)) ||
+        (rc = c->st_bounds.reserve(ng * 32)))
+      return rc;
+    GSW_CUDA(cudaMemcpyAsync(c->st_idx.p, sidx.data(), n * 4, cudaMemcpyHostToDevice, s));
+  }
+  if (Nm > 0) {
+    const size_t m = (size_t)Nm, ng = (size_t)((Nm + 255) / 256);
+    if ((rc = c->mov_idx.reserve(m * 4)) || (rc = c->mov_xyz.reserve(m * 12)) ||
+        (rc = c->mov_scale_act.reserve(m * 12)) || (rc = c->mov_opacity.reserve(m * 4)) ||
+        (rc = c->mov_sh.reserve(m * 192)) || (rc = c->mov_log_scale.reserve(m * 12)) ||
+        (rc = c->mov_quat_raw.reserve(m * 16)) || (rc = c->mov_slot.reserve(m * 4)) ||
+        (rc = c->mov_bounds.reserve(ng * 32)))
+      return rc;
+    GSW_CUDA(cudaMemcpyAsync(c->mov_idx.p, midx.data(), m * 4, cudaMemcpyHostToDevice, s));
+  }
+  c->Ns = Ns;
+  c->Nm = Nm;
+  if ((rc = launch_gather_layers(c, s))) return rc;
+  GSW_CUDA(cudaStreamSynchronize(s));  // host staging vectors go out of scope
+  // the static layer the per-step launches consume: compact small arrays in Morton order, SH rows by original index
+  GaussArrays st{};
+  st.xyz = c->st_xyz.as<float>();
+  st.scale_act = c->st_scale.as<float>();
+  st.quat_act = c->st_quat.as<float>();
+  st.opacity = c->st_opacity.as<float>();
+  st.sh = sh;
+  st.key_idx = c->st_idx.as<int32_t>();
+  st.sh_idx = c->st_idx.as<int32_t>();
+  st.bounds = c->st_bounds.as<float>();
+  st.sh_degree = 3;
+  st.M = 16;
+  c->stat_layer = st;
   c->have_scene = true;
   return GSW_OK;
 }
@@ -349,11 +428,13 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   dyn.log_scale_raw = c->mov_log_scale.as<float>();
   dyn.quat_raw = c->mov_quat_raw.as<float>();
   dyn.mov_slot = c->mov_slot.as<int32_t>();
-  dyn.mov_idx = c->mov_idx.as<int32_t>();
+  dyn.key_idx = c->mov_idx.as<int32_t>();
+  dyn.bounds = c->mov_bounds.as<float>();
   dyn.sh_degree = 3;
   dyn.M = 16;
 
-  int rc = run_pipeline(c, c->scene, c->N, &dyn, c->Nm, d->num_views, d->num_frames, g, d->viewmatrix,
+  int rc = run_pipeline(c, c->stat_layer, c->N, c->Ns, c->slot_orig, c->pos_of.as<int32_t>(), &dyn, c->Nm,
+                        d->num_views, d->num_frames, g, d->viewmatrix,
                         d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s);
   if (rc) return rc;
   c->last.single = false;
@@ -530,7 +611,8 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   const float* tanfov = c->ws.cam.as<float>();
   const int32_t* fe = c->ws.cam.as<int32_t>() + 2;
   const int32_t* fv = c->ws.cam.as<int32_t>() + 3;
-  rc = run_pipeline(c, st, P, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv, nullptr, 0, s);
+  rc = run_pipeline(c, st, P, P, nullptr, nullptr, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv,
+                    nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
   if ((rc = launch_blend(c, 1, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
@@ -706,7 +788,8 @@ int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const 
   // Every workspace request below fits its slice (sizes were checked against the maxima above), so the
   // grow-only buffers never reach their allocation branch; the zero-initialised state is set by
   // run_pipeline's memsets on the stream.
-  int rc = run_pipeline(c, st, P, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv, nullptr, 0, s);
+  int rc = run_pipeline(c, st, P, P, nullptr, nullptr, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe,
+                        fv, nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
   if ((rc = launch_blend(c, 1, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))

@@ -60,7 +60,10 @@ struct GaussArrays {
   const float* log_scale_raw;  // [n,3]
   const float* quat_raw;       // [n,4]
   const int32_t* mov_slot;     // [n]
-  const int32_t* mov_idx;      // [n] original index
+  // index maps of a layer whose items are a re-ordered subset of the scene (null = identity)
+  const int32_t* key_idx;      // [n] original Gaussian index (goes into the sort key / radii)
+  const int32_t* sh_idx;       // [n] row of `sh` / `colors_precomp` / `cov3d_precomp` to read
+  const float* bounds;         // [ceil(n/256), 8] bounding data of each 256-item group (null = no group culling)
   int32_t sh_degree;
   int32_t M;
 };
@@ -101,7 +104,14 @@ struct gsw_ctx {
   int32_t num_slots = 0;
   int64_t Nm = 0;  // movable count
   gsw::GaussArrays scene{};
-  gsw::DevBuf mov_xyz, mov_scale_act, mov_opacity, mov_sh, mov_log_scale, mov_quat_raw, mov_slot, mov_idx, mov_pos;
+  gsw::DevBuf mov_xyz, mov_scale_act, mov_opacity, mov_sh, mov_log_scale, mov_quat_raw, mov_slot, mov_idx, mov_bounds;
+  // static layer: the Gaussians with slot < 0, re-ordered along a Morton curve so that 256-item groups are
+  // spatially compact (per-view frustum culling of whole groups); compact copies of the small arrays
+  int64_t Ns = 0;
+  gsw::DevBuf st_xyz, st_scale, st_quat, st_opacity, st_idx, st_bounds;
+  gsw::DevBuf pos_of;           // [N] original index -> position inside its layer (static or movable)
+  const int32_t* slot_orig = nullptr;  // caller's slot array (original order)
+  gsw::GaussArrays stat_layer{};
   bool have_scene = false;
   // rig constants (gsw_rig_set): sim->GS similarity, its inverse, per-link scan-pose inverses, objects
   struct {
@@ -119,7 +129,9 @@ struct gsw_ctx {
     bool valid = false;
     bool single = false;  // gsw_rasterize_forward launch (scene arrays are the caller's)
     int32_t V = 0, F = 0;
-    int64_t N = 0, Nm = 0;
+    int64_t N = 0, Ns = 0, Nm = 0;        // original count, static-layer items per view, movable items per frame
+    const int32_t* slot_orig = nullptr;   // null: every Gaussian is in the static layer
+    const int32_t* pos_of = nullptr;      // null: identity
     gsw::FrameGeom g{};
     gsw::GaussArrays stat{};
     const int32_t* frame_env = nullptr;
@@ -148,11 +160,11 @@ int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_
 int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s);
 int launch_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, float near_plane, uint8_t* out,
                         cudaStream_t s);
-int launch_gather_movable(const gsw_ctx* ctx, cudaStream_t s);
+int launch_gather_layers(const gsw_ctx* ctx, cudaStream_t s);  // compact static + movable copies, group bounds
 
 // binsort.cu
 int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s);
-int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t N, int64_t Nm, const FrameGeom& g,
+int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g,
                      int64_t cap, cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                        int64_t cap, cudaStream_t s);

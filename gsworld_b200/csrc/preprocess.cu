@@ -123,6 +123,7 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   float sc[3] = {0.f, 0.f, 0.f};
   float q[4] = {1.f, 0.f, 0.f, 0.f};
   const bool have_cov = (!DYN) && ga.cov3d_precomp != nullptr;
+  const int64_t big = ga.sh_idx ? (int64_t)ga.sh_idx[i] : i;  // row of the large per-Gaussian arrays
 
   if (DYN) {
     // ---- rigid transform of a movable Gaussian (gs_utils.py:283-385 order: scale, rotate, translate) ----
@@ -203,7 +204,7 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   float tr_sigma;  // trace of the 3D covariance >= its largest eigenvalue
   if (have_cov) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) c3[k] = ga.cov3d_precomp[6 * i + k];
+    for (int k = 0; k < 6; ++k) c3[k] = ga.cov3d_precomp[6 * big + k];
     tr_sigma = c3[0] + c3[3] + c3[5];
   } else {
     if (!DYN) {
@@ -302,16 +303,16 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   // ---- colour ----
   float rgb[3];
   if (!DYN && ga.colors_precomp != nullptr) {
-    rgb[0] = ga.colors_precomp[3 * i];
-    rgb[1] = ga.colors_precomp[3 * i + 1];
-    rgb[2] = ga.colors_precomp[3 * i + 2];
+    rgb[0] = ga.colors_precomp[3 * big];
+    rgb[1] = ga.colors_precomp[3 * big + 1];
+    rgb[2] = ga.colors_precomp[3 * big + 2];
   } else {
     float dx = p[0] - vs.cam[0], dy = p[1] - vs.cam[1], dz = p[2] - vs.cam[2];
     const float len = sqrtf(dx * dx + dy * dy + dz * dz);
     dx = dx / len;
     dy = dy / len;
     dz = dz / len;
-    const float* shp = ga.sh + (size_t)i * ga.M * 3;
+    const float* shp = ga.sh + (size_t)big * ga.M * 3;
     if (ga.M == 16 && ((reinterpret_cast<uintptr_t>(shp) & 15) == 0)) {
       float c[48];
       const float4* s4 = reinterpret_cast<const float4*>(shp);
@@ -359,6 +360,67 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
       for (int x = rc.x0; x < rc.x1; ++x)
         atomicAdd(&bin_count[(lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk], 1u);
   }
+}
+
+// ---- group-level frustum culling ----
+// Items are stored so that 256 consecutive ones are spatially compact (Morton order, see gsw_scene_set);
+// `b` = {cx, cy, cz, rho, sigma, smax, slot, -}: bounding sphere of the group's centres (scene frame, scan
+// pose for movable ones), sigma = max sqrt(trace(Sigma)) at scale_modifier 1, smax = largest raw scale,
+// slot = the group's single pose slot or -1.  Returns true when every item of the group is certain to end
+// with "no tile" in the exact path: either behind the near plane, or even the item-level radius bound
+// (see the conservative frustum cull in preprocess_item) cannot reach the tile grid.  The side-plane tests
+// assume the standard projection (w_clip = view depth, x_clip = x_view / tan); `proj_std` says whether the
+// view's matrices have that form.
+struct ViewCull {
+  float fx, fy, a, nzl, nzr, nzt, nzb;
+  int proj_std;
+};
+
+template <bool DYN>
+__device__ bool group_culled(const float* __restrict__ b, const ViewSmem& vs, const ViewCull& vc, const FrameGeom& g,
+                             const float* pose_s) {
+  float cx = b[0], cy = b[1], cz = b[2], rho = b[3], sigma = b[4];
+  if (DYN) {
+    const int slot = (int)b[6];
+    if (slot < 0) return false;  // group spans several links: no common transform
+    const float* ps = pose_s + slot * GSW_POSE_STRIDE;
+    float k = 1.0f;
+    if (ps[17] != 0.f) {  // object: positions scaled by kappa, scales go through u / (1 - u)
+      k = ps[16];
+      const float u = k * b[5];
+      if (!(u < 0.5f) || !(k > 0.f)) return false;
+      sigma = sigma * k / (1.0f - u);
+    }
+    const float x = k * cx, y = k * cy, z = k * cz;
+    cx = ps[0] * x + ps[1] * y + ps[2] * z + ps[9];
+    cy = ps[3] * x + ps[4] * y + ps[5] * z + ps[10];
+    cz = ps[6] * x + ps[7] * y + ps[8] * z + ps[11];
+    // |R|_2^2 <= Gershgorin bound of R^T R (1 for a rotation)
+    float rn = 0.f;
+    for (int a = 0; a < 3; ++a) {
+      float row = 0.f;
+      for (int c = 0; c < 3; ++c) row += fabsf(ps[a] * ps[c] + ps[3 + a] * ps[3 + c] + ps[6 + a] * ps[6 + c]);
+      rn = fmaxf(rn, row);
+    }
+    rho = rho * fabsf(k) * sqrtf(rn) * 1.001f;
+    sigma = sigma * sqrtf(rn) * 1.001f;
+  }
+  const float* V = vs.V;
+  const float vx = V[0] * cx + V[4] * cy + V[8] * cz + V[12];
+  const float vy = V[1] * cx + V[5] * cy + V[9] * cz + V[13];
+  const float vz = V[2] * cx + V[6] * cy + V[10] * cz + V[14];
+  const float wn = sqrtf(vs.wnorm);
+  const float r = rho * wn * 1.001f + 1e-4f * (1.0f + fabsf(vx) + fabsf(vy) + fabsf(vz));
+  if (vz + r <= g.near_plane) return true;  // whole sphere at or behind the near plane
+  if (!vc.proj_std) return false;
+  const float s = sigma * g.scale_modifier * vc.a * 1.01f;
+  if (!(s >= 0.f)) return false;
+  // left / right / top / bottom: linear in (x, z) resp. (y, z), maximised over the sphere
+  if (vc.fx * vx + vc.nzl * vz + r * sqrtf(vc.fx * vc.fx + vc.nzl * vc.nzl) + s < 0.f) return true;
+  if (vc.fx * vx - vc.nzr * vz - r * sqrtf(vc.fx * vc.fx + vc.nzr * vc.nzr) - s > 0.f) return true;
+  if (vc.fy * vy + vc.nzt * vz + r * sqrtf(vc.fy * vc.fy + vc.nzt * vc.nzt) + s < 0.f) return true;
+  if (vc.fy * vy - vc.nzb * vz - r * sqrtf(vc.fy * vc.fy + vc.nzb * vc.nzb) - s > 0.f) return true;
+  return false;
 }
 
 // ---- TMA bulk staging (cp.async.bulk + mbarrier): one elected thread pulls the CTA's contiguous slices of
@@ -426,25 +488,8 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
   float* q_s = DYN ? ls_s + 3 * IPB : sc_s + 3 * IPB;         // 16 B aligned: IPB multiple of 4
   float* op_s = q_s + 4 * IPB;
   int32_t* slot_s = reinterpret_cast<int32_t*>(op_s + IPB);
-  if (staged && threadIdx.x == 0) {
-    const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar_s);
-    mbar_init(mb, 1);
-    const bool want_slot = DYN || ga.slot != nullptr;
-    const uint32_t bytes = (uint32_t)IPB * ((DYN ? 56u : 44u) + (want_slot ? 4u : 0u));
-    mbar_expect_tx(mb, bytes);
-    auto sa = [](const void* p) { return (uint32_t)__cvta_generic_to_shared(p); };
-    bulk_g2s(sa(xyz_s), ga.xyz + 3 * base, IPB * 12, mb);
-    bulk_g2s(sa(sc_s), ga.scale_act + 3 * base, IPB * 12, mb);
-    if (DYN) {
-      bulk_g2s(sa(ls_s), ga.log_scale_raw + 3 * base, IPB * 12, mb);
-      bulk_g2s(sa(q_s), ga.quat_raw + 4 * base, IPB * 16, mb);
-      bulk_g2s(sa(slot_s), ga.mov_slot + base, IPB * 4, mb);
-    } else {
-      bulk_g2s(sa(q_s), ga.quat_act + 4 * base, IPB * 16, mb);
-      if (want_slot) bulk_g2s(sa(slot_s), ga.slot + base, IPB * 4, mb);
-    }
-    bulk_g2s(sa(op_s), ga.opacity + base, IPB * 4, mb);
-  }
+  __shared__ ViewCull vc;
+  __shared__ int grp_culled[IPT];
   if (threadIdx.x < 16) {
     vs.V[threadIdx.x] = views[view * 16 + threadIdx.x];
     vs.P[threadIdx.x] = projs[view * 16 + threadIdx.x];
@@ -466,6 +511,38 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
       best = fmaxf(best, row);
     }
     vs.wnorm = best * 1.001f;
+  } else if (threadIdx.x == 64) {  // constants of the group-level side-plane tests
+    const float* Vg = views + view * 16;
+    const float* Pg = projs + view * 16;
+    const float tanx = tanfov[view * 2], tany = tanfov[view * 2 + 1];
+    const float fx = (float)g.W / (2.0f * tanx), fy = (float)g.H / (2.0f * tany);
+    // standard projection: clip.w = view.z, clip.x = view.x / tanx, clip.y = view.y / tany  (transposed storage)
+    bool ok = true;
+    for (int k = 0; k < 4; ++k) {
+      const float tol = 1e-4f * (1.0f + fabsf(Vg[4 * k + 2]) + fabsf(Vg[4 * k]) + fabsf(Vg[4 * k + 1]));
+      ok = ok && fabsf(Pg[4 * k + 3] - Vg[4 * k + 2]) <= tol && fabsf(Pg[4 * k] * tanx - Vg[4 * k]) <= tol &&
+           fabsf(Pg[4 * k + 1] * tany - Vg[4 * k + 1]) <= tol;
+    }
+    float wn = 0.f;
+    {
+      float w[3][3];
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) w[r][c] = Vg[4 * c + r];
+      for (int a = 0; a < 3; ++a) {
+        float row = 0.f;
+        for (int b = 0; b < 3; ++b) row += fabsf(w[0][a] * w[0][b] + w[1][a] * w[1][b] + w[2][a] * w[2][b]);
+        wn = fmaxf(wn, row);
+      }
+    }
+    const float kj = fx * fx * (1.0f + 1.69f * tanx * tanx) + fy * fy * (1.0f + 1.69f * tany * tany);
+    vc.fx = fx;
+    vc.fy = fy;
+    vc.a = 3.0f * sqrtf(1.02f * kj * wn * 1.001f);
+    vc.nzl = 0.5f * (float)g.W + 6.0f;
+    vc.nzr = (float)(g.gx * kTile) - 0.5f * (float)g.W + 7.0f;
+    vc.nzt = 0.5f * (float)g.H + 6.0f;
+    vc.nzb = (float)(g.gy * kTile) - 0.5f * (float)g.H + 7.0f;
+    vc.proj_std = ok ? 1 : 0;
   }
   if (use_hist)
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
@@ -473,7 +550,46 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
       pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
   }
-  __syncthreads();  // mbarrier initialised, view / pose / histogram ready
+  __syncthreads();  // view / pose / histogram ready
+  if (threadIdx.x < IPT) {
+    const int64_t g0 = base + (int64_t)threadIdx.x * 256;
+    int c = 0;
+    if (g0 >= n_items) c = 1;
+    else if (ga.bounds != nullptr) c = group_culled<DYN>(ga.bounds + (g0 >> 8) * 8, vs, vc, g, pose_s) ? 1 : 0;
+    grp_culled[threadIdx.x] = c;
+  }
+  __syncthreads();
+  bool any_live = false;
+#pragma unroll
+  for (int it = 0; it < IPT; ++it) any_live = any_live || grp_culled[it] == 0;
+  if (!any_live) {  // nothing of this chunk can reach the image: mark every item "no tile" and leave
+#pragma unroll 1
+    for (int it = 0; it < IPT; ++it) {
+      const int64_t i = base + it * 256 + threadIdx.x;
+      if (i < n_items) rad[item_base + (int64_t)list * n_items + i] = 0;
+    }
+    return;
+  }
+  if (staged && threadIdx.x == 0) {
+    const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar_s);
+    mbar_init(mb, 1);
+    const bool want_slot = DYN || ga.slot != nullptr;
+    const uint32_t bytes = (uint32_t)IPB * ((DYN ? 56u : 44u) + (want_slot ? 4u : 0u));
+    mbar_expect_tx(mb, bytes);
+    auto sa = [](const void* p) { return (uint32_t)__cvta_generic_to_shared(p); };
+    bulk_g2s(sa(xyz_s), ga.xyz + 3 * base, IPB * 12, mb);
+    bulk_g2s(sa(sc_s), ga.scale_act + 3 * base, IPB * 12, mb);
+    if (DYN) {
+      bulk_g2s(sa(ls_s), ga.log_scale_raw + 3 * base, IPB * 12, mb);
+      bulk_g2s(sa(q_s), ga.quat_raw + 4 * base, IPB * 16, mb);
+      bulk_g2s(sa(slot_s), ga.mov_slot + base, IPB * 4, mb);
+    } else {
+      bulk_g2s(sa(q_s), ga.quat_act + 4 * base, IPB * 16, mb);
+      if (want_slot) bulk_g2s(sa(slot_s), ga.slot + base, IPB * 4, mb);
+    }
+    bulk_g2s(sa(op_s), ga.opacity + base, IPB * 4, mb);
+  }
+  if (staged) __syncthreads();  // mbarrier initialised before anyone waits on it
   GaussArrays la = ga;
   if (staged) {
     mbar_wait((uint32_t)__cvta_generic_to_shared(&mbar_s), 0);
@@ -494,12 +610,17 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     const int il = it * 256 + threadIdx.x;
     const int64_t i = base + il;
     if (i < n_items) {
+      const int64_t item = item_base + (int64_t)list * n_items + i;
+      if (grp_culled[it]) {
+        rad[item] = 0;
+        continue;
+      }
       if (TMA)
-        preprocess_item<DYN>(ga, la, i, staged ? (int64_t)il : i, item_base + (int64_t)list * n_items + i,
-                             list_base + list, g, vs, pose_s, recA, recB, recC, rad, bin_count, hist);
+        preprocess_item<DYN>(ga, la, i, staged ? (int64_t)il : i, item, list_base + list, g, vs, pose_s, recA, recB,
+                             recC, rad, bin_count, hist);
       else  // same object for both roles: every load stays a read-only global load
-        preprocess_item<DYN>(ga, ga, i, i, item_base + (int64_t)list * n_items + i, list_base + list, g, vs, pose_s,
-                             recA, recB, recC, rad, bin_count, hist);
+        preprocess_item<DYN>(ga, ga, i, i, item, list_base + list, g, vs, pose_s, recA, recB, recC, rad, bin_count,
+                             hist);
     }
   }
   if (use_hist) {
@@ -565,7 +686,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     const float4 a = recA[4 * item];
     const float depth = recC[4 * item].w;
     const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
-    const uint32_t idx = DYN ? (uint32_t)ga.mov_idx[i] : (uint32_t)i;
+    const uint32_t idx = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
     const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | idx;
     const uint32_t bk = depth_bucket(depth, g);
     for (int y = rc.y0; y < rc.y1; ++y)
@@ -581,20 +702,25 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   }
 }
 
+// Where the preprocess record of original Gaussian i lives for frame f (view v):
+// static layer item = v*Ns + pos, dynamic layer item = V*Ns + f*Nm + pos, pos = pos_of[i] (identity if null).
+__device__ __forceinline__ int64_t item_of(int64_t i, int32_t f, int32_t v, int32_t V, int64_t Ns, int64_t Nm,
+                                           const int32_t* slot, const int32_t* pos_of) {
+  const int64_t pos = pos_of ? (int64_t)pos_of[i] : i;
+  if (slot != nullptr && slot[i] >= 0) return (int64_t)V * Ns + (int64_t)f * Nm + pos;
+  return (int64_t)v * Ns + pos;
+}
+
 // Per-Gaussian taps of one frame, addressed by original index (parity tests / radii output).
-__global__ void frame_attrs_kernel(int64_t N, int64_t Nm, int32_t V, int32_t frame, const int32_t* frame_view,
-                                   const int32_t* slot, const int32_t* mov_pos, FrameGeom g,
+__global__ void frame_attrs_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V, int32_t frame,
+                                   const int32_t* frame_view, const int32_t* slot, const int32_t* pos_of, FrameGeom g,
                                    const float4* recA, const float4* recB, const float4* recC, const int32_t* rad,
                                    int32_t* radii, int32_t* tiles, float* depth, float* xy, float* conic_o,
                                    float* rgb) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int view = frame_view ? frame_view[frame] : 0;
-  int64_t item;
-  if (slot != nullptr && slot[i] >= 0)
-    item = (int64_t)V * N + (int64_t)frame * Nm + mov_pos[i];
-  else
-    item = (int64_t)view * N + i;
+  const int64_t item = item_of(i, frame, view, V, Ns, Nm, slot, pos_of);
   const int r = rad[item];
   float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
   int tt = 0;
@@ -621,18 +747,13 @@ __global__ void frame_attrs_kernel(int64_t N, int64_t Nm, int32_t V, int32_t fra
 }
 
 // radii of every frame: out[f, i]
-__global__ void radii_kernel(int64_t N, int64_t Nm, int32_t V, const int32_t* frame_view, const int32_t* slot,
-                             const int32_t* mov_pos, const int32_t* rad, int32_t* out) {
+__global__ void radii_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V, const int32_t* frame_view,
+                             const int32_t* slot, const int32_t* pos_of, const int32_t* rad, int32_t* out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int f = blockIdx.y;
   const int view = frame_view ? frame_view[f] : 0;
-  int64_t item;
-  if (slot != nullptr && slot[i] >= 0)
-    item = (int64_t)V * N + (int64_t)f * Nm + mov_pos[i];
-  else
-    item = (int64_t)view * N + i;
-  out[(int64_t)f * N + i] = rad[item];
+  out[(int64_t)f * N + i] = rad[item_of(i, f, view, V, Ns, Nm, slot, pos_of)];
 }
 
 __global__ void mark_visible_kernel(int32_t P, const float* xyz, const float* V, float near_plane, uint8_t* out) {
@@ -643,7 +764,20 @@ __global__ void mark_visible_kernel(int32_t P, const float* xyz, const float* V,
   out[i] = pvz > near_plane ? 1 : 0;
 }
 
-// compact copy of the movable Gaussians, made once per scene upload
+// compact, re-ordered copies of the two layers, made once per scene upload
+__global__ void gather_static_kernel(int64_t Ns, const int32_t* idx, GaussArrays sc, float* xyz, float* scale,
+                                     float* quat, float* opac) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= Ns) return;
+  const int64_t i = idx[j];
+  for (int k = 0; k < 3; ++k) {
+    xyz[3 * j + k] = sc.xyz[3 * i + k];
+    scale[3 * j + k] = sc.scale_act[3 * i + k];
+  }
+  for (int k = 0; k < 4; ++k) quat[4 * j + k] = sc.quat_act[4 * i + k];
+  opac[j] = sc.opacity[i];
+}
+
 __global__ void gather_movable_kernel(int64_t Nm, const int32_t* mov_idx, GaussArrays sc, float* xyz, float* scale,
                                       float* opac, float* sh, float* ls, float* qr, int32_t* mslot) {
   const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -658,6 +792,108 @@ __global__ void gather_movable_kernel(int64_t Nm, const int32_t* mov_idx, GaussA
   opac[m] = sc.opacity[i];
   for (int k = 0; k < 48; ++k) sh[48 * m + k] = sc.sh[48 * i + k];
   mslot[m] = sc.slot[i];
+}
+
+// One CTA (256 threads) per 256-item group of a layer's compact arrays: bounding sphere of the centres,
+// sigma = max sqrt(trace Sigma) (static: from the activated scale and quaternion; movable: sqrt(sum s^2),
+// the transformed quaternion is re-normalised), smax = largest scale, slot = the group's slot or -1.
+__global__ void __launch_bounds__(256)
+group_bounds_kernel(int64_t n, const float* __restrict__ xyz, const float* __restrict__ scale,
+                    const float* __restrict__ quat /*static only*/, const int32_t* __restrict__ mslot /*movable only*/,
+                    float* __restrict__ out) {
+  __shared__ float red[8][8];
+  __shared__ float cen[3];
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  const bool ok = i < n;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float p[3] = {0.f, 0.f, 0.f}, sig = 0.f, smax = 0.f;
+  int sl = -2;
+  if (ok) {
+    for (int k = 0; k < 3; ++k) p[k] = xyz[3 * i + k];
+    const float s0 = scale[3 * i], s1 = scale[3 * i + 1], s2 = scale[3 * i + 2];
+    smax = fmaxf(s0, fmaxf(s1, s2));
+    if (quat != nullptr) {
+      const float r = quat[4 * i], x = quat[4 * i + 1], y = quat[4 * i + 2], z = quat[4 * i + 3];
+      const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                             {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                             {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+      const float sc[3] = {s0, s1, s2};
+      float tr = 0.f;
+      for (int c = 0; c < 3; ++c)
+        for (int rr = 0; rr < 3; ++rr) tr += (sc[rr] * R[c][rr]) * (sc[rr] * R[c][rr]);
+      sig = sqrtf(tr);
+    } else {
+      sig = sqrtf(s0 * s0 + s1 * s1 + s2 * s2);
+    }
+    if (mslot != nullptr) sl = mslot[i];
+  }
+  // AABB -> centre
+  float mn[3], mx[3];
+  for (int k = 0; k < 3; ++k) {
+    mn[k] = ok ? p[k] : 3.0e38f;
+    mx[k] = ok ? p[k] : -3.0e38f;
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+      mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+    }
+  }
+  if (lane == 0)
+    for (int k = 0; k < 3; ++k) {
+      red[w][k] = mn[k];
+      red[w][3 + k] = mx[k];
+    }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float a = 3.0e38f, b = -3.0e38f;
+    for (int q = 0; q < 8; ++q) {
+      a = fminf(a, red[q][threadIdx.x]);
+      b = fmaxf(b, red[q][3 + threadIdx.x]);
+    }
+    cen[threadIdx.x] = 0.5f * (a + b);
+  }
+  __syncthreads();
+  float d = 0.f;
+  if (ok) {
+    const float dx = p[0] - cen[0], dy = p[1] - cen[1], dz = p[2] - cen[2];
+    d = sqrtf(dx * dx + dy * dy + dz * dz);
+  }
+  int smin = ok ? sl : 0x7fffffff, smaxi = ok ? sl : -0x7fffffff;
+  for (int o = 16; o > 0; o >>= 1) {
+    d = fmaxf(d, __shfl_xor_sync(0xffffffffu, d, o));
+    sig = fmaxf(sig, __shfl_xor_sync(0xffffffffu, sig, o));
+    smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, o));
+    smin = min(smin, __shfl_xor_sync(0xffffffffu, smin, o));
+    smaxi = max(smaxi, __shfl_xor_sync(0xffffffffu, smaxi, o));
+  }
+  __syncthreads();
+  if (lane == 0) {
+    red[w][0] = d;
+    red[w][1] = sig;
+    red[w][2] = smax;
+    red[w][3] = __int_as_float(smin);
+    red[w][4] = __int_as_float(smaxi);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float D = 0.f, S = 0.f, M = 0.f;
+    int a = 0x7fffffff, b = -0x7fffffff;
+    for (int q = 0; q < 8; ++q) {
+      D = fmaxf(D, red[q][0]);
+      S = fmaxf(S, red[q][1]);
+      M = fmaxf(M, red[q][2]);
+      a = min(a, __float_as_int(red[q][3]));
+      b = max(b, __float_as_int(red[q][4]));
+    }
+    float* o = out + (int64_t)blockIdx.x * 8;
+    o[0] = cen[0];
+    o[1] = cen[1];
+    o[2] = cen[2];
+    o[3] = D * 1.0001f + 1e-6f;
+    o[4] = S * 1.0001f;
+    o[5] = M * 1.0001f;
+    o[6] = (mslot != nullptr && a == b) ? (float)a : -1.0f;
+    o[7] = 0.f;
+  }
 }
 
 }  // namespace
@@ -758,9 +994,9 @@ int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_
   auto& w = ctx->ws;
   if (L.N <= 0) return 0;
   frame_attrs_kernel<<<(unsigned)((L.N + 255) / 256), 256, 0, s>>>(
-      L.N, L.Nm, L.V, frame, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(), L.g, w.rec.as<float4>(),
-      w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(), radii, tiles_touched, depth, xy, conic_opacity,
-      rgb);
+      L.N, L.Ns, L.Nm, L.V, frame, L.frame_view, L.slot_orig, L.pos_of, L.g, w.rec.as<float4>(),
+      w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(), radii, tiles_touched, depth, xy,
+      conic_opacity, rgb);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
@@ -771,8 +1007,8 @@ int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s) {
   auto& w = ctx->ws;
   if (L.N <= 0 || L.F <= 0) return 0;
   dim3 grid((unsigned)((L.N + 255) / 256), (unsigned)L.F);
-  radii_kernel<<<grid, 256, 0, s>>>(L.N, L.Nm, L.V, L.frame_view, L.stat.slot, ctx->mov_pos.as<int32_t>(),
-                                    w.rad.as<int32_t>(), out_radii);
+  radii_kernel<<<grid, 256, 0, s>>>(L.N, L.Ns, L.Nm, L.V, L.frame_view, L.slot_orig, L.pos_of, w.rad.as<int32_t>(),
+                                    out_radii);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
@@ -787,13 +1023,28 @@ int launch_mark_visible(int32_t P, const float* means3D, const float* viewmatrix
   return 0;
 }
 
-int launch_gather_movable(const gsw_ctx* ctx, cudaStream_t s) {
-  if (ctx->Nm <= 0) return 0;
-  gather_movable_kernel<<<(unsigned)((ctx->Nm + 255) / 256), 256, 0, s>>>(
-      ctx->Nm, ctx->mov_idx.as<int32_t>(), ctx->scene, ctx->mov_xyz.as<float>(), ctx->mov_scale_act.as<float>(),
-      ctx->mov_opacity.as<float>(), ctx->mov_sh.as<float>(), ctx->mov_log_scale.as<float>(),
-      ctx->mov_quat_raw.as<float>(), ctx->mov_slot.as<int32_t>());
-  count_launches(1);
+// `src` = the caller's scene arrays in original order (xyz, scale_act, quat_act, opacity, sh, raw arrays, slot)
+int launch_gather_layers(const gsw_ctx* ctx, cudaStream_t s) {
+  const GaussArrays& src = ctx->scene;
+  if (ctx->Ns > 0) {
+    const unsigned nb = (unsigned)((ctx->Ns + 255) / 256);
+    gather_static_kernel<<<nb, 256, 0, s>>>(ctx->Ns, ctx->st_idx.as<int32_t>(), src, ctx->st_xyz.as<float>(),
+                                            ctx->st_scale.as<float>(), ctx->st_quat.as<float>(),
+                                            ctx->st_opacity.as<float>());
+    group_bounds_kernel<<<nb, 256, 0, s>>>(ctx->Ns, ctx->st_xyz.as<float>(), ctx->st_scale.as<float>(),
+                                           ctx->st_quat.as<float>(), nullptr, ctx->st_bounds.as<float>());
+    count_launches(2);
+  }
+  if (ctx->Nm > 0) {
+    const unsigned nb = (unsigned)((ctx->Nm + 255) / 256);
+    gather_movable_kernel<<<nb, 256, 0, s>>>(ctx->Nm, ctx->mov_idx.as<int32_t>(), src, ctx->mov_xyz.as<float>(),
+                                             ctx->mov_scale_act.as<float>(), ctx->mov_opacity.as<float>(),
+                                             ctx->mov_sh.as<float>(), ctx->mov_log_scale.as<float>(),
+                                             ctx->mov_quat_raw.as<float>(), ctx->mov_slot.as<int32_t>());
+    group_bounds_kernel<<<nb, 256, 0, s>>>(ctx->Nm, ctx->mov_xyz.as<float>(), ctx->mov_scale_act.as<float>(), nullptr,
+                                           ctx->mov_slot.as<int32_t>(), ctx->mov_bounds.as<float>());
+    count_launches(2);
+  }
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
