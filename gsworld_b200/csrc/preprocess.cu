@@ -638,6 +638,11 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
 // stable (tile, depth) radix sort exactly (ties on depth fall back to ascending Gaussian index).
 // With use_hist the CTA first counts its own entries per bin in shared memory, reserves one contiguous
 // range per non-empty bin with a single global atomic, then hands out slots with shared-memory atomics.
+// Item handled by thread t in iteration it of a 2048-item chunk.  Items are spatially ordered, so the 256
+// items of a group fall into very few tile bins; letting the 32 lanes of a warp take 4 items from each of
+// the chunk's 8 groups (instead of 32 neighbours) cuts same-address shared-memory atomic conflicts 8-fold.
+__device__ __forceinline__ int scatter_slot(int it, int t) { return ((t & 7) << 8) | (it << 5) | (t >> 3); }
+
 template <bool DYN>
 __global__ void __launch_bounds__(256)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
@@ -656,7 +661,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     __syncthreads();
 #pragma unroll 1
     for (int it = 0; it < kItemsPerThread; ++it) {
-      const int64_t i = base + (int64_t)it * 256 + threadIdx.x;
+      const int64_t i = base + scatter_slot(it, threadIdx.x);
       if (i >= n_items) continue;
       const int64_t item = item_base + (int64_t)list * n_items + i;
       const int radius = rad[item];
@@ -678,7 +683,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   }
 #pragma unroll 1
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + (int64_t)it * 256 + threadIdx.x;
+    const int64_t i = base + scatter_slot(it, threadIdx.x);
     if (i >= n_items) continue;
     const int64_t item = item_base + (int64_t)list * n_items + i;
     const int radius = rad[item];
