@@ -51,9 +51,9 @@ def matrix_to_quaternion(m):
         torch.stack([m02 - m20, m10 + m01, q_abs[:, 2] ** 2, m12 + m21], -1),
         torch.stack([m10 - m01, m20 + m02, m21 + m12, q_abs[:, 3] ** 2], -1),
     ]
-    cand = torch.stack(rows, 1) / (2.0 * torch.maximum(q_abs, torch.tensor(0.1, dtype=q_abs.dtype))[..., None])
+    cand = torch.stack(rows, 1) / (2.0 * torch.maximum(q_abs, torch.tensor(0.1, dtype=q_abs.dtype, device=q_abs.device))[..., None])
     best = q_abs.argmax(-1)
-    return cand[torch.arange(m.shape[0]), best].reshape(b + (4,))
+    return cand[torch.arange(m.shape[0], device=m.device), best].reshape(b + (4,))
 
 
 def pose7_to_matrix(pose):
@@ -63,7 +63,7 @@ def pose7_to_matrix(pose):
     R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
                      2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
                      2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], -1).reshape(-1, 3, 3)
-    M = torch.eye(4, dtype=pose.dtype).repeat(pose.shape[0], 1, 1)
+    M = torch.eye(4, dtype=pose.dtype, device=pose.device).repeat(pose.shape[0], 1, 1)
     M[:, :3, :3] = R
     M[:, :3, 3] = p
     return M
@@ -82,7 +82,7 @@ def extract_rigid_transform(M):
     U, S, Vh = torch.linalg.svd(A)
     scales = S.mean(dim=1)
     R = U @ Vh
-    Mr = torch.eye(4, dtype=M.dtype).repeat(M.shape[0], 1, 1)
+    Mr = torch.eye(4, dtype=M.dtype, device=M.device).repeat(M.shape[0], 1, 1)
     Mr[:, :3, :3] = R
     Mr[:, :3, 3] = t
     return (Mr[0], scales[0], R[0], t[0]) if single else (Mr, scales, R, t)
@@ -143,13 +143,18 @@ class RefPath:
     """The reference wrapper's per-step logic over a duck-typed env (CPU torch)."""
 
     def __init__(self, env, scene, sim2gs_arm, link_labels, scan_link_mats, obj_sim2gs, obj_labels,
-                 obj_offset, obj_scale, xarm_offset=None):
+                 obj_offset, obj_scale, xarm_offset=None, device="cpu", rasterizer=None):
+        # device="cpu": the oracle.  device="cuda" + a GPU `rasterizer(cam, model) -> color (3,H,W) tensor`:
+        # the same statements on the device, used only by bench.py's restated-reference GPU comparison point.
         self.env = env
         self.num_envs = env.num_envs
         self.scene = scene
-        self.S = torch.as_tensor(sim2gs_arm, dtype=torch.float32)
+        self.device = torch.device(device)
+        self.rasterizer = rasterizer
+        self.S = torch.as_tensor(sim2gs_arm, dtype=torch.float32, device=self.device)
         self.gs_semantics = dict(link_labels)
-        self.gs_link_pose_mats = [torch.as_tensor(m, dtype=torch.float32).reshape(1, 4, 4) for m in scan_link_mats]
+        self.gs_link_pose_mats = [torch.as_tensor(m, dtype=torch.float32, device=self.device).reshape(1, 4, 4)
+                                  for m in scan_link_mats]
         self.obj_sim2gs, self.obj_labels = obj_sim2gs, obj_labels
         self.obj_offset, self.obj_scale = obj_offset, obj_scale
         self.xarm_offset = xarm_offset
@@ -160,7 +165,7 @@ class RefPath:
         """(B,L,4,4) S @ M_link @ inv(M_scan) @ inv(S)   (gs_world_wrapper.py:115-120)."""
         out = []
         for idx, link in enumerate(self.env.agent.robot.get_links()):
-            m = link.pose.to_transformation_matrix().to(torch.float32).cpu().clone()
+            m = link.pose.to_transformation_matrix().to(self.device, torch.float32).clone()
             if self.xarm_offset is not None:
                 for i in range(3):
                     m[:, i, 3] += self.xarm_offset[i]
@@ -174,11 +179,12 @@ class RefPath:
         for k in actors:
             if k not in self.obj_sim2gs:
                 continue
-            mat = pose7_to_matrix(actors[k][:, :7].to(torch.float32).cpu())
+            mat = pose7_to_matrix(actors[k][:, :7].to(self.device, torch.float32))
             if k in self.obj_offset:
                 for i in range(3):
                     mat[:, i, 3] += self.obj_offset[k][i]
-            full = self.S @ mat @ torch.linalg.inv(torch.as_tensor(self.obj_sim2gs[k], dtype=torch.float32))
+            full = self.S @ mat @ torch.linalg.inv(torch.as_tensor(self.obj_sim2gs[k], dtype=torch.float32,
+                                                                   device=self.device))
             rigid, scale, _, _ = extract_rigid_transform(full)
             out[k] = (rigid, scale * self.obj_scale[k])
         return out
@@ -188,7 +194,7 @@ class RefPath:
         sem = g._semantics.long().squeeze(-1)
         lt = self.link_transforms()
         for idx, link in enumerate(self.env.agent.robot.get_links()):
-            target = torch.as_tensor(self.gs_semantics[link.name]).long().reshape(-1)
+            target = torch.as_tensor(self.gs_semantics[link.name], device=sem.device).long().reshape(-1)
             mask = torch.isin(sem, target)
             self.gs_movable_pts[link.name] = transform_gaussians(
                 g, torch.where(mask)[0], None, lt[:, idx, :3, :3], lt[:, idx, :3, 3])
@@ -208,16 +214,16 @@ class RefPath:
             per_env = []
             for e in range(self.num_envs):
                 src = 0 if strict else e
-                ext = p["extrinsic_cv"][src].to(torch.float32).cpu()
-                K = p["intrinsic_cv"][src].to(torch.float32).cpu()
-                w2c = torch.vstack([ext, torch.tensor([0, 0, 0, 1], dtype=ext.dtype)])
+                ext = p["extrinsic_cv"][src].to(self.device, torch.float32)
+                K = p["intrinsic_cv"][src].to(self.device, torch.float32)
+                w2c = torch.vstack([ext, torch.tensor([0, 0, 0, 1], dtype=ext.dtype, device=ext.device)])
                 c2w = torch.linalg.inv(w2c)
                 fovx = 2 * torch.arctan(W / (2 * K[0, 0]))
                 fovy = 2 * torch.arctan(H / (2 * K[1, 1]))
                 c2w[:3, 3] = c2w[:3, 3] * self.scale_sim2real
                 real_w2c = torch.linalg.inv(self.rigid_sim2real @ c2w)
-                R = real_w2c[:3, :3].T.numpy()
-                T = real_w2c[:3, 3].numpy()
+                R = real_w2c[:3, :3].T.cpu().numpy()
+                T = real_w2c[:3, 3].cpu().numpy()
                 per_env.append(camera_tensors(R, T, float(fovx), float(fovy), H, W))
             out[cam] = per_env
         return out
@@ -232,7 +238,8 @@ class RefPath:
             for i in range(self.num_envs):
                 g = copy.deepcopy(self.scene)
                 for key, pts in self.gs_movable_pts.items():
-                    mask = torch.isin(base_sem, torch.as_tensor(self.gs_semantics[key]).long().reshape(-1))
+                    mask = torch.isin(base_sem, torch.as_tensor(self.gs_semantics[key],
+                                                                device=base_sem.device).long().reshape(-1))
                     if pts[0].shape[0] == self.num_envs:
                         g._xyz[mask] = pts[0][i]
                     if pts[1].shape[0] == self.num_envs:
@@ -241,10 +248,15 @@ class RefPath:
                         g._rotation[mask] = pts[2][i]
                     if pts[3].shape[0] == self.num_envs:
                         g._opacity[mask] = pts[3][i]
+                if self.rasterizer is not None:  # device path: render() + the wrapper's uint8 conversion in torch
+                    rendering = self.rasterizer(per_env[i], g).clamp(0, 1)
+                    gs_render = rendering.permute(1, 2, 0).unsqueeze(dim=0)
+                    frames.append((gs_render * 255).clamp(0, 255).to(torch.uint8))
+                    continue
                 r = render_ref(per_env[i], g)
                 frames.append(orc.to_uint8_hwc(np.clip(r["color"], 0.0, 1.0))[None])
                 auxes.append(r)
-            outs[cam] = np.concatenate(frames, 0)
+            outs[cam] = torch.vstack(frames) if self.rasterizer is not None else np.concatenate(frames, 0)
             aux[cam] = auxes
         return (outs, aux) if return_aux else outs
 
