@@ -59,7 +59,8 @@ class GSWorldWrapper(_Base):
                  device: Union[str, torch.device] = "cuda", log_state: bool = False,
                  state_log_path: str = "./exp_log", cam_randomization: bool = False, *, merged_model=None,
                  scan_link_mats=None, strict_reference: bool = True, engine: Optional[Engine] = None,
-                 fused_host: bool = True):
+                 fused_host: bool = True, cfg_dir: Optional[str] = None, asset_dir: Optional[str] = None,
+                 inv_depth_obs: bool = False):
         super().__init__(env)
         self.num_envs = env.num_envs
         self.robot_pipe = robot_pipe
@@ -79,10 +80,21 @@ class GSWorldWrapper(_Base):
         self.sim2gs_arm_trans = torch.tensor(rt.SIM2GS_ROBOT[fam], dtype=torch.float32, device=self.device)
         self.obj_gs_semantics = rt.OBJECT_LABELS
         self.rigid_sim2real, self.scale_sim2real, _, _ = extract_rigid_transform(self.sim2gs_arm_trans)
+        # True: also expose the rasterizer's inverse-depth image as obs['sensor_data'][cam]['inv_depth']
+        # (float32 (B,H,W,1)); the reference computes it (render()'s "depth") and drops it.
+        self.inv_depth_obs = inv_depth_obs
+        if merged_model is None and cfg_dir is not None:
+            # reference path: GaussianModelMerger().load_models_from_config(CFG_DIR/<name>.json) + merge_models()
+            # (gs_world_wrapper.py:75-79)
+            import os
+            from .gaussian_merger import GaussianModelMerger
+            merger = GaussianModelMerger(device=self.device, asset_dir=asset_dir)
+            merger.load_models_from_config(os.path.join(cfg_dir, f"{scene_gs_cfg_name}.json"))
+            merged_model = merger.merge_models()
         if merged_model is None or scan_link_mats is None:
             raise NotImplementedError(
-                "pass merged_model= (loaded Gaussians) and scan_link_mats= (link poses at the scan qpos); the PLY "
-                "merger and the ManiSkill scan-pose probe are outside this package's hot path")
+                "pass merged_model= (or cfg_dir= / asset_dir= for the PLY merger) and scan_link_mats= (link poses at "
+                "the scan qpos; the reference probes them through a second ManiSkill env, gs_world_wrapper.py:82-103)")
         self.initial_merger_robot = merged_model
         self.gs_link_pose_mats = [torch.as_tensor(m, dtype=torch.float32, device=self.device).reshape(1, 4, 4)
                                   for m in scan_link_mats]
@@ -320,26 +332,34 @@ class GSWorldWrapper(_Base):
             fe = self._maps(len(names))
             out = self._engine.render_frames(
                 self._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=self.num_envs, bg=(0.0, 0.0, 0.0),
-                antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True, finish=self.sync_each_step)
+                antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True, want_invdepth=self.inv_depth_obs,
+                finish=self.sync_each_step)
             rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
             for i, c in enumerate(names):
                 gs_renders[c] = rgb[i]
+            if self.inv_depth_obs:
+                inv = out["invdepth"].view(len(names), self.num_envs, H, W, 1)
+                self.last_inv_depth = {c: inv[i] for i, c in enumerate(names)}
         return {c: gs_renders[c] for c in cam_names}
 
     # ------------------------------------------------------------------ gym surface
     def step(self, action):
         obs, reward, terminated, truncated, info = self.env.step(action)
         self.transform_gs_perlink(self.initial_merger_robot)
-        for cam_name, gs_render in self._render_gsworld().items():
-            obs["sensor_data"][cam_name]["rgb"] = gs_render
+        self._write_obs(obs)
         return obs, reward, terminated, truncated, info
 
     def reset(self, *, seed=None, options=None):
         obs, info = self.env.reset(seed=seed, options=options)
         self.transform_gs_perlink(self.initial_merger_robot)
+        self._write_obs(obs)
+        return obs, info
+
+    def _write_obs(self, obs):
         for cam_name, gs_render in self._render_gsworld().items():
             obs["sensor_data"][cam_name]["rgb"] = gs_render
-        return obs, info
+            if self.inv_depth_obs:
+                obs["sensor_data"][cam_name]["inv_depth"] = self.last_inv_depth[cam_name]
 
     def render(self):
         return self.env.render()
@@ -354,6 +374,5 @@ class GSWorldWrapper(_Base):
         else:
             terminated = info["fail"].clone() if "fail" in info else torch.zeros(self.num_envs, dtype=bool,
                                                                                  device=self.device)
-        for cam_name, gs_render in self._render_gsworld().items():
-            obs["sensor_data"][cam_name]["rgb"] = gs_render
+        self._write_obs(obs)
         return obs, reward, terminated, torch.zeros(self.num_envs, dtype=bool, device=self.device), info
