@@ -22,7 +22,7 @@ class FramesDesc(C.Structure):
         ("pose", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
         ("tanfov", C.c_void_p), ("frame_env", C.c_void_p), ("frame_view", C.c_void_p),
         ("out_rgb_u8", C.c_void_p), ("out_color", C.c_void_p), ("out_invdepth", C.c_void_p),
-        ("out_radii", C.c_void_p),
+        ("out_radii", C.c_void_p), ("host_rgb_u8", C.c_void_p),
     ]
 
 

@@ -56,13 +56,14 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
 
 __global__ void __launch_bounds__(256)
 blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
+             int32_t f_begin,
              const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats, int64_t cap, FrameGeom g,
              float bg0, float bg1, float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8,
              float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status) {
   __shared__ float4 sRec[kChunk * 3];                  // staged records, 48 B each: {a, b, c}
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
   __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
-  const int64_t ft = blockIdx.x;
+  const int64_t ft = (int64_t)f_begin * g.T + blockIdx.x;
   const int f = (int)(ft / g.T), tile = (int)(ft % g.T);
   const int tx = tile % g.gx, ty = tile / g.gx;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -220,13 +221,14 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
 
 }  // namespace
 
-int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
-                 const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
-                 float* out_invdepth, cudaStream_t s) {
+// blends frames [f_begin, f_begin + F)
+int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view,
+                 int64_t cap, const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8,
+                 float* out_color, float* out_invdepth, cudaStream_t s) {
   const int64_t FT = (int64_t)F * g.T;
   if (FT <= 0) return 0;
   auto& w = ctx->ws;
-  blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, frame_view, V,
+  blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin,
                                             w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g,
                                             bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8,
                                             out_color, out_invdepth, w.status.as<long long>());

@@ -203,6 +203,9 @@ int gsw_create(int device, gsw_ctx** out) {
   cudaError_t e = cudaMallocHost((void**)&c->h_status, 8 * sizeof(int64_t));
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->done_evt, cudaEventDisableTiming);
   for (int k = 0; k <= kNumStages && e == cudaSuccess; ++k) e = cudaEventCreate(&c->stage_evt[k]);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->grp_evt[k], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->copy_evt, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_error("gsw_create: %s", cudaGetErrorString(e));
     delete c;
@@ -226,6 +229,10 @@ int gsw_destroy(gsw_ctx* c) {
   for (DevBuf* b : bufs) b->release();
   if (c->h_status) cudaFreeHost(c->h_status);
   if (c->done_evt) cudaEventDestroy(c->done_evt);
+  for (int k = 0; k < 4; ++k)
+    if (c->grp_evt[k]) cudaEventDestroy(c->grp_evt[k]);
+  if (c->copy_evt) cudaEventDestroy(c->copy_evt);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   for (int k = 0; k <= kNumStages; ++k)
     if (c->stage_evt[k]) cudaEventDestroy(c->stage_evt[k]);
   delete c;
@@ -438,9 +445,27 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                         d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s);
   if (rc) return rc;
   c->last.single = false;
-  if ((rc = launch_blend(c, d->num_views, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg, nullptr,
-                         d->out_rgb_u8, d->out_color, d->out_invdepth, s)))
+  if (d->host_rgb_u8 && d->out_rgb_u8) {
+    // blend in up to 4 frame groups; each group's uint8 frames go to the pinned host buffer on the copy stream
+    // as soon as that group is done, while the next group is being composited
+    const int G = d->num_frames < 4 ? d->num_frames : 4;
+    const size_t frame_bytes = (size_t)d->height * d->width * 3;
+    for (int k = 0; k < G; ++k) {
+      const int f0 = (int)((int64_t)d->num_frames * k / G), f1 = (int)((int64_t)d->num_frames * (k + 1) / G);
+      if ((rc = launch_blend(c, d->num_views, f0, f1 - f0, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
+                             nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, s)))
+        return rc;
+      GSW_CUDA(cudaEventRecord(c->grp_evt[k], s));
+      GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[k], 0));
+      GSW_CUDA(cudaMemcpyAsync(d->host_rgb_u8 + (size_t)f0 * frame_bytes, d->out_rgb_u8 + (size_t)f0 * frame_bytes,
+                               (size_t)(f1 - f0) * frame_bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+    GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
+    GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+  } else if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
+                                nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, s))) {
     return rc;
+  }
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (d->out_radii)
     if ((rc = launch_radii(c, d->out_radii, s))) return rc;
@@ -615,7 +640,7 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
                     nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend(c, 1, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
+  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
     return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (out_radii)
@@ -792,7 +817,7 @@ int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const 
                         fv, nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend(c, 1, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
+  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
     return rc;
   if (out_radii)
     if ((rc = launch_radii(c, out_radii, s))) return rc;

@@ -142,6 +142,9 @@ struct gsw_ctx {
   bool profile = false;         // record an event after every stage (gsw_profile_*)
   cudaEvent_t stage_evt[gsw::kNumStages + 1] = {};
   cudaEvent_t done_evt = nullptr;
+  cudaStream_t copy_stream = nullptr;  // device->host delivery of finished frame groups (host_rgb_u8)
+  cudaEvent_t grp_evt[4] = {};
+  cudaEvent_t copy_evt = nullptr;
   int64_t launches = 0;
 };
 
@@ -176,7 +179,7 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
                            float* view, float* proj, float* campos, float* tanfov, cudaStream_t s);
 
 // blend.cu
-int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
+int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
                  const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
                  float* out_invdepth, cudaStream_t s);
 

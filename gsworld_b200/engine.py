@@ -119,7 +119,7 @@ class Engine:
     def render_frames(self, pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view, H, W, *,
                       num_envs, bg=(0.0, 0.0, 0.0), antialiasing=False, scale_modifier=1.0, near=NEAR_GSWORLD,
                       out_rgb_u8=None, out_color=None, out_invdepth=None, out_radii=None, want_u8=True,
-                      want_color=False, want_invdepth=False, want_radii=False, finish=True):
+                      want_color=False, want_invdepth=False, want_radii=False, finish=True, host_rgb_u8=None):
         """Enqueue one batched transform+rasterize launch set.  Returns dict of output tensors.
 
         pose [B,S,20] fp32; viewmatrix/projmatrix [V,4,4]; campos [V,3]; tanfov [V,2];
@@ -137,6 +137,13 @@ class Engine:
             pose = _chk(pose.reshape(num_envs, self.num_slots, _lib.POSE_STRIDE), f32, "pose", d)
         if want_u8 and out_rgb_u8 is None:
             out_rgb_u8 = torch.empty((F, H, W, 3), dtype=torch.uint8, device=d)
+        elif out_rgb_u8 is not None:
+            # a device tensor, or pinned host memory (unified addressing: the kernel writes it over PCIe)
+            ok_dev = out_rgb_u8.device == d or (out_rgb_u8.device.type == "cpu" and out_rgb_u8.is_pinned())
+            if not ok_dev or out_rgb_u8.dtype != torch.uint8 or not out_rgb_u8.is_contiguous() \
+                    or out_rgb_u8.numel() != F * H * W * 3:
+                raise ValueError("out_rgb_u8 must be a contiguous uint8 (F,H,W,3) tensor on the device or in pinned "
+                                 "host memory")
         if want_color and out_color is None:
             out_color = torch.empty((F, 3, H, W), dtype=f32, device=d)
         if want_invdepth and out_invdepth is None:
@@ -156,6 +163,13 @@ class Engine:
         desc.out_color = None if out_color is None else out_color.data_ptr()
         desc.out_invdepth = None if out_invdepth is None else out_invdepth.data_ptr()
         desc.out_radii = None if out_radii is None else out_radii.data_ptr()
+        if host_rgb_u8 is not None:
+            if not (host_rgb_u8.device.type == "cpu" and host_rgb_u8.is_pinned() and host_rgb_u8.is_contiguous()
+                    and host_rgb_u8.dtype == torch.uint8 and host_rgb_u8.numel() == F * H * W * 3):
+                raise ValueError("host_rgb_u8 must be a contiguous pinned uint8 (F,H,W,3) host tensor")
+            desc.host_rgb_u8 = host_rgb_u8.data_ptr()
+        else:
+            desc.host_rgb_u8 = None
         self._last_inputs = (pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view)
         self._dbg_N = None
         for _attempt in range(4):

@@ -83,6 +83,13 @@ class GSWorldWrapper(_Base):
         # True: also expose the rasterizer's inverse-depth image as obs['sensor_data'][cam]['inv_depth']
         # (float32 (B,H,W,1)); the reference computes it (render()'s "depth") and drops it.
         self.inv_depth_obs = inv_depth_obs
+        # Optional caller-owned destination of the uint8 observations, shape (n_cams, B, H, W, 3): a device tensor,
+        # or a PINNED HOST tensor, in which case the blend kernel's epilogue writes the pixels straight into
+        # host memory over PCIe while later tiles are still being composited (no separate D2H copy).
+        self.obs_out = None
+        # Optional PINNED HOST tensor (n_cams, B, H, W, 3) uint8: the observations are also delivered there, copied
+        # group by group while later frames are still being blended (gsw_frames_desc.host_rgb_u8).
+        self.obs_host = None
         if merged_model is None and cfg_dir is not None:
             # reference path: GaussianModelMerger().load_models_from_config(CFG_DIR/<name>.json) + merge_models()
             # (gs_world_wrapper.py:75-79)
@@ -330,10 +337,15 @@ class GSWorldWrapper(_Base):
             H, W = self._sensor_hw(names[0])
             view, proj, campos, tanfov, fv = self._views(names)
             fe = self._maps(len(names))
+            dst = None
+            if self.obs_out is not None and len(groups) == 1:
+                dst = self.obs_out.view(len(names) * self.num_envs, H, W, 3)
             out = self._engine.render_frames(
                 self._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=self.num_envs, bg=(0.0, 0.0, 0.0),
                 antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True, want_invdepth=self.inv_depth_obs,
-                finish=self.sync_each_step)
+                out_rgb_u8=dst, finish=self.sync_each_step,
+                host_rgb_u8=None if (self.obs_host is None or len(groups) != 1) else
+                self.obs_host.view(len(names) * self.num_envs, H, W, 3))
             rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
             for i, c in enumerate(names):
                 gs_renders[c] = rgb[i]

@@ -97,6 +97,10 @@ typedef struct gsw_frames_desc {
   float* out_color;          /* [F,3,H,W] or NULL: un-clamped C + T*bg as the rasterizer returns it */
   float* out_invdepth;       /* [F,1,H,W] or NULL */
   int32_t* out_radii;        /* [F,N] or NULL */
+  uint8_t* host_rgb_u8;      /* HOST pinned [F,H,W,3] or NULL: needs out_rgb_u8; the frames are blended in up to 4
+                              * groups and each group is copied device->host on the context's copy stream as soon
+                              * as it is done, overlapping the copy with the blending of the next group.  `stream`
+                              * waits for the last copy, so synchronising `stream` makes the host buffer valid. */
 } gsw_frames_desc;
 
 /* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous. */

@@ -147,3 +147,19 @@ def test_wrapper_from_ply_config_and_inverse_depth_obs(tmp_path):
         assert torch.equal(o1["sensor_data"][cam]["rgb"], o2["sensor_data"][cam]["rgb"])
         d = o2["sensor_data"][cam]["inv_depth"]
         assert d.shape == (2, 48, 48, 1) and d.dtype == torch.float32 and float(d.min()) >= 0.0 and float(d.max()) > 0.0
+
+
+def test_host_delivery_matches_device_output():
+    """gsw_frames_desc.host_rgb_u8: the grouped blend + overlapped device->host copies must deliver exactly the
+    frames the single-launch path leaves on the device (also with a frame count that does not divide by 4)."""
+    scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", 3, (64, 48), ("006_mustard_bottle",), True)
+    obs, _ = wrap.reset(seed=5)
+    torch.cuda.synchronize()
+    want = {c: obs["sensor_data"][c]["rgb"].clone() for c in env.cameras}
+    pinned = torch.zeros((len(env.cameras), 3, 64, 48, 3), dtype=torch.uint8).pin_memory()
+    wrap.obs_host = pinned
+    out = wrap._render_gsworld()
+    torch.cuda.current_stream().synchronize()
+    for i, c in enumerate(env.cameras):
+        assert torch.equal(out[c].cpu(), want[c].cpu())
+        assert torch.equal(pinned[i], want[c].cpu())
