@@ -59,7 +59,13 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              int32_t f_begin,
              const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats, int64_t cap, FrameGeom g,
              float bg0, float bg1, float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8,
-             float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status) {
+             float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status,
+             int mode, const uint32_t* __restrict__ view_cnt, const uint8_t* __restrict__ st_u8,
+             const float* __restrict__ st_color, const float* __restrict__ st_invd) {
+  // mode 0: frames.  mode 1: "view pass": blockIdx enumerates (view, tile); renders the static list of every
+  // view that is shared by >= 2 frames into the st_* images (passed as out_*), once.  In mode 0 a tile whose
+  // frame has no dynamic entries there is then a plain copy of the view's tile: same list, same code, same
+  // bits, computed once instead of once per env.
   __shared__ float4 sRec[kChunk * 3];                  // staged records, 48 B each: {a, b, c}
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
   __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
@@ -73,15 +79,37 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   const float pxf = (float)px, pyf = (float)py;
   const float bx0 = (float)wx, bx1 = (float)(wx + 7), by0 = (float)wy, by1 = (float)(wy + 3);
 
-  const int v = frame_view ? frame_view[f] : 0;
+  const int v = mode == 1 ? f : (frame_view ? frame_view[f] : 0);
+  if (mode == 1 && view_cnt[v] < 2u) return;  // view used by a single frame: nothing to share
   const int64_t sb = ((int64_t)v * g.T + tile) * g.NB, db = ((int64_t)(V + f) * g.T + tile) * g.NB;
-  const uint32_t s0 = bin_off[sb], d0 = bin_off[db];
-  uint32_t ns = bin_off[sb + g.NB] - s0, nd = bin_off[db + g.NB] - d0;
+  const uint32_t s0 = bin_off[sb], d0 = mode == 1 ? 0u : bin_off[db];
+  uint32_t ns = bin_off[sb + g.NB] - s0, nd = mode == 1 ? 0u : bin_off[db + g.NB] - d0;
   const uint32_t D = bin_off[nbins];
   if ((int64_t)D > cap) ns = nd = 0;  // workspace overflow: lists are incomplete; the launch is flagged invalid
-  if (ft == 0 && threadIdx.x == 0) {
+  if (mode == 0 && ft == 0 && threadIdx.x == 0) {
     status[0] = (long long)D;
     if ((int64_t)D > cap) status[2] = 1;
+  }
+  if (mode == 0 && view_cnt != nullptr && nd == 0 && view_cnt[v] >= 2u) {  // static-only tile of a shared view
+    if (inside) {
+      const size_t HW = (size_t)g.H * g.W, pid = (size_t)py * g.W + px;
+      if (out_u8) {
+        const uint8_t* src = st_u8 + ((size_t)v * HW + pid) * 3;
+        uint8_t* o = out_u8 + ((size_t)f * HW + pid) * 3;
+        o[0] = src[0];
+        o[1] = src[1];
+        o[2] = src[2];
+      }
+      if (out_color) {
+        const float* src = st_color + (size_t)v * 3 * HW + pid;
+        float* o = out_color + (size_t)f * 3 * HW + pid;
+        o[0] = src[0];
+        o[HW] = src[HW];
+        o[2 * HW] = src[2 * HW];
+      }
+      if (out_invd) out_invd[(size_t)f * HW + pid] = st_invd[(size_t)v * HW + pid];
+    }
+    return;
   }
   const uint32_t total = ns + nd;
   uint32_t i0 = 0, j0 = 0;  // consumed from the static / dynamic stream (block-uniform)
@@ -219,19 +247,45 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   }
 }
 
+__global__ void count_view_frames_kernel(int32_t F, const int32_t* __restrict__ frame_view, uint32_t* view_cnt) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f < F) atomicAdd(&view_cnt[frame_view[f]], 1u);
+}
+
 }  // namespace
 
+// Static-tile sharing set-up: counts frames per view and renders the static-only image of every view that is
+// shared by >= 2 frames (mode 1).  Buffers live in the workspace; call before launch_blend when F > V.
+int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
+                           int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
+                           bool want_invd, cudaStream_t s) {
+  auto& w = ctx->ws;
+  GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
+  count_view_frames_kernel<<<(F + 255) / 256, 256, 0, s>>>(F, frame_view, w.view_cnt.as<uint32_t>());
+  blend_kernel<<<(unsigned)((int64_t)V * g.T), 256, 0, s>>>(
+      w.bin_off.as<uint32_t>(), nbins, frame_view, V, 0, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g,
+      bg[0], bg[1], bg[2], nullptr, want_u8 ? w.st_u8.as<uint8_t>() : nullptr,
+      want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,
+      w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr);
+  count_launches(2);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // blends frames [f_begin, f_begin + F)
+// `share`: the view pass ran for this launch set, static-only tiles of shared views are copied from it
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view,
                  int64_t cap, const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8,
-                 float* out_color, float* out_invdepth, cudaStream_t s) {
+                 float* out_color, float* out_invdepth, bool share, cudaStream_t s) {
   const int64_t FT = (int64_t)F * g.T;
   if (FT <= 0) return 0;
   auto& w = ctx->ws;
   blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin,
                                             w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g,
                                             bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8,
-                                            out_color, out_invdepth, w.status.as<long long>());
+                                            out_color, out_invdepth, w.status.as<long long>(), 0,
+                                            share ? w.view_cnt.as<uint32_t>() : nullptr, w.st_u8.as<uint8_t>(),
+                                            w.st_color.as<float>(), w.st_invd.as<float>());
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -222,7 +222,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
@@ -445,6 +445,21 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                         d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s);
   if (rc) return rc;
   c->last.single = false;
+  // static-tile sharing: when some view is looked through by several frames, its static-only tiles are
+  // composited once (view pass) and copied into every frame that has no movable Gaussian in that tile
+  const bool share = d->num_frames > d->num_views;
+  if (share) {
+    auto& w = c->ws;
+    const size_t HW = (size_t)d->height * d->width, Vn = (size_t)d->num_views;
+    if ((rc = w.view_cnt.reserve(Vn * 4)) || (rc = w.st_u8.reserve(Vn * HW * 3)) ||
+        (rc = w.st_color.reserve(d->out_color ? Vn * HW * 12 : 16)) ||
+        (rc = w.st_invd.reserve(d->out_invdepth ? Vn * HW * 4 : 16)))
+      return rc;
+    if ((rc = launch_blend_view_pass(c, d->num_views, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g,
+                                     d->bg, d->out_rgb_u8 != nullptr, d->out_color != nullptr,
+                                     d->out_invdepth != nullptr, s)))
+      return rc;
+  }
   if (d->host_rgb_u8 && d->out_rgb_u8) {
     // blend in up to 4 frame groups; each group's uint8 frames go to the pinned host buffer on the copy stream
     // as soon as that group is done, while the next group is being composited
@@ -453,7 +468,7 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     for (int k = 0; k < G; ++k) {
       const int f0 = (int)((int64_t)d->num_frames * k / G), f1 = (int)((int64_t)d->num_frames * (k + 1) / G);
       if ((rc = launch_blend(c, d->num_views, f0, f1 - f0, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
-                             nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, s)))
+                             nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, share, s)))
         return rc;
       GSW_CUDA(cudaEventRecord(c->grp_evt[k], s));
       GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[k], 0));
@@ -463,7 +478,7 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
     GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
   } else if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
-                                nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, s))) {
+                                nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, share, s))) {
     return rc;
   }
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
@@ -640,7 +655,7 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
                     nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
+  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, false, s)))
     return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (out_radii)
@@ -817,7 +832,7 @@ int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const 
                         fv, nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, s)))
+  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, false, s)))
     return rc;
   if (out_radii)
     if ((rc = launch_radii(c, out_radii, s))) return rc;

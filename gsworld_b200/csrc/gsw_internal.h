@@ -91,6 +91,7 @@ struct Workspace {
   DevBuf splats;  // Splat [cap_entries] blend records in the same order
   DevBuf merge_cnt, merge_off;  // u32 [T + 1] scratch of the debug list dump
   DevBuf seg_queue;             // Segment[]: depth sub-ranges of bins too large for one shared-memory sort
+  DevBuf view_cnt, st_u8, st_color, st_invd;  // frames per view; static-only image of each shared view
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -181,7 +182,10 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
 // blend.cu
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
                  const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
-                 float* out_invdepth, cudaStream_t s);
+                 float* out_invdepth, bool share, cudaStream_t s);
+int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
+                           int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
+                           bool want_invd, cudaStream_t s);
 
 size_t scan_tmp_elems(int64_t n);
 
