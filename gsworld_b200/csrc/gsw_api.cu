@@ -102,7 +102,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
               (long long)items);
     return GSW_E_INVALID;
   }
-  if (ctx->cap_entries == 0) ctx->cap_entries = items > (4 << 20) ? items : (4 << 20);
+  if (ctx->cap_entries == 0) ctx->cap_entries = items + items / 2 > (4 << 20) ? items + items / 2 : (4 << 20);
   if (ctx->cap_entries >= ((int64_t)1 << 32) - 1) ctx->cap_entries = ((int64_t)1 << 32) - 2;
   const int64_t cap = ctx->cap_entries;
   int rc;

@@ -190,7 +190,7 @@ class Engine:
         rc = self.lib.gsw_finish(self._h, C.byref(need), C.byref(stats))
         self.last_stats = dict(D=stats[0], staged=stats[1], cap=stats[2], launches=stats[3])
         if rc == _lib.GSW_E_CAPACITY:
-            self.reserve_entries(int(need.value * 1.25) + 1024)
+            self.reserve_entries(int(need.value * 1.5) + 1024)
             if raise_on_overflow:
                 _lib.check(rc)
             return False

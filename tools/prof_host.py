@@ -19,6 +19,10 @@ t=time.perf_counter()
 for _ in range(100): step()
 t1=time.perf_counter(); torch.cuda.synchronize(); t2=time.perf_counter()
 print(f"host issue {1e3*(t1-t)/100:.3f} ms/step, total {1e3*(t2-t)/100:.3f} ms/step")
+hs = []
+for _ in range(30):  # queue empty at every step: pure host cost of issuing one step
+    torch.cuda.synchronize(); a = time.perf_counter(); step(); hs.append(time.perf_counter() - a)
+hs.sort(); print(f"host cost of issuing one step with an empty queue: median {1e3*hs[len(hs)//2]:.3f} ms, min {1e3*hs[0]:.3f} ms")
 pr = cProfile.Profile(); pr.enable()
 for _ in range(100): step()
 pr.disable(); torch.cuda.synchronize()
