@@ -494,7 +494,8 @@ def run_ours(args):
             "preprocess_static": V * N_GAUSS * (12 + 12 + 16 + 4 + 4 + 4),
             "preprocess_dynamic": F * Nm * (12 + 12 + 12 + 16 + 4 + 4 + 4 + 4),
             "scatter": (V * N_GAUSS + F * Nm) * 4 + D * 8,
-            "sort": D * (8 + 8 + 48 + 48),
+            "sort": D * (8 + 8),
+            "gather": D * (8 + 4 + 64 + 48),
             "blend": R * 48 + F * H * W * 3,
         }
         ach = alg.get(dom, 0) / (stages[dom] * 1e-3) / 1e9 if stages[dom] > 0 else 0.0

@@ -542,8 +542,7 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
   auto& w = ctx->ws;
   constexpr size_t smem_m = (size_t)kSortSmemKeys * sizeof(unsigned long long);  // 32 KB
   constexpr size_t smem_s = (size_t)kSmallKeys * sizeof(unsigned long long);     // 8 KB
-  const int32_t bpl = g.T * g.NB;
-  const int32_t n_lists = (int32_t)(nbins / bpl);
+  (void)V; (void)Ns; (void)Nm; (void)g;
   // queue storage: [small: nbins][huge: nbins][medium: the rest]
   Queues Q;
   Segment* base = w.seg_queue.as<Segment>();
@@ -563,10 +562,21 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
                                                                         w.keys.as<unsigned long long>());
   sort_segments_kernel<kSmallKeys, 128><<<148 * 12, 128, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
                                                                       w.keys.as<unsigned long long>());
+  count_launches(4);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g, int64_t cap,
+                  cudaStream_t s) {
+  if (nbins <= 0) return 0;
+  auto& w = ctx->ws;
+  const int32_t bpl = g.T * g.NB;
+  const int32_t n_lists = (int32_t)(nbins / bpl);
   gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, Ns, Nm, bpl,
                                                 ctx->last.pos_of, w.keys.as<unsigned long long>(),
                                                 w.rec.as<float4>(), w.splats.as<Splat>(), cap);
-  count_launches(5);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

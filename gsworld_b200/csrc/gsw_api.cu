@@ -149,6 +149,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   ctx->last.pos_of = pos_of;  // the gather reads it
   if ((rc = launch_sort_bins(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
   mark(5);
+  if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
   mark(6);
 
   ctx->last.valid = true;

@@ -17,7 +17,7 @@ void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
 void count_launches(int n);  // bookkeeping for gsw_kernel_launches()
 
-constexpr int kNumStages = 8;  // preprocess_static, preprocess_dynamic, scan, scatter, sort, (unused), blend, radii
+constexpr int kNumStages = 8;  // preprocess_static, preprocess_dynamic, scan, scatter, sort (keys), gather, blend, radii
 
 #define GSW_CUDA(expr)                                                                   \
   do {                                                                                   \
@@ -170,6 +170,8 @@ int launch_gather_layers(const gsw_ctx* ctx, cudaStream_t s);  // compact static
 int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s);
 int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g,
                      int64_t cap, cudaStream_t s);
+int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g, int64_t cap,
+                  cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                        int64_t cap, cudaStream_t s);
 

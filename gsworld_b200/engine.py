@@ -236,7 +236,7 @@ class Engine:
         return out.bool()
 
     # -- measurement hooks --
-    STAGES = ("preprocess_static", "preprocess_dynamic", "scan", "scatter", "sort", "reserved", "blend", "radii")
+    STAGES = ("preprocess_static", "preprocess_dynamic", "scan", "scatter", "sort", "gather", "blend", "radii")
 
     def profile(self, on: bool):
         _lib.check(self.lib.gsw_profile_enable(self._h, int(bool(on))))

@@ -174,7 +174,7 @@ int gsw_compose_cameras(gsw_ctx* ctx, int n, const float* extrinsic_cv, const fl
 long long gsw_kernel_launches(void);
 /* With profiling on, every launch records a CUDA event after each stage on the launch stream;
  * gsw_profile_read waits for the last launch and returns the stage durations in ms, in the order
- * preprocess_static, preprocess_dynamic, scan, scatter, sort, (reserved), blend, radii (n >= 8). */
+ * preprocess_static, preprocess_dynamic, scan, scatter, sort (keys), gather, blend (incl. view pass), radii (n >= 8). */
 int gsw_profile_enable(gsw_ctx* ctx, int on);
 int gsw_profile_read(gsw_ctx* ctx, float* stage_ms, int n);
 
