@@ -163,3 +163,12 @@ def test_host_delivery_matches_device_output():
     for i, c in enumerate(env.cameras):
         assert torch.equal(out[c].cpu(), want[c].cpu())
         assert torch.equal(pinned[i], want[c].cpu())
+
+
+def test_cfg4_like_pour_mustard_objects_128():
+    # BASELINE config 4 shape at test size: fr3_umi, 128x128, 2 cameras, mustard bottle + bread slice
+    # (object_scale 0.95, 13x object frame: the kappa path of quirk Q4), per-env cameras
+    scene, env, wrap = _make("fr3_umi", "fr3_pour_mustard", 4, (128, 128), ("006_mustard_bottle", "bread_slice"),
+                             False, n_total=40_000, seed=17)
+    wrap.reset(seed=4)
+    _check_frames(scene, env, wrap, 128, 128)
