@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libgsw.so")
 POSE_STRIDE = 20
 
 GSW_E_CAPACITY = -3
+SEG_NONE = -2  # GSW_SEG_NONE
 
 
 class FramesDesc(C.Structure):
@@ -22,7 +23,7 @@ class FramesDesc(C.Structure):
         ("pose", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
         ("tanfov", C.c_void_p), ("frame_env", C.c_void_p), ("frame_view", C.c_void_p),
         ("out_rgb_u8", C.c_void_p), ("out_color", C.c_void_p), ("out_invdepth", C.c_void_p),
-        ("out_radii", C.c_void_p), ("host_rgb_u8", C.c_void_p),
+        ("out_radii", C.c_void_p), ("host_rgb_u8", C.c_void_p), ("out_seg", C.c_void_p),
     ]
 
 
@@ -34,6 +35,7 @@ SYMBOLS = {
     "gsw_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
     "gsw_destroy": (C.c_int, [_vp]),
     "gsw_scene_set": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]),
+    "gsw_scene_set_labels": (C.c_int, [_vp, _vp]),
     "gsw_render_frames": (C.c_int, [_vp, C.POINTER(FramesDesc), _vp]),
     "gsw_finish": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64 * 4)]),
     "gsw_reserve_entries": (C.c_int, [_vp, _i64]),

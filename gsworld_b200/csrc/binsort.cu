@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(256)
 gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t Ns,
                      int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ pos_of,
                      const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
-                     int64_t cap) {
+                     int64_t cap, const int32_t* __restrict__ labels, int32_t* __restrict__ lab_stream) {
   const uint32_t D = bin_off[nbins];
   if ((int64_t)D > cap) return;
   for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < D; p += gridDim.x * blockDim.x) {
@@ -269,6 +269,7 @@ gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_
     const int64_t pos = pos_of ? (int64_t)pos_of[idx] : (int64_t)idx;  // position inside the Gaussian's layer
     const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)(lo - V) * Nm + pos : (int64_t)lo * Ns + pos;
     splats[p] = make_splat(rec, item);
+    if (lab_stream != nullptr) lab_stream[p] = labels[idx];  // segmentation observation only
   }
 }
 
@@ -568,14 +569,15 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
 }
 
 int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g, int64_t cap,
-                  cudaStream_t s) {
+                  bool with_labels, cudaStream_t s) {
   if (nbins <= 0) return 0;
   auto& w = ctx->ws;
   const int32_t bpl = g.T * g.NB;
   const int32_t n_lists = (int32_t)(nbins / bpl);
   gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, Ns, Nm, bpl,
                                                 ctx->last.pos_of, w.keys.as<unsigned long long>(),
-                                                w.rec.as<float4>(), w.splats.as<Splat>(), cap);
+                                                w.rec.as<float4>(), w.splats.as<Splat>(), cap, ctx->labels,
+                                                with_labels ? w.lab_stream.as<int32_t>() : nullptr);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -54,6 +54,7 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
   asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v));
 }
 
+template <bool SEG>
 __global__ void __launch_bounds__(256)
 blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
              int32_t f_begin,
@@ -61,7 +62,10 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              float bg0, float bg1, float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8,
              float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status,
              int mode, const uint32_t* __restrict__ view_cnt, const uint8_t* __restrict__ st_u8,
-             const float* __restrict__ st_color, const float* __restrict__ st_invd) {
+             const float* __restrict__ st_color, const float* __restrict__ st_invd,
+             const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg, const int32_t* __restrict__ st_seg) {
+  // SEG: additionally reports, per pixel, the label of the Gaussian with the largest blending weight alpha*T
+  // (GSW_SEG_NONE where nothing was composited); lab_stream holds the label of every stream entry.
   // mode 0: frames.  mode 1: "view pass": blockIdx enumerates (view, tile); renders the static list of every
   // view that is shared by >= 2 frames into the st_* images (passed as out_*), once.  In mode 0 a tile whose
   // frame has no dynamic entries there is then a plain copy of the view's tile: same list, same code, same
@@ -69,6 +73,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   __shared__ float4 sRec[kChunk * 3];                  // staged records, 48 B each: {a, b, c}
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
   __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
+  __shared__ int32_t sLab[SEG ? kChunk : 1];
   const int64_t ft = (int64_t)f_begin * g.T + blockIdx.x;
   const int f = (int)(ft / g.T), tile = (int)(ft % g.T);
   const int tx = tile % g.gx, ty = tile / g.gx;
@@ -108,6 +113,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         o[2 * HW] = src[2 * HW];
       }
       if (out_invd) out_invd[(size_t)f * HW + pid] = st_invd[(size_t)v * HW + pid];
+      if (SEG && out_seg) out_seg[(size_t)f * HW + pid] = st_seg[(size_t)v * HW + pid];
     }
     return;
   }
@@ -120,6 +126,8 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   // Tacc is the transmittance used for accumulation; it is forced to 0 once the pixel has saturated so
   // that every later record fails the T test at once.  Tout keeps the value the reference writes out.
   float Tacc = inside ? 1.0f : 0.0f, Tout = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
+  float best_w = 0.f;
+  int32_t best_lab = GSW_SEG_NONE;
   uint32_t base = 0;
   for (; base < total; base += kChunk) {
     if (__syncthreads_and(Tacc == 0.0f)) break;  // also protects the staging buffers of the previous round
@@ -132,6 +140,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         sRec[3 * threadIdx.x] = __ldg(&sp->a);
         sRec[3 * threadIdx.x + 1] = __ldg(&sp->b);
         sRec[3 * threadIdx.x + 2] = __ldg(&sp->c);
+        if (SEG) sLab[threadIdx.x] = lab_stream[src + threadIdx.x];
       }
       if (rd == 0) i0 += n; else j0 += n;
     } else {  // merge-path over two key windows
@@ -149,10 +158,12 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         }
         const uint32_t a = lo, b = t - lo;
         take_s = a < ws && (b >= wd || kS[a] < kD[b]);
-        const Splat* sp = splats + (take_s ? s0 + i0 + a : d0 + j0 + b);
+        const uint32_t pos = take_s ? s0 + i0 + a : d0 + j0 + b;
+        const Splat* sp = splats + pos;
         sRec[3 * t] = __ldg(&sp->a);
         sRec[3 * t + 1] = __ldg(&sp->b);
         sRec[3 * t + 2] = __ldg(&sp->c);
+        if (SEG) sLab[t] = lab_stream[pos];
       }
       const uint32_t cs = (uint32_t)__syncthreads_count(take_s);
       i0 += cs;
@@ -196,7 +207,8 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
       const uint32_t kend = min(cnt, k0 + 16);
 #pragma unroll 4
       for (uint32_t k = k0; k < kend; ++k) {
-        const uint32_t ra = aRec + lds_u8(aQ + k) * 48;
+        const uint32_t qi = lds_u8(aQ + k);
+        const uint32_t ra = aRec + qi * 48;
         const float2 xy = lds64(ra);
         const float4 b = lds128(ra + 16);
         const float dx = xy.x - pxf, dy = xy.y - pyf;
@@ -215,6 +227,10 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         C1 += c.y * wgt;
         C2 += c.z * wgt;
         invd += c.w * wgt;
+        if (SEG && wgt > best_w) {
+          best_w = wgt;
+          best_lab = sLab[qi];
+        }
         Tacc = test_T;
         Tout = test_T;
       }
@@ -238,6 +254,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
       o[2 * HW] = b;
     }
     if (out_invd) out_invd[(size_t)f * HW + pid] = invd;
+    if (SEG && out_seg) out_seg[(size_t)f * HW + pid] = best_lab;
     if (out_u8) {
       uint8_t* o = out_u8 + ((size_t)f * HW + pid) * 3;
       o[0] = (uint8_t)(fminf(fmaxf(r, 0.f), 1.f) * 255.f);
@@ -258,15 +275,22 @@ __global__ void count_view_frames_kernel(int32_t F, const int32_t* __restrict__ 
 // shared by >= 2 frames (mode 1).  Buffers live in the workspace; call before launch_blend when F > V.
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
-                           bool want_invd, cudaStream_t s) {
+                           bool want_invd, bool want_seg, cudaStream_t s) {
   auto& w = ctx->ws;
   GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
   count_view_frames_kernel<<<(F + 255) / 256, 256, 0, s>>>(F, frame_view, w.view_cnt.as<uint32_t>());
-  blend_kernel<<<(unsigned)((int64_t)V * g.T), 256, 0, s>>>(
-      w.bin_off.as<uint32_t>(), nbins, frame_view, V, 0, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g,
-      bg[0], bg[1], bg[2], nullptr, want_u8 ? w.st_u8.as<uint8_t>() : nullptr,
-      want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,
-      w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr);
+#define GSW_VIEW_PASS(SEG_)                                                                                      \
+  blend_kernel<SEG_><<<(unsigned)((int64_t)V * g.T), 256, 0, s>>>(                                                 \
+      w.bin_off.as<uint32_t>(), nbins, frame_view, V, 0, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g, \
+      bg[0], bg[1], bg[2], nullptr, want_u8 ? w.st_u8.as<uint8_t>() : nullptr,                                      \
+      want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
+      w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
+      want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr)
+  if (want_seg)
+    GSW_VIEW_PASS(true);
+  else
+    GSW_VIEW_PASS(false);
+#undef GSW_VIEW_PASS
   count_launches(2);
   GSW_CUDA(cudaGetLastError());
   return 0;
@@ -276,16 +300,21 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
 // `share`: the view pass ran for this launch set, static-only tiles of shared views are copied from it
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view,
                  int64_t cap, const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8,
-                 float* out_color, float* out_invdepth, bool share, cudaStream_t s) {
+                 float* out_color, float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s) {
   const int64_t FT = (int64_t)F * g.T;
   if (FT <= 0) return 0;
   auto& w = ctx->ws;
-  blend_kernel<<<(unsigned)FT, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin,
-                                            w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g,
-                                            bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8,
-                                            out_color, out_invdepth, w.status.as<long long>(), 0,
-                                            share ? w.view_cnt.as<uint32_t>() : nullptr, w.st_u8.as<uint8_t>(),
-                                            w.st_color.as<float>(), w.st_invd.as<float>());
+#define GSW_BLEND(SEG_)                                                                                            \
+  blend_kernel<SEG_><<<(unsigned)FT, 256, 0, s>>>(                                                                   \
+      w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), \
+      cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
+      w.status.as<long long>(), 0, share ? w.view_cnt.as<uint32_t>() : nullptr, w.st_u8.as<uint8_t>(),                \
+      w.st_color.as<float>(), w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>())
+  if (out_seg)
+    GSW_BLEND(true);
+  else
+    GSW_BLEND(false);
+#undef GSW_BLEND
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -92,7 +92,7 @@ struct Guard {  // make ctx->device current for the duration of a call
 int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, const int32_t* slot_orig,
                  const int32_t* pos_of, const GaussArrays* dyn, int64_t Nm, int32_t V, int32_t F, const FrameGeom& g, const float* view, const float* proj, const float* campos,
                  const float* tanfov, const int32_t* frame_env, const int32_t* frame_view, const float* pose,
-                 int32_t num_slots, cudaStream_t s) {
+                 int32_t num_slots, cudaStream_t s, bool with_labels = false) {
   auto& w = ctx->ws;
   const int64_t items = (int64_t)V * Ns + (int64_t)F * Nm;  // N = original count (outputs), Ns = static-layer items
   const int64_t nbins = (int64_t)(V + F) * g.T * g.NB;
@@ -149,7 +149,8 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   ctx->last.pos_of = pos_of;  // the gather reads it
   if ((rc = launch_sort_bins(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
   mark(5);
-  if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
+  if (with_labels && (rc = w.lab_stream.reserve((size_t)cap * 4))) return rc;
+  if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, with_labels, s))) return rc;
   mark(6);
 
   ctx->last.valid = true;
@@ -223,7 +224,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
@@ -273,6 +274,7 @@ int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_ac
   c->scene.sh_degree = 3;
   c->scene.M = 16;
   c->slot_orig = c->scene.slot;
+  c->labels = nullptr;
   c->Nm = 0;
   c->Ns = 0;
   if (N == 0) {
@@ -385,6 +387,15 @@ int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_ac
   return GSW_OK;
 }
 
+int gsw_scene_set_labels(gsw_ctx* c, const int32_t* labels) {
+  if (!c) {
+    set_error("gsw_scene_set_labels: NULL ctx");
+    return GSW_E_INVALID;
+  }
+  c->labels = labels;
+  return GSW_OK;
+}
+
 int gsw_set_depth_buckets(gsw_ctx* c, int nb) {
   if (!c || nb < 0 || nb > 64 || (nb & (nb - 1))) {
     set_error("gsw_set_depth_buckets: nb must be 0 or a power of two <= 64");
@@ -410,6 +421,10 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   }
   if (!c->have_scene) {
     set_error("gsw_render_frames: call gsw_scene_set first");
+    return GSW_E_STATE;
+  }
+  if (d->out_seg && !c->labels) {
+    set_error("gsw_render_frames: out_seg needs per-Gaussian labels (gsw_scene_set_labels)");
     return GSW_E_STATE;
   }
   if (d->num_frames <= 0 || d->num_views <= 0 || d->num_envs <= 0 || d->height <= 0 || d->width <= 0 ||
@@ -443,7 +458,8 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
 
   int rc = run_pipeline(c, c->stat_layer, c->N, c->Ns, c->slot_orig, c->pos_of.as<int32_t>(), &dyn, c->Nm,
                         d->num_views, d->num_frames, g, d->viewmatrix,
-                        d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s);
+                        d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s,
+                        d->out_seg != nullptr);
   if (rc) return rc;
   c->last.single = false;
   // static-tile sharing: when some view is looked through by several frames, its static-only tiles are
@@ -454,11 +470,12 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     const size_t HW = (size_t)d->height * d->width, Vn = (size_t)d->num_views;
     if ((rc = w.view_cnt.reserve(Vn * 4)) || (rc = w.st_u8.reserve(Vn * HW * 3)) ||
         (rc = w.st_color.reserve(d->out_color ? Vn * HW * 12 : 16)) ||
-        (rc = w.st_invd.reserve(d->out_invdepth ? Vn * HW * 4 : 16)))
+        (rc = w.st_invd.reserve(d->out_invdepth ? Vn * HW * 4 : 16)) ||
+        (rc = w.st_seg.reserve(d->out_seg ? Vn * HW * 4 : 16)))
       return rc;
     if ((rc = launch_blend_view_pass(c, d->num_views, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g,
                                      d->bg, d->out_rgb_u8 != nullptr, d->out_color != nullptr,
-                                     d->out_invdepth != nullptr, s)))
+                                     d->out_invdepth != nullptr, d->out_seg != nullptr, s)))
       return rc;
   }
   if (d->host_rgb_u8 && d->out_rgb_u8) {
@@ -469,7 +486,7 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     for (int k = 0; k < G; ++k) {
       const int f0 = (int)((int64_t)d->num_frames * k / G), f1 = (int)((int64_t)d->num_frames * (k + 1) / G);
       if ((rc = launch_blend(c, d->num_views, f0, f1 - f0, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
-                             nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, share, s)))
+                             nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s)))
         return rc;
       GSW_CUDA(cudaEventRecord(c->grp_evt[k], s));
       GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[k], 0));
@@ -479,7 +496,7 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
     GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
   } else if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
-                                nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, share, s))) {
+                                nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s))) {
     return rc;
   }
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
@@ -656,7 +673,7 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
                     nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, false, s)))
+  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, nullptr, false, s)))
     return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[7], s);
   if (out_radii)
@@ -833,7 +850,7 @@ int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const 
                         fv, nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
-  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, false, s)))
+  if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, nullptr, false, s)))
     return rc;
   if (out_radii)
     if ((rc = launch_radii(c, out_radii, s))) return rc;

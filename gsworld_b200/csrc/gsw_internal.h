@@ -91,7 +91,8 @@ struct Workspace {
   DevBuf splats;  // Splat [cap_entries] blend records in the same order
   DevBuf merge_cnt, merge_off;  // u32 [T + 1] scratch of the debug list dump
   DevBuf seg_queue;             // Segment[]: depth sub-ranges of bins too large for one shared-memory sort
-  DevBuf view_cnt, st_u8, st_color, st_invd;  // frames per view; static-only image of each shared view
+  DevBuf view_cnt, st_u8, st_color, st_invd, st_seg;  // frames per view; static-only image of each shared view
+  DevBuf lab_stream;            // int32 [cap_entries]: label of every stream entry (segmentation observation only)
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -112,6 +113,7 @@ struct gsw_ctx {
   gsw::DevBuf st_xyz, st_scale, st_quat, st_opacity, st_idx, st_bounds;
   gsw::DevBuf pos_of;           // [N] original index -> position inside its layer (static or movable)
   const int32_t* slot_orig = nullptr;  // caller's slot array (original order)
+  const int32_t* labels = nullptr;     // caller's per-Gaussian labels (original order), gsw_scene_set_labels
   gsw::GaussArrays stat_layer{};
   bool have_scene = false;
   // rig constants (gsw_rig_set): sim->GS similarity, its inverse, per-link scan-pose inverses, objects
@@ -171,7 +173,7 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t*
 int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g,
                      int64_t cap, cudaStream_t s);
 int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g, int64_t cap,
-                  cudaStream_t s);
+                  bool with_labels, cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                        int64_t cap, cudaStream_t s);
 
@@ -184,10 +186,10 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
 // blend.cu
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
                  const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
-                 float* out_invdepth, bool share, cudaStream_t s);
+                 float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s);
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
-                           bool want_invd, cudaStream_t s);
+                           bool want_invd, bool want_seg, cudaStream_t s);
 
 size_t scan_tmp_elems(int64_t n);
 

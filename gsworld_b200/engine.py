@@ -80,6 +80,12 @@ class Engine:
                                           self._stream()))
         self.N, self.num_slots = N, int(num_slots)
 
+    def set_labels(self, labels):
+        """Per-Gaussian int32 labels (original order) for the segmentation output; kept alive here, used in place."""
+        labels = _chk(labels.reshape(self.N), torch.int32, "labels", self.device)
+        self._keep["labels"] = labels
+        _lib.check(self.lib.gsw_scene_set_labels(self._h, _ptr(labels)))
+
     def set_depth_buckets(self, nb: int):
         _lib.check(self.lib.gsw_set_depth_buckets(self._h, int(nb)))
 
@@ -119,7 +125,8 @@ class Engine:
     def render_frames(self, pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view, H, W, *,
                       num_envs, bg=(0.0, 0.0, 0.0), antialiasing=False, scale_modifier=1.0, near=NEAR_GSWORLD,
                       out_rgb_u8=None, out_color=None, out_invdepth=None, out_radii=None, want_u8=True,
-                      want_color=False, want_invdepth=False, want_radii=False, finish=True, host_rgb_u8=None):
+                      want_color=False, want_invdepth=False, want_radii=False, finish=True, host_rgb_u8=None,
+                      want_seg=False):
         """Enqueue one batched transform+rasterize launch set.  Returns dict of output tensors.
 
         pose [B,S,20] fp32; viewmatrix/projmatrix [V,4,4]; campos [V,3]; tanfov [V,2];
@@ -163,6 +170,8 @@ class Engine:
         desc.out_color = None if out_color is None else out_color.data_ptr()
         desc.out_invdepth = None if out_invdepth is None else out_invdepth.data_ptr()
         desc.out_radii = None if out_radii is None else out_radii.data_ptr()
+        out_seg = torch.empty((F, H, W), dtype=torch.int32, device=d) if want_seg else None
+        desc.out_seg = None if out_seg is None else out_seg.data_ptr()
         if host_rgb_u8 is not None:
             if not (host_rgb_u8.device.type == "cpu" and host_rgb_u8.is_pinned() and host_rgb_u8.is_contiguous()
                     and host_rgb_u8.dtype == torch.uint8 and host_rgb_u8.numel() == F * H * W * 3):
@@ -180,7 +189,7 @@ class Engine:
                 break
         else:
             raise _lib.GswError(_lib.GSW_E_CAPACITY, "tile-entry workspace kept overflowing")
-        return dict(rgb_u8=out_rgb_u8, color=out_color, invdepth=out_invdepth, radii=out_radii)
+        return dict(rgb_u8=out_rgb_u8, color=out_color, invdepth=out_invdepth, radii=out_radii, seg=out_seg)
 
     def finish(self, raise_on_overflow=True) -> bool:
         """Wait for the last launch.  Returns True if it was valid; on overflow grows the workspace

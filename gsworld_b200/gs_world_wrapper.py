@@ -60,7 +60,7 @@ class GSWorldWrapper(_Base):
                  state_log_path: str = "./exp_log", cam_randomization: bool = False, *, merged_model=None,
                  scan_link_mats=None, strict_reference: bool = True, engine: Optional[Engine] = None,
                  fused_host: bool = True, cfg_dir: Optional[str] = None, asset_dir: Optional[str] = None,
-                 inv_depth_obs: bool = False):
+                 inv_depth_obs: bool = False, segmentation_obs: bool = False):
         super().__init__(env)
         self.num_envs = env.num_envs
         self.robot_pipe = robot_pipe
@@ -83,6 +83,10 @@ class GSWorldWrapper(_Base):
         # True: also expose the rasterizer's inverse-depth image as obs['sensor_data'][cam]['inv_depth']
         # (float32 (B,H,W,1)); the reference computes it (render()'s "depth") and drops it.
         self.inv_depth_obs = inv_depth_obs
+        # True: obs['sensor_data'][cam]['segmentation'] = int32 (B,H,W,1), the scene label (link / object label,
+        # -1 background) of the Gaussian with the largest blending weight at each pixel, -2 where nothing was
+        # drawn.  Stands in for SAPIEN's segmentation image (Vulkan; unavailable here).  SURVEY.md §8(f) row 3.
+        self.segmentation_obs = segmentation_obs
         # Optional caller-owned destination of the uint8 observations, shape (n_cams, B, H, W, 3): a device tensor,
         # or a PINNED HOST tensor, in which case the blend kernel's epilogue writes the pixels straight into
         # host memory over PCIe while later tiles are still being composited (no separate D2H copy).
@@ -150,6 +154,8 @@ class GSWorldWrapper(_Base):
             f(g._xyz), f(torch.exp(g._scaling)), f(torch.nn.functional.normalize(g._rotation)),
             f(torch.sigmoid(g._opacity).reshape(-1)), f(torch.cat((g._features_dc, g._features_rest), dim=1)),
             f(g._scaling), f(g._rotation), slot.to(dev).contiguous(), self.num_slots)
+        if self.segmentation_obs:
+            self._engine.set_labels(sem.to(dev, torch.int32).contiguous())
         self._pose = torch.zeros((self.num_envs, self.num_slots, _lib.POSE_STRIDE), dtype=torch.float32, device=dev)
         self._frame_maps = {}
         self._engine.set_rig(
@@ -343,7 +349,7 @@ class GSWorldWrapper(_Base):
             out = self._engine.render_frames(
                 self._pose, view, proj, campos, tanfov, fe, fv, H, W, num_envs=self.num_envs, bg=(0.0, 0.0, 0.0),
                 antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True, want_invdepth=self.inv_depth_obs,
-                out_rgb_u8=dst, finish=self.sync_each_step,
+                want_seg=self.segmentation_obs, out_rgb_u8=dst, finish=self.sync_each_step,
                 host_rgb_u8=None if (self.obs_host is None or len(groups) != 1) else
                 self.obs_host.view(len(names) * self.num_envs, H, W, 3))
             rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
@@ -352,6 +358,9 @@ class GSWorldWrapper(_Base):
             if self.inv_depth_obs:
                 inv = out["invdepth"].view(len(names), self.num_envs, H, W, 1)
                 self.last_inv_depth = {c: inv[i] for i, c in enumerate(names)}
+            if self.segmentation_obs:
+                seg = out["seg"].view(len(names), self.num_envs, H, W, 1)
+                self.last_segmentation = {c: seg[i] for i, c in enumerate(names)}
         return {c: gs_renders[c] for c in cam_names}
 
     # ------------------------------------------------------------------ gym surface
@@ -372,6 +381,8 @@ class GSWorldWrapper(_Base):
             obs["sensor_data"][cam_name]["rgb"] = gs_render
             if self.inv_depth_obs:
                 obs["sensor_data"][cam_name]["inv_depth"] = self.last_inv_depth[cam_name]
+            if self.segmentation_obs:
+                obs["sensor_data"][cam_name]["segmentation"] = self.last_segmentation[cam_name]
 
     def render(self):
         return self.env.render()

@@ -56,6 +56,8 @@ extern "C" {
 
 /* floats per (env, slot) pose row: R[9] row-major, t[3], qR[4] wxyz, kappa, has_scale, pad[2] */
 #define GSW_POSE_STRIDE 20
+/* value of out_seg where no Gaussian was composited */
+#define GSW_SEG_NONE (-2)
 
 typedef struct gsw_ctx gsw_ctx;
 typedef void* gsw_stream; /* cudaStream_t */
@@ -76,6 +78,10 @@ int gsw_destroy(gsw_ctx* ctx);
 int gsw_scene_set(gsw_ctx* ctx, int64_t N, const float* xyz, const float* scale_act, const float* quat_act,
                   const float* opacity_act, const float* sh, const float* log_scale_raw, const float* quat_raw,
                   const int32_t* slot, int num_slots, gsw_stream stream);
+
+/* Optional per-Gaussian integer labels (device int32[N], original order, e.g. the scene's `_semantics`), used
+ * in place; needed only for gsw_frames_desc.out_seg.  Reset by gsw_scene_set. */
+int gsw_scene_set_labels(gsw_ctx* ctx, const int32_t* labels);
 
 typedef struct gsw_frames_desc {
   int32_t num_envs;   /* B */
@@ -101,6 +107,10 @@ typedef struct gsw_frames_desc {
                               * groups and each group is copied device->host on the context's copy stream as soon
                               * as it is done, overlapping the copy with the blending of the next group.  `stream`
                               * waits for the last copy, so synchronising `stream` makes the host buffer valid. */
+  int32_t* out_seg;          /* [F,H,W] or NULL: label (gsw_scene_set_labels) of the Gaussian with the largest blending
+                              * weight alpha*T at each pixel, GSW_SEG_NONE where nothing was composited.  No counterpart
+                              * in the reference (its segmentation comes from SAPIEN's Vulkan renderer, unavailable
+                              * here): SURVEY.md §8(f) row 3. */
 } gsw_frames_desc;
 
 /* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous. */

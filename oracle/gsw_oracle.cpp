@@ -285,7 +285,9 @@ void orc_transform_gaussians(int n, const float* xyz, const float* log_scale, co
 //   dbg_keys[cap] / dbg_vals[cap] (sorted, first D valid), dbg_ranges[T,2], dbg_ncontrib[H,W],
 //   dbg_final_T[H,W], dbg_fragile[H,W] (1 where a threshold decision was within `fragile_eps`
 //   relative distance of flipping: alpha vs 1/255, T vs 1e-4, power vs 0), dbg_pairs (count of
-//   blend-loop iterations = sum over pixels of entries visited).
+//   blend-loop iterations = sum over pixels of entries visited), dbg_best_id[H,W] / dbg_best_margin[H,W]
+//   (index of the Gaussian with the largest blending weight alpha*T, -1 if none, and how far ahead of the
+//   runner-up it is, relative; for the segmentation observation, which has no counterpart in the reference).
 // Returns D (number of tile duplicates), or -1 if dbg_keys capacity was too small.
 // near_plane: 0.05 for GSWorld (README.md:33); 0.2 upstream.
 // ---------------------------------------------------------------------------
@@ -299,7 +301,7 @@ long long orc_rasterize_forward(int P, int D_sh, int M, const float* bg, int W, 
                                 float* dbg_rgb, unsigned long long* dbg_keys, unsigned int* dbg_vals,
                                 long long dbg_cap, int* dbg_ranges, int* dbg_ncontrib, float* dbg_final_T,
                                 unsigned char* dbg_fragile, float fragile_eps, long long* dbg_pairs,
-                                int global_stable_sort) {
+                                int global_stable_sort, int* dbg_best_id, float* dbg_best_margin) {
   const int gx = (W + kTile - 1) / kTile, gy = (H + kTile - 1) / kTile;
   const int T = gx * gy;
   const float focal_y = (float)H / (2.0f * tan_fovy);
@@ -471,6 +473,9 @@ long long orc_rasterize_forward(int P, int D_sh, int M, const float* bg, int W, 
         float invd = 0.f;
         uint32_t contributor = 0, last = 0;
         unsigned char fragile = 0;
+        // segmentation tap (no counterpart in the reference): Gaussian with the largest blending weight alpha*T
+        float best_w = 0.f, second_w = 0.f;
+        int best_id = -1;
         for (int k = r0; k < r1; ++k) {
           ++contributor;
           const uint32_t id = svals[k];
@@ -487,6 +492,16 @@ long long orc_rasterize_forward(int P, int D_sh, int M, const float* bg, int W, 
           if (test_T < 0.0001f) break;  // `done = true` in the published kernel
           for (int ch = 0; ch < 3; ++ch) C[ch] += rgb[3 * (size_t)id + ch] * alpha * Tr;
           invd += (1 / depth[id]) * alpha * Tr;
+          {
+            const float wgt = alpha * Tr;
+            if (wgt > best_w) {
+              second_w = best_w;
+              best_w = wgt;
+              best_id = (int)id;
+            } else if (wgt > second_w) {
+              second_w = wgt;
+            }
+          }
           Tr = test_T;
           last = contributor;
         }
@@ -497,6 +512,8 @@ long long orc_rasterize_forward(int P, int D_sh, int M, const float* bg, int W, 
         if (dbg_ncontrib) dbg_ncontrib[pid] = (int)last;
         if (dbg_final_T) dbg_final_T[pid] = Tr;
         if (dbg_fragile) dbg_fragile[pid] = fragile;
+        if (dbg_best_id) dbg_best_id[pid] = best_id;
+        if (dbg_best_margin) dbg_best_margin[pid] = best_w > 0.f ? (best_w - second_w) / best_w : 1.0f;
       }
   }
 

@@ -116,7 +116,8 @@ def rasterize_forward(
             xy=np.zeros((P, 2), np.float32), conic_opacity=np.zeros((P, 4), np.float32),
             rgb=np.zeros((P, 3), np.float32), ranges=np.zeros((T, 2), np.int32),
             n_contrib=np.zeros((H, W), np.int32), final_T=np.zeros((H, W), np.float32),
-            fragile=np.zeros((H, W), np.uint8),
+            fragile=np.zeros((H, W), np.uint8), best_id=np.zeros((H, W), np.int32),
+            best_margin=np.zeros((H, W), np.float32),
         )
         cap = max(16, P * 16)
         dbg["keys"] = np.zeros((cap,), np.uint64)
@@ -132,7 +133,8 @@ def rasterize_forward(
             _p(dbg.get("tiles_touched")), _p(dbg.get("depth")), _p(dbg.get("xy")), _p(dbg.get("conic_opacity")),
             _p(dbg.get("rgb")), _p(dbg.get("keys")), _p(dbg.get("vals")), C.c_longlong(cap), _p(dbg.get("ranges")),
             _p(dbg.get("n_contrib")), _p(dbg.get("final_T")), _p(dbg.get("fragile")), C.c_float(fragile_eps),
-            C.byref(pairs), C.c_int(1 if global_stable_sort else 0),
+            C.byref(pairs), C.c_int(1 if global_stable_sort else 0), _p(dbg.get("best_id")),
+            _p(dbg.get("best_margin")),
         )
 
     D = call()

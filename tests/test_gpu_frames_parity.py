@@ -172,3 +172,43 @@ def test_cfg4_like_pour_mustard_objects_128():
                              False, n_total=40_000, seed=17)
     wrap.reset(seed=4)
     _check_frames(scene, env, wrap, 128, 128)
+
+
+@pytest.mark.parametrize("strict", [True, False], ids=["shared_views", "per_env_views"])
+def test_segmentation_observation_matches_oracle_argmax(strict):
+    """out_seg: label of the Gaussian with the largest blending weight.  Checked against the oracle's best_id on
+    every pixel that is neither threshold-fragile nor a near tie between the two largest weights."""
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200.gaussian_renderer import PipelineParams
+    from gsworld_b200.gs_world_wrapper import GSWorldWrapper
+    dev = torch.device("cuda:0")
+    objects = ("006_mustard_bottle", "snack_box")
+    scene = fx.make_scene(fx.SceneSpec(robot="fr3_umi", n_total=24_000, per_link=250, objects=objects, per_object=1200,
+                                       seed=23))
+    env = fx.FakeEnv("fr3_umi", num_envs=3, hw=(64, 64), objects=objects, seed=23, device=dev)
+    scan = fx.forward_kinematics("fr3_umi", fx.rt.ROBOT_SCAN_QPOS["fr3_umi"][None])[0]
+    wrap = GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene.to(dev),
+                          scan_link_mats=list(scan), strict_reference=strict, segmentation_obs=True)
+    obs, _ = wrap.reset(seed=7)
+    torch.cuda.synchronize()
+    labels = scene._semantics.reshape(-1).numpy().astype(np.int32)
+    pose = wrap._pose.cpu().numpy()
+    slot = wrap._engine._keep["slot"].cpu().numpy()
+    names = list(env.cameras)
+    view, proj, campos, tanfov, fv = wrap._views(names)
+    checked = 0
+    for ci, name in enumerate(names):
+        seg = obs["sensor_data"][name]["segmentation"]
+        assert seg.shape == (3, 64, 64, 1) and seg.dtype == torch.int32
+        for e in range(3):
+            v = int(fv[ci * 3 + e])
+            fin = oracle_frame_inputs(scene, slot, pose[e], 14)
+            want = orc.rasterize_forward(fin["xyz"], fin["opacities"], view[v].cpu().numpy(), proj[v].cpu().numpy(),
+                                         campos[v].cpu().numpy(), float(tanfov[v, 0]), float(tanfov[v, 1]), 64, 64,
+                                         shs=fin["shs"], scales=fin["scales"], rotations=fin["rotations"], debug=True)
+            exp = np.where(want["best_id"] >= 0, labels[np.maximum(want["best_id"], 0)], -2)
+            ok = (~want["fragile"].astype(bool)) & (want["best_margin"] > 1e-3)
+            got = seg[e, :, :, 0].cpu().numpy()
+            assert (got[ok] == exp[ok]).all()
+            checked += int(ok.sum())
+    assert checked > 0.9 * 2 * 3 * 64 * 64
