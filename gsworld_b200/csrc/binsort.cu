@@ -559,7 +559,7 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
                                                                       w.status.as<long long>());
   refine_big_bins_kernel<<<148 * 2, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
                                                  w.status.as<long long>());
-  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 6, 256, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
+  sort_segments_kernel<kSortSmemKeys, 512><<<148 * 3, 512, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
                                                                         w.keys.as<unsigned long long>());
   sort_segments_kernel<kSmallKeys, 128><<<148 * 12, 128, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
                                                                       w.keys.as<unsigned long long>());
