@@ -192,6 +192,17 @@ def traffic_of(stage):
         return None
 
 
+def hbm_roofline(stages, alg, peak):
+    """The largest HBM-facing stage (the dominant kernel, blend, is bound by the SM issue rate instead)."""
+    cands = {k: stages[k] for k in ("gather", "scatter", "preprocess_static", "preprocess_dynamic") if stages.get(k, 0) > 0}
+    if not cands:
+        return None
+    k = max(cands, key=cands.get)
+    ach = alg[k] / (stages[k] * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": k, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": traffic_of(k), "kernel_ms": stages[k]}
+
+
 def cpu_reference_sample(scene, n_envs, steps, warmup, strict=True):
     """The reference path on host cores: torch transform + per-frame deepcopy/isin + CPU rasterizer."""
     from gsworld_b200 import fixtures as fx
@@ -528,6 +539,7 @@ def run_ours(args):
                          "note": ("blend is bound by the SM issue rate (ncu: ~86 % issue-slot utilisation, <1 % DRAM), "
                                   "not by HBM; its HBM fraction is low by construction (profiles/README.md)")
                          if dom == "blend" else None},
+            "roofline_hbm_kernel": hbm_roofline(stages, alg, peak),
             "stages_ms": {k: round(v, 4) for k, v in stages.items()},
             "stage_gbs": {k: round(alg[k] / (stages[k] * 1e-3) / 1e9, 1) for k in alg if stages.get(k, 0) > 0},
             "counts": {"N": N_GAUSS, "movable": Nm, "D": D, "blend_staged": R},
