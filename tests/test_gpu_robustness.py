@@ -84,3 +84,29 @@ def test_invalid_arguments_are_rejected_with_messages():
     with pytest.raises(_lib.GswError, match="power of two"):
         eng.set_depth_buckets(3)
     eng.close()
+
+
+def test_very_large_image_uses_global_atomic_binning_path():
+    """20608 tiles: the per-CTA shared-memory tile histogram no longer fits, so counting/scatter fall back to
+    global atomics; results must not change."""
+    from gsworld_b200.engine import Engine
+    eng = Engine("cuda:0")
+    dev = eng.device
+    H, W = 2048, 2576
+    g = random_gaussians(3000, seed=77, log_scale_mean=np.log(0.03))
+    cam = look_at_camera(H, W, eye=(0.1, 0.2, -3.0))
+    want = orc.rasterize_forward(g["xyz"].numpy(), g["opacities"].numpy(), cam["view"].numpy(), cam["proj"].numpy(),
+                                 cam["campos"].numpy(), cam["tanfovx"], cam["tanfovy"], H, W, shs=g["shs"].numpy(),
+                                 scales=g["scales"].numpy(), rotations=g["rotations"].numpy(), debug=True)
+    color, radii, invd = eng.rasterize_forward(
+        g["xyz"].to(dev), g["opacities"].to(dev), cam["view"].to(dev), cam["proj"].to(dev), cam["campos"].to(dev),
+        cam["tanfovx"], cam["tanfovy"], H, W, torch.zeros(3, device=dev), shs=g["shs"].to(dev),
+        scales=g["scales"].to(dev), rotations=g["rotations"].to(dev))
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(radii.cpu().numpy(), want["radii"])
+    T = ((H + 15) // 16) * ((W + 15) // 16)
+    lists = eng.debug_frame_lists(0, T)
+    assert lists["D"] == want["D"]
+    np.testing.assert_array_equal(lists["vals"].cpu().numpy().view(np.uint32), want["vals"])
+    assert_image_close(color.cpu().numpy(), want["color"], want["fragile"].astype(bool))
+    eng.close()
