@@ -234,27 +234,17 @@ struct Segment {  // a slice of the key array that is sorted independently (a wh
   uint32_t start, count, bin, pad;
 };
 
-// Record gather for one entry: key -> per-item record (64 B slot) -> blend record.  The conic is pre-scaled
-// so the blend evaluates alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A,
-// B' = -log2(e) B, C' = -0.5 log2(e) C.
-__device__ __forceinline__ Splat make_splat(const float4* __restrict__ rec, int64_t item) {
-  constexpr float kLog2e = 1.4426950408889634f;
-  const float4 a = rec[4 * item], b = rec[4 * item + 1], c = rec[4 * item + 2];
-  Splat sp;
-  sp.a = a;
-  sp.b = make_float4(-0.5f * kLog2e * b.x, -kLog2e * b.y, -0.5f * kLog2e * b.z, b.w);
-  sp.c = make_float4(c.x, c.y, c.z, 1 / c.w);
-  return sp;
-}
-
 // One thread per tile entry, over the whole sorted key array: fully parallel random gather (two aligned
 // 32 B sectors per entry), coalesced key reads and splat writes.  The list an entry belongs to is found
 // by binary search over the V+F list boundaries (bin_off at multiples of bins_per_list).
+// Static lists of views that a single frame looks through are NOT materialised: typically only a quarter of
+// their entries is ever reached before the pixels saturate, so the blend fetches those records itself.
 __global__ void __launch_bounds__(256)
 gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t Ns,
                      int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ pos_of,
                      const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
-                     int64_t cap, const int32_t* __restrict__ labels, int32_t* __restrict__ lab_stream) {
+                     int64_t cap, const int32_t* __restrict__ labels, int32_t* __restrict__ lab_stream,
+                     const uint32_t* __restrict__ view_cnt) {
   const uint32_t D = bin_off[nbins];
   if ((int64_t)D > cap) return;
   for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < D; p += gridDim.x * blockDim.x) {
@@ -263,9 +253,10 @@ gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_
       const int mid = (lo + hi + 1) >> 1;
       if (bin_off[(int64_t)mid * bins_per_list] <= p) lo = mid; else hi = mid - 1;
     }
+    const bool dyn = lo >= V;
+    if (!dyn && view_cnt[lo] < 2u) continue;  // fetched lazily by the blend
     const u64 key = keys[p];
     const uint32_t idx = (uint32_t)(key & 0xffffffffull);
-    const bool dyn = lo >= V;
     const int64_t pos = pos_of ? (int64_t)pos_of[idx] : (int64_t)idx;  // position inside the Gaussian's layer
     const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)(lo - V) * Nm + pos : (int64_t)lo * Ns + pos;
     splats[p] = make_splat(rec, item);
@@ -577,7 +568,8 @@ int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int6
   gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, Ns, Nm, bpl,
                                                 ctx->last.pos_of, w.keys.as<unsigned long long>(),
                                                 w.rec.as<float4>(), w.splats.as<Splat>(), cap, ctx->labels,
-                                                with_labels ? w.lab_stream.as<int32_t>() : nullptr);
+                                                with_labels ? w.lab_stream.as<int32_t>() : nullptr,
+                                                w.view_cnt.as<uint32_t>());
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

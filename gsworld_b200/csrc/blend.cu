@@ -63,7 +63,12 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              float* __restrict__ out_color, float* __restrict__ out_invd, long long* __restrict__ status,
              int mode, const uint32_t* __restrict__ view_cnt, const uint8_t* __restrict__ st_u8,
              const float* __restrict__ st_color, const float* __restrict__ st_invd,
-             const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg, const int32_t* __restrict__ st_seg) {
+             const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg, const int32_t* __restrict__ st_seg,
+             int use_view_images, const float4* __restrict__ rec, const int32_t* __restrict__ pos_of, int64_t Ns,
+             const int32_t* __restrict__ labels) {
+  // A static list whose view is looked through by one frame only is not materialised as a splat stream
+  // (gather_splats_kernel skips it): this kernel then fetches the records of the entries it actually reaches
+  // from the per-item records through the sorted keys ("lazy" stream A).
   // SEG: additionally reports, per pixel, the label of the Gaussian with the largest blending weight alpha*T
   // (GSW_SEG_NONE where nothing was composited); lab_stream holds the label of every stream entry.
   // mode 0: frames.  mode 1: "view pass": blockIdx enumerates (view, tile); renders the static list of every
@@ -95,7 +100,8 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     status[0] = (long long)D;
     if ((int64_t)D > cap) status[2] = 1;
   }
-  if (mode == 0 && view_cnt != nullptr && nd == 0 && view_cnt[v] >= 2u) {  // static-only tile of a shared view
+  const bool lazyA = mode == 0 && view_cnt[v] < 2u;
+  if (mode == 0 && use_view_images && nd == 0 && view_cnt[v] >= 2u) {  // static-only tile of a shared view
     if (inside) {
       const size_t HW = (size_t)g.H * g.W, pid = (size_t)py * g.W + px;
       if (out_u8) {
@@ -136,11 +142,20 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     if (rs == 0 || rd == 0) {  // single-stream chunk
       const uint32_t src = rd == 0 ? s0 + i0 : d0 + j0;
       if (threadIdx.x < n) {
-        const Splat* sp = splats + src + threadIdx.x;
-        sRec[3 * threadIdx.x] = __ldg(&sp->a);
-        sRec[3 * threadIdx.x + 1] = __ldg(&sp->b);
-        sRec[3 * threadIdx.x + 2] = __ldg(&sp->c);
-        if (SEG) sLab[threadIdx.x] = lab_stream[src + threadIdx.x];
+        if (rd == 0 && lazyA) {
+          const uint32_t idx = (uint32_t)(keys[src + threadIdx.x] & 0xffffffffull);
+          const Splat sp = make_splat(rec, (int64_t)v * Ns + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
+          sRec[3 * threadIdx.x] = sp.a;
+          sRec[3 * threadIdx.x + 1] = sp.b;
+          sRec[3 * threadIdx.x + 2] = sp.c;
+          if (SEG) sLab[threadIdx.x] = labels[idx];
+        } else {
+          const Splat* sp = splats + src + threadIdx.x;
+          sRec[3 * threadIdx.x] = __ldg(&sp->a);
+          sRec[3 * threadIdx.x + 1] = __ldg(&sp->b);
+          sRec[3 * threadIdx.x + 2] = __ldg(&sp->c);
+          if (SEG) sLab[threadIdx.x] = lab_stream[src + threadIdx.x];
+        }
       }
       if (rd == 0) i0 += n; else j0 += n;
     } else {  // merge-path over two key windows
@@ -159,11 +174,20 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         const uint32_t a = lo, b = t - lo;
         take_s = a < ws && (b >= wd || kS[a] < kD[b]);
         const uint32_t pos = take_s ? s0 + i0 + a : d0 + j0 + b;
-        const Splat* sp = splats + pos;
-        sRec[3 * t] = __ldg(&sp->a);
-        sRec[3 * t + 1] = __ldg(&sp->b);
-        sRec[3 * t + 2] = __ldg(&sp->c);
-        if (SEG) sLab[t] = lab_stream[pos];
+        if (take_s && lazyA) {
+          const uint32_t idx = (uint32_t)(kS[a] & 0xffffffffull);
+          const Splat sp = make_splat(rec, (int64_t)v * Ns + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
+          sRec[3 * t] = sp.a;
+          sRec[3 * t + 1] = sp.b;
+          sRec[3 * t + 2] = sp.c;
+          if (SEG) sLab[t] = labels[idx];
+        } else {
+          const Splat* sp = splats + pos;
+          sRec[3 * t] = __ldg(&sp->a);
+          sRec[3 * t + 1] = __ldg(&sp->b);
+          sRec[3 * t + 2] = __ldg(&sp->c);
+          if (SEG) sLab[t] = lab_stream[pos];
+        }
       }
       const uint32_t cs = (uint32_t)__syncthreads_count(take_s);
       i0 += cs;
@@ -273,25 +297,36 @@ __global__ void count_view_frames_kernel(int32_t F, const int32_t* __restrict__ 
 
 // Static-tile sharing set-up: counts frames per view and renders the static-only image of every view that is
 // shared by >= 2 frames (mode 1).  Buffers live in the workspace; call before launch_blend when F > V.
+// frames per view (view_cnt): decides which static lists are shared (materialised once, tiles re-used) and
+// which are private to one frame (fetched lazily by the blend)
+int launch_count_views(const gsw_ctx* ctx, int32_t V, int32_t F, const int32_t* frame_view, cudaStream_t s) {
+  auto& w = ctx->ws;
+  GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
+  count_view_frames_kernel<<<(F + 255) / 256, 256, 0, s>>>(F, frame_view, w.view_cnt.as<uint32_t>());
+  count_launches(1);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
                            bool want_invd, bool want_seg, cudaStream_t s) {
   auto& w = ctx->ws;
-  GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
-  count_view_frames_kernel<<<(F + 255) / 256, 256, 0, s>>>(F, frame_view, w.view_cnt.as<uint32_t>());
+  (void)F;
 #define GSW_VIEW_PASS(SEG_)                                                                                      \
   blend_kernel<SEG_><<<(unsigned)((int64_t)V * g.T), 256, 0, s>>>(                                                 \
       w.bin_off.as<uint32_t>(), nbins, frame_view, V, 0, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g, \
       bg[0], bg[1], bg[2], nullptr, want_u8 ? w.st_u8.as<uint8_t>() : nullptr,                                      \
       want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
       w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
-      want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr)
+      want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr, 0, w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns,    \
+      ctx->labels)
   if (want_seg)
     GSW_VIEW_PASS(true);
   else
     GSW_VIEW_PASS(false);
 #undef GSW_VIEW_PASS
-  count_launches(2);
+  count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
@@ -308,8 +343,9 @@ int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int6
   blend_kernel<SEG_><<<(unsigned)FT, 256, 0, s>>>(                                                                   \
       w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), \
       cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
-      w.status.as<long long>(), 0, share ? w.view_cnt.as<uint32_t>() : nullptr, w.st_u8.as<uint8_t>(),                \
-      w.st_color.as<float>(), w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>())
+      w.status.as<long long>(), 0, w.view_cnt.as<uint32_t>(), w.st_u8.as<uint8_t>(), w.st_color.as<float>(),          \
+      w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>(), share ? 1 : 0,              \
+      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels)
   if (out_seg)
     GSW_BLEND(true);
   else

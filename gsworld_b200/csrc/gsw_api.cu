@@ -146,6 +146,8 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if (dyn && Nm > 0)
     if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, s))) return rc;
   mark(4);
+  if ((rc = w.view_cnt.reserve((size_t)V * 4 + 16))) return rc;
+  if ((rc = launch_count_views(ctx, V, F, frame_view, s))) return rc;
   ctx->last.pos_of = pos_of;  // the gather reads it
   if ((rc = launch_sort_bins(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
   mark(5);
@@ -468,7 +470,7 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   if (share) {
     auto& w = c->ws;
     const size_t HW = (size_t)d->height * d->width, Vn = (size_t)d->num_views;
-    if ((rc = w.view_cnt.reserve(Vn * 4)) || (rc = w.st_u8.reserve(Vn * HW * 3)) ||
+    if ((rc = w.st_u8.reserve(Vn * HW * 3)) ||
         (rc = w.st_color.reserve(d->out_color ? Vn * HW * 12 : 16)) ||
         (rc = w.st_invd.reserve(d->out_invdepth ? Vn * HW * 4 : 16)) ||
         (rc = w.st_seg.reserve(d->out_seg ? Vn * HW * 4 : 16)))
@@ -756,6 +758,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.status, 64);
   carve(w.seg_queue, (size_t)(2 * (kNaMaxEntries / kSortSmemKeys) + 3 * nbins + 16) * 16);
   carve(w.cam, 64);
+  carve(w.view_cnt, 64);  // one view
   if (off > kNaBytes) {
     set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);
     return GSW_E_NOMEM;

@@ -46,6 +46,22 @@ struct Splat {
   float4 a, b, c;
 };
 
+#ifdef __CUDACC__
+// Preprocess record (64 B item slot {px,py,hx,hy | conic,opacity | r,g,b,depth}) -> blend record.  The conic is
+// pre-scaled so the blend evaluates alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A,
+// B' = -log2(e) B, C' = -0.5 log2(e) C.  Used by the gather kernel and by the blend's own (lazy) fetch, so both
+// produce the same bits.
+__device__ __forceinline__ Splat make_splat(const float4* __restrict__ rec, int64_t item) {
+  constexpr float kLog2e = 1.4426950408889634f;
+  const float4 a = rec[4 * item], b = rec[4 * item + 1], c = rec[4 * item + 2];
+  Splat sp;
+  sp.a = a;
+  sp.b = make_float4(-0.5f * kLog2e * b.x, -kLog2e * b.y, -0.5f * kLog2e * b.z, b.w);
+  sp.c = make_float4(c.x, c.y, c.z, 1 / c.w);
+  return sp;
+}
+#endif
+
 // Inputs of one preprocess "layer" launch.
 struct GaussArrays {
   const float* xyz;            // [n,3]
@@ -187,6 +203,7 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
                  const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
                  float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s);
+int launch_count_views(const gsw_ctx* ctx, int32_t V, int32_t F, const int32_t* frame_view, cudaStream_t s);
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
                            bool want_invd, bool want_seg, cudaStream_t s);
