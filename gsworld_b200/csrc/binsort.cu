@@ -237,28 +237,28 @@ struct Segment {  // a slice of the key array that is sorted independently (a wh
 // One thread per tile entry, over the whole sorted key array: fully parallel random gather (two aligned
 // 32 B sectors per entry), coalesced key reads and splat writes.  The list an entry belongs to is found
 // by binary search over the V+F list boundaries (bin_off at multiples of bins_per_list).
-// Static lists of views that a single frame looks through are NOT materialised: typically only a quarter of
-// their entries is ever reached before the pixels saturate, so the blend fetches those records itself.
+// Only static lists of views shared by several frames are materialised (their records are re-read by every
+// frame of the view and by the view pass).  Static lists private to one frame and all dynamic lists are not:
+// part of their entries is never reached before the pixels saturate, so the blend fetches those records itself.
 __global__ void __launch_bounds__(256)
 gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t Ns,
                      int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ pos_of,
                      const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
                      int64_t cap, const int32_t* __restrict__ labels, int32_t* __restrict__ lab_stream,
                      const uint32_t* __restrict__ view_cnt) {
-  const uint32_t D = bin_off[nbins];
-  if ((int64_t)D > cap) return;
+  if ((int64_t)bin_off[nbins] > cap) return;
+  const uint32_t D = bin_off[(int64_t)V * bins_per_list];  // end of the static lists
   for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < D; p += gridDim.x * blockDim.x) {
-    int lo = 0, hi = n_lists - 1;  // last list whose start is <= p
+    int lo = 0, hi = V - 1;  // last list whose start is <= p
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
       if (bin_off[(int64_t)mid * bins_per_list] <= p) lo = mid; else hi = mid - 1;
     }
-    const bool dyn = lo >= V;
-    if (!dyn && view_cnt[lo] < 2u) continue;  // fetched lazily by the blend
+    if (view_cnt[lo] < 2u) continue;  // fetched lazily by the blend
     const u64 key = keys[p];
     const uint32_t idx = (uint32_t)(key & 0xffffffffull);
-    const int64_t pos = pos_of ? (int64_t)pos_of[idx] : (int64_t)idx;  // position inside the Gaussian's layer
-    const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)(lo - V) * Nm + pos : (int64_t)lo * Ns + pos;
+    const int64_t pos = pos_of ? (int64_t)pos_of[idx] : (int64_t)idx;  // position inside the static layer
+    const int64_t item = (int64_t)lo * Ns + pos;
     splats[p] = make_splat(rec, item);
     if (lab_stream != nullptr) lab_stream[p] = labels[idx];  // segmentation observation only
   }

@@ -65,10 +65,11 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              const float* __restrict__ st_color, const float* __restrict__ st_invd,
              const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg, const int32_t* __restrict__ st_seg,
              int use_view_images, const float4* __restrict__ rec, const int32_t* __restrict__ pos_of, int64_t Ns,
-             const int32_t* __restrict__ labels) {
-  // A static list whose view is looked through by one frame only is not materialised as a splat stream
-  // (gather_splats_kernel skips it): this kernel then fetches the records of the entries it actually reaches
-  // from the per-item records through the sorted keys ("lazy" stream A).
+             const int32_t* __restrict__ labels, int64_t Nm) {
+  // Only static lists of views shared by several frames are materialised as a splat stream
+  // (gather_splats_kernel); for every other list this kernel fetches the records of the entries it actually
+  // reaches (about 70 % of them at cfg3, a quarter with per-env cameras) from the per-item records through
+  // the sorted keys: key -> Gaussian index -> position in its layer -> 64 B record -> make_splat().
   // SEG: additionally reports, per pixel, the label of the Gaussian with the largest blending weight alpha*T
   // (GSW_SEG_NONE where nothing was composited); lab_stream holds the label of every stream entry.
   // mode 0: frames.  mode 1: "view pass": blockIdx enumerates (view, tile); renders the static list of every
@@ -101,6 +102,8 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     if ((int64_t)D > cap) status[2] = 1;
   }
   const bool lazyA = mode == 0 && view_cnt[v] < 2u;
+  constexpr bool lazyD = true;  // dynamic lists are never materialised
+  const int64_t itemA = (int64_t)v * Ns, itemD = (int64_t)V * Ns + (int64_t)f * Nm;
   if (mode == 0 && use_view_images && nd == 0 && view_cnt[v] >= 2u) {  // static-only tile of a shared view
     if (inside) {
       const size_t HW = (size_t)g.H * g.W, pid = (size_t)py * g.W + px;
@@ -142,9 +145,9 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     if (rs == 0 || rd == 0) {  // single-stream chunk
       const uint32_t src = rd == 0 ? s0 + i0 : d0 + j0;
       if (threadIdx.x < n) {
-        if (rd == 0 && lazyA) {
+        if (rd == 0 ? lazyA : lazyD) {
           const uint32_t idx = (uint32_t)(keys[src + threadIdx.x] & 0xffffffffull);
-          const Splat sp = make_splat(rec, (int64_t)v * Ns + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
+          const Splat sp = make_splat(rec, (rd == 0 ? itemA : itemD) + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
           sRec[3 * threadIdx.x] = sp.a;
           sRec[3 * threadIdx.x + 1] = sp.b;
           sRec[3 * threadIdx.x + 2] = sp.c;
@@ -174,9 +177,9 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         const uint32_t a = lo, b = t - lo;
         take_s = a < ws && (b >= wd || kS[a] < kD[b]);
         const uint32_t pos = take_s ? s0 + i0 + a : d0 + j0 + b;
-        if (take_s && lazyA) {
-          const uint32_t idx = (uint32_t)(kS[a] & 0xffffffffull);
-          const Splat sp = make_splat(rec, (int64_t)v * Ns + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
+        if (take_s ? lazyA : lazyD) {
+          const uint32_t idx = (uint32_t)((take_s ? kS[a] : kD[b]) & 0xffffffffull);
+          const Splat sp = make_splat(rec, (take_s ? itemA : itemD) + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
           sRec[3 * t] = sp.a;
           sRec[3 * t + 1] = sp.b;
           sRec[3 * t + 2] = sp.c;
@@ -320,7 +323,7 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
       want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
       w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
       want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr, 0, w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns,    \
-      ctx->labels)
+      ctx->labels, ctx->last.Nm)
   if (want_seg)
     GSW_VIEW_PASS(true);
   else
@@ -345,7 +348,7 @@ int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int6
       cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
       w.status.as<long long>(), 0, w.view_cnt.as<uint32_t>(), w.st_u8.as<uint8_t>(), w.st_color.as<float>(),          \
       w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>(), share ? 1 : 0,              \
-      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels)
+      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm)
   if (out_seg)
     GSW_BLEND(true);
   else
