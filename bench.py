@@ -468,6 +468,19 @@ def run_ours(args):
             for k, v in eng.stage_ms().items():
                 acc[k] = acc.get(k, 0.0) + v / 3
         eng.profile(False)
+        if os.environ.get("GSW_BENCH_DEBUG") and rank == 0:  # bin-size histogram of the last step (tuning aid)
+            import numpy as np
+            off = eng.debug_bin_offsets().astype(np.int64)
+            n = np.diff(off)
+            Vn = int(wrap._views(list(CAMERAS))[0].shape[0])
+            T = (len(n)) // (Vn + F)
+            for name, part in (("static", n[:Vn * T]), ("dynamic", n[Vn * T:])):
+                edges = [0, 1, 65, 129, 257, 513, 1025, 2049, 4097, 16385, 1 << 30]
+                h, _ = np.histogram(part, bins=edges)
+                w, _ = np.histogram(part, bins=edges, weights=part)
+                log(f"[bins {mode} {name}] total {int(part.sum())} in {len(part)} bins; per size class "
+                    f"(upper edge: bins/keys): " + ", ".join(f"<{e}: {int(a)}/{int(b)}" for e, a, b in
+                                                            zip(edges[1:], h, w)))
         st = dict(eng.last_stats)
         results[mode] = dict(ms=ms, fps=world * F * args.steps / (ms * 1e-3), stages=acc, stats=st,
                              V=int(wrap._views(list(CAMERAS))[0].shape[0]))

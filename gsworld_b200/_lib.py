@@ -53,6 +53,7 @@ SYMBOLS = {
     "gsw_profile_read": (C.c_int, [_vp, C.POINTER(C.c_float), C.c_int]),
     "gsw_debug_frame_attrs": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gsw_debug_frame_lists": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i64, C.POINTER(_i64), _vp]),
+    "gsw_debug_bin_offsets": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), _vp]),
 }
 
 _lib = None

@@ -166,6 +166,13 @@ __device__ __forceinline__ void sort8(u64 (&k)[8]) {
 // Sorts buf[0..n) in place (padded to n8 = roundup(n,8) with +inf).  Each merge round computes a thread's
 // output chunks into registers, then all threads write back after a barrier, so one buffer suffices.
 // CPT = max chunks (of 8 keys) per thread = capacity / (8 * THREADS).
+// Shared-memory layout of the sort buffer: logical element e lives at e ^ ((e >> 4) & 7), a permutation inside
+// every aligned block of 8 keys.  With the plain layout a warp whose lanes each own 8 consecutive 64-bit keys
+// (the chunk loads/stores below, lane stride 64 B) hits two bank pairs only -> 16 wavefronts per access; with
+// the swizzle a half-warp covers all 32 banks once -> 2 wavefronts, the minimum for 256 B.  The merge-path
+// reads (lane stride ~4 keys) spread the same way.
+__device__ __forceinline__ uint32_t swz(uint32_t e) { return e ^ ((e >> 4) & 7u); }
+
 template <int THREADS, int CPT>
 __device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
   const uint32_t n8 = (n + 7u) & ~7u;
@@ -174,12 +181,13 @@ __device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
   for (int q = 0; q < CPT; ++q) {
     const uint32_t c = threadIdx.x + q * THREADS;
     if (c < chunks) {
+      const uint32_t x = (c >> 1) & 7u;  // swz(8c + i) = 8c + (i ^ x)
       u64 k[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) k[i] = (8 * c + i < n) ? buf[8 * c + i] : ~0ull;
+      for (int i = 0; i < 8; ++i) k[i] = (8 * c + i < n) ? buf[8 * c + (i ^ x)] : ~0ull;
       sort8(k);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) buf[8 * c + i] = k[i];
+      for (int i = 0; i < 8; ++i) buf[8 * c + (i ^ x)] = k[i];
     }
   }
   __syncthreads();
@@ -193,26 +201,25 @@ __device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
         const uint32_t pbase = (o / (2 * L)) * (2 * L);
         const uint32_t lenA = min(L, n8 - pbase);
         const uint32_t lenB = (n8 - pbase > L) ? min(L, n8 - pbase - L) : 0u;
-        const u64* A = buf + pbase;
-        const u64* B = A + L;
+        const uint32_t A = pbase, B = pbase + L;  // logical positions of the two runs
         const uint32_t d = o - pbase;
         uint32_t lo = d > lenB ? d - lenB : 0u, hi = min(d, lenA);
         while (lo < hi) {
           const uint32_t mid = (lo + hi) >> 1;
-          if (A[mid] < B[d - 1 - mid]) lo = mid + 1; else hi = mid;
+          if (buf[swz(A + mid)] < buf[swz(B + d - 1 - mid)]) lo = mid + 1; else hi = mid;
         }
         uint32_t a = lo, b = d - lo;
-        u64 ka = a < lenA ? A[a] : ~0ull, kb = b < lenB ? B[b] : ~0ull;
+        u64 ka = a < lenA ? buf[swz(A + a)] : ~0ull, kb = b < lenB ? buf[swz(B + b)] : ~0ull;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const bool ta = (b >= lenB) || (a < lenA && ka <= kb);
           out[q][i] = ta ? ka : kb;
           if (ta) {
             ++a;
-            ka = a < lenA ? A[a] : ~0ull;
+            ka = a < lenA ? buf[swz(A + a)] : ~0ull;
           } else {
             ++b;
-            kb = b < lenB ? B[b] : ~0ull;
+            kb = b < lenB ? buf[swz(B + b)] : ~0ull;
           }
         }
       }
@@ -222,8 +229,9 @@ __device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
     for (int q = 0; q < CPT; ++q) {
       const uint32_t c = threadIdx.x + q * THREADS;
       if (c < chunks) {
+        const uint32_t x = (c >> 1) & 7u;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) buf[8 * c + i] = out[q][i];
+        for (int i = 0; i < 8; ++i) buf[8 * c + (i ^ x)] = out[q][i];
       }
     }
     __syncthreads();
@@ -297,21 +305,25 @@ __global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64
   }
 }
 
-// Persistent CTAs pull segments of one size class and sort their keys in shared memory.
+// Persistent CTAs pull segments of one size class (ticket counter: segment sizes vary by 4x inside a class)
+// and sort their keys in shared memory.
 template <int CAP, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 sort_segments_kernel(const Segment* __restrict__ queue, const uint32_t* __restrict__ queue_count, uint32_t queue_cap,
-                     u64* __restrict__ keys) {
+                     u64* __restrict__ keys, uint32_t* __restrict__ ticket) {
   extern __shared__ u64 sbuf[];
+  __shared__ uint32_t s_next;
   const uint32_t nseg = min(*queue_count, queue_cap);
-  for (uint32_t sidx = blockIdx.x; sidx < nseg; sidx += gridDim.x) {
+  for (uint32_t sidx = blockIdx.x; sidx < nseg;) {
     const Segment sg = queue[sidx];
+    if (threadIdx.x == 0) s_next = gridDim.x + atomicAdd(ticket, 1u);
     const uint32_t start = sg.start, n = sg.count;
-    for (uint32_t t = threadIdx.x; t < n; t += THREADS) sbuf[t] = keys[start + t];
+    for (uint32_t t = threadIdx.x; t < n; t += THREADS) sbuf[swz(t)] = keys[start + t];
     __syncthreads();
     smem_merge_sort<THREADS, CAP / (8 * THREADS)>(sbuf, n);
-    for (uint32_t t = threadIdx.x; t < n; t += THREADS) keys[start + t] = sbuf[t];
-    __syncthreads();  // buffer is reused by the next segment of this CTA
+    for (uint32_t t = threadIdx.x; t < n; t += THREADS) keys[start + t] = sbuf[swz(t)];
+    sidx = s_next;    // written before the barriers inside the sort
+    __syncthreads();  // buffer (and s_next) are reused by the next segment of this CTA
   }
 }
 
@@ -546,14 +558,15 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
   Q.q[1] = base + 2 * nbins;
   Q.cap[1] = total - 2 * (uint32_t)nbins;
   Q.count = w.status.as<uint32_t>() + 12;  // three words of the status block (zeroed every launch)
+  uint32_t* ticket = w.status.as<uint32_t>() + 16;  // two more: work tickets of the medium / small sort
   classify_bins_kernel<<<(unsigned)((nbins + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, cap, Q,
                                                                       w.status.as<long long>());
   refine_big_bins_kernel<<<148 * 2, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
                                                  w.status.as<long long>());
   sort_segments_kernel<kSortSmemKeys, 512><<<148 * 3, 512, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
-                                                                        w.keys.as<unsigned long long>());
+                                                                        w.keys.as<unsigned long long>(), ticket);
   sort_segments_kernel<kSmallKeys, 128><<<148 * 12, 128, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
-                                                                      w.keys.as<unsigned long long>());
+                                                                      w.keys.as<unsigned long long>(), ticket + 1);
   count_launches(4);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -117,13 +117,13 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   const int64_t mc = (int64_t)g.T + 1;
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
-  if ((rc = w.status.reserve(64))) return rc;
+  if ((rc = w.status.reserve(128))) return rc;
   // every queued sub-segment but the last of a bin pairs with a neighbour to more than kSortSmemKeys entries
   if ((rc = w.seg_queue.reserve((size_t)(2 * (cap / kSortSmemKeys) + 3 * nbins + 16) * 16))) return rc;
 
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
-  GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 64, s));
+  GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 128, s));
   auto mark = [&](int k) {
     if (ctx->profile) cudaEventRecord(ctx->stage_evt[k], s);
   };
@@ -755,7 +755,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.merge_off, (size_t)(kNaMaxTiles + 1) * 4);
   carve(w.keys, (size_t)kNaMaxEntries * 8);
   carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
-  carve(w.status, 64);
+  carve(w.status, 128);
   carve(w.seg_queue, (size_t)(2 * (kNaMaxEntries / kSortSmemKeys) + 3 * nbins + 16) * 16);
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view
@@ -900,6 +900,23 @@ int gsw_debug_frame_lists(gsw_ctx* c, int32_t frame, int32_t* ranges, uint64_t* 
     set_error("gsw_debug_frame_lists: need %u entries, cap %lld", total, (long long)cap);
     return GSW_E_CAPACITY;
   }
+  return GSW_OK;
+}
+
+int gsw_debug_bin_offsets(gsw_ctx* c, uint32_t* dst_host, int64_t max_bins, int64_t* nbins, gsw_stream stream) {
+  if (!c || !c->last.valid || !dst_host) {
+    set_error("gsw_debug_bin_offsets: no valid launch / bad argument");
+    return GSW_E_STATE;
+  }
+  if (nbins) *nbins = c->last.nbins;
+  if (max_bins < c->last.nbins) {
+    set_error("gsw_debug_bin_offsets: need room for %lld bins", (long long)c->last.nbins);
+    return GSW_E_CAPACITY;
+  }
+  Guard gd(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  GSW_CUDA(cudaMemcpyAsync(dst_host, c->ws.bin_off.p, (size_t)(c->last.nbins + 1) * 4, cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaStreamSynchronize(s));
   return GSW_OK;
 }
 

@@ -273,6 +273,18 @@ class Engine:
     def _last_N(self):
         return getattr(self, "_dbg_N", None) or self.N
 
+    def debug_bin_offsets(self):
+        """Exclusive (list, tile) bin offsets of the last launch as a numpy uint32 array [nbins + 1]."""
+        import numpy as np
+
+        n = C.c_int64(0)
+        buf = np.zeros((1,), np.uint32)
+        rc = self.lib.gsw_debug_bin_offsets(self._h, buf.ctypes.data, 0, C.byref(n), self._stream())
+        buf = np.zeros((int(n.value) + 1,), np.uint32)
+        _lib.check(self.lib.gsw_debug_bin_offsets(self._h, buf.ctypes.data, int(n.value) + 1, C.byref(n),
+                                                  self._stream()))
+        return buf
+
     def debug_frame_lists(self, frame: int, T: int):
         d = self.device
         cap = 1 << 16

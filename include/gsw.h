@@ -197,6 +197,11 @@ int gsw_debug_frame_attrs(gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* 
  * too small; *count (host) receives D for the frame.  Synchronises. */
 int gsw_debug_frame_lists(gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
                           int64_t cap, int64_t* count, gsw_stream stream);
+/* Exclusive offsets of the (list, tile) bins of the last launch, copied to HOST memory: lists 0..V-1 are the
+ * static lists of the views, V..V+F-1 the dynamic lists of the frames; dst[nbins] = total entries.  *nbins
+ * receives the bin count; GSW_E_CAPACITY if max_bins is too small.  Tuning / test aid (bin-size histogram);
+ * no counterpart in the reference.  Synchronises. */
+int gsw_debug_bin_offsets(gsw_ctx* ctx, uint32_t* dst_host, int64_t max_bins, int64_t* nbins, gsw_stream stream);
 
 #ifdef __cplusplus
 }
