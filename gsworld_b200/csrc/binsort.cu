@@ -144,7 +144,7 @@ __device__ __forceinline__ uint32_t pow2ceil(uint32_t n) {
   return n <= 1 ? 1u : 1u << (32 - __clz(n - 1));
 }
 
-// ---- shared-memory merge sort of one segment (n <= kSortSmemKeys), 8 keys per thread step ----
+// ---- shared-memory merge sort of one segment (n <= kSortSmemKeys), 16 keys per thread step ----
 typedef unsigned long long u64;
 
 __device__ __forceinline__ void cswap(u64& a, u64& b) {
@@ -153,73 +153,84 @@ __device__ __forceinline__ void cswap(u64& a, u64& b) {
   b = hi;
 }
 
-// Batcher odd-even merge sort network for 8 keys (19 comparators)
-__device__ __forceinline__ void sort8(u64 (&k)[8]) {
-  cswap(k[0], k[1]); cswap(k[2], k[3]); cswap(k[4], k[5]); cswap(k[6], k[7]);
-  cswap(k[0], k[2]); cswap(k[1], k[3]); cswap(k[4], k[6]); cswap(k[5], k[7]);
-  cswap(k[1], k[2]); cswap(k[5], k[6]);
-  cswap(k[0], k[4]); cswap(k[1], k[5]); cswap(k[2], k[6]); cswap(k[3], k[7]);
-  cswap(k[2], k[4]); cswap(k[3], k[5]);
-  cswap(k[1], k[2]); cswap(k[3], k[4]); cswap(k[5], k[6]);
+// 16-key sorting network with 60 comparators in 10 layers (Green's network; checked exhaustively with the
+// 0-1 principle by tests/test_sort_network.py)
+__device__ __forceinline__ void sort16(u64 (&k)[16]) {
+  cswap(k[0], k[13]); cswap(k[1], k[12]); cswap(k[2], k[15]); cswap(k[3], k[14]); cswap(k[4], k[8]); cswap(k[5], k[6]); cswap(k[7], k[11]); cswap(k[9], k[10]);
+  cswap(k[0], k[5]); cswap(k[1], k[7]); cswap(k[2], k[9]); cswap(k[3], k[4]); cswap(k[6], k[13]); cswap(k[8], k[14]); cswap(k[10], k[15]); cswap(k[11], k[12]);
+  cswap(k[0], k[1]); cswap(k[2], k[3]); cswap(k[4], k[5]); cswap(k[6], k[8]); cswap(k[7], k[9]); cswap(k[10], k[11]); cswap(k[12], k[13]); cswap(k[14], k[15]);
+  cswap(k[0], k[2]); cswap(k[1], k[3]); cswap(k[4], k[10]); cswap(k[5], k[11]); cswap(k[6], k[7]); cswap(k[8], k[9]); cswap(k[12], k[14]); cswap(k[13], k[15]);
+  cswap(k[1], k[2]); cswap(k[3], k[12]); cswap(k[4], k[6]); cswap(k[5], k[7]); cswap(k[8], k[10]); cswap(k[9], k[11]); cswap(k[13], k[14]);
+  cswap(k[1], k[4]); cswap(k[2], k[6]); cswap(k[5], k[8]); cswap(k[7], k[10]); cswap(k[9], k[13]); cswap(k[11], k[14]);
+  cswap(k[2], k[4]); cswap(k[3], k[6]); cswap(k[9], k[12]); cswap(k[11], k[13]);
+  cswap(k[3], k[5]); cswap(k[6], k[8]); cswap(k[7], k[9]); cswap(k[10], k[12]);
+  cswap(k[3], k[4]); cswap(k[5], k[6]); cswap(k[7], k[8]); cswap(k[9], k[10]); cswap(k[11], k[12]);
+  cswap(k[6], k[7]); cswap(k[8], k[9]);
 }
 
-// Sorts buf[0..n) in place (padded to n8 = roundup(n,8) with +inf).  Each merge round computes a thread's
-// output chunks into registers, then all threads write back after a barrier, so one buffer suffices.
-// CPT = max chunks (of 8 keys) per thread = capacity / (8 * THREADS).
-// Shared-memory layout of the sort buffer: logical element e lives at e ^ ((e >> 4) & 7), a permutation inside
-// every aligned block of 8 keys.  With the plain layout a warp whose lanes each own 8 consecutive 64-bit keys
-// (the chunk loads/stores below, lane stride 64 B) hits two bank pairs only -> 16 wavefronts per access; with
-// the swizzle a half-warp covers all 32 banks once -> 2 wavefronts, the minimum for 256 B.  The merge-path
-// reads (lane stride ~4 keys) spread the same way.
-__device__ __forceinline__ uint32_t swz(uint32_t e) { return e ^ ((e >> 4) & 7u); }
+// Shared-memory layout of the sort buffer: logical element e lives at e ^ ((e >> 4) & 15), a permutation
+// inside every aligned block of 16 keys.  With the plain layout a warp whose lanes each own 16 consecutive
+// 64-bit keys (the chunk loads/stores below, lane stride 128 B) would hit ONE bank pair -> 32 wavefronts per
+// access; with the swizzle a half-warp covers all 32 banks once -> 2 wavefronts, the minimum for 256 B.
+// The merge-path reads (lane stride ~8 keys) spread the same way.
+__device__ __forceinline__ uint32_t swz(uint32_t e) { return e ^ ((e >> 4) & 15u); }
 
+// Sorts buf[0..n) in place (logically padded to nP = roundup(n,16) with +inf; buf holds the swizzled layout).
+// Registers first: every thread sorts 16 keys with the network.  Then log2(nP/16) merge rounds: a thread finds
+// the merge-path split of its 16 outputs by binary search and merges sequentially, keeping the two run heads
+// in registers; all threads write back after a barrier, so one buffer suffices.  Instruction count is what
+// bounds this kernel (ncu: issue-bound once the bank conflicts are gone), hence 16 keys per search and the
+// branch-free inner step.  CPT = max 16-key chunks per thread = capacity / (16 * THREADS).
 template <int THREADS, int CPT>
 __device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
-  const uint32_t n8 = (n + 7u) & ~7u;
-  const uint32_t chunks = n8 >> 3;
+  const uint32_t nP = (n + 15u) & ~15u;
+  const uint32_t chunks = nP >> 4;
 #pragma unroll
   for (int q = 0; q < CPT; ++q) {
     const uint32_t c = threadIdx.x + q * THREADS;
     if (c < chunks) {
-      const uint32_t x = (c >> 1) & 7u;  // swz(8c + i) = 8c + (i ^ x)
-      u64 k[8];
+      const uint32_t x = c & 15u;  // swz(16c + i) = 16c + (i ^ x)
+      u64 k[16];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) k[i] = (8 * c + i < n) ? buf[8 * c + (i ^ x)] : ~0ull;
-      sort8(k);
+      for (int i = 0; i < 16; ++i) k[i] = (16 * c + i < n) ? buf[16 * c + (i ^ x)] : ~0ull;
+      sort16(k);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) buf[8 * c + (i ^ x)] = k[i];
+      for (int i = 0; i < 16; ++i) buf[16 * c + (i ^ x)] = k[i];
     }
   }
   __syncthreads();
-  for (uint32_t L = 8; L < n8; L <<= 1) {
-    u64 out[CPT][8];
+  for (uint32_t L = 16; L < nP; L <<= 1) {
+    u64 out[CPT][16];
 #pragma unroll
     for (int q = 0; q < CPT; ++q) {
       const uint32_t c = threadIdx.x + q * THREADS;
       if (c < chunks) {
-        const uint32_t o = 8 * c;
-        const uint32_t pbase = (o / (2 * L)) * (2 * L);
-        const uint32_t lenA = min(L, n8 - pbase);
-        const uint32_t lenB = (n8 - pbase > L) ? min(L, n8 - pbase - L) : 0u;
-        const uint32_t A = pbase, B = pbase + L;  // logical positions of the two runs
-        const uint32_t d = o - pbase;
+        const uint32_t o = 16 * c;
+        const uint32_t A = o & ~(2 * L - 1), B = A + L;  // logical starts of the two runs
+        const uint32_t lenA = min(L, nP - A);
+        const uint32_t lenB = (nP - A > L) ? min(L, nP - B) : 0u;
+        const uint32_t d = o - A;
         uint32_t lo = d > lenB ? d - lenB : 0u, hi = min(d, lenA);
         while (lo < hi) {
           const uint32_t mid = (lo + hi) >> 1;
           if (buf[swz(A + mid)] < buf[swz(B + d - 1 - mid)]) lo = mid + 1; else hi = mid;
         }
-        uint32_t a = lo, b = d - lo;
-        u64 ka = a < lenA ? buf[swz(A + a)] : ~0ull, kb = b < lenB ? buf[swz(B + b)] : ~0ull;
+        uint32_t ia = A + lo, ib = B + (d - lo);
+        const uint32_t endA = A + lenA, endB = B + lenB;
+        // exhausted runs read as +inf (no real key is: depth bits of a finite positive float), so the head
+        // comparison alone decides
+        u64 ka = ia < endA ? buf[swz(ia)] : ~0ull, kb = ib < endB ? buf[swz(ib)] : ~0ull;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const bool ta = (b >= lenB) || (a < lenA && ka <= kb);
+        for (int i = 0; i < 16; ++i) {
+          const bool ta = ka <= kb;
           out[q][i] = ta ? ka : kb;
-          if (ta) {
-            ++a;
-            ka = a < lenA ? buf[swz(A + a)] : ~0ull;
-          } else {
-            ++b;
-            kb = b < lenB ? buf[swz(B + b)] : ~0ull;
+          if (i < 15) {
+            ia += ta ? 1u : 0u;
+            ib += ta ? 0u : 1u;
+            const uint32_t p = ta ? ia : ib;
+            const u64 v = p < (ta ? endA : endB) ? buf[swz(p)] : ~0ull;
+            ka = ta ? v : ka;
+            kb = ta ? kb : v;
           }
         }
       }
@@ -229,9 +240,9 @@ __device__ __forceinline__ void smem_merge_sort(u64* buf, uint32_t n) {
     for (int q = 0; q < CPT; ++q) {
       const uint32_t c = threadIdx.x + q * THREADS;
       if (c < chunks) {
-        const uint32_t x = (c >> 1) & 7u;
+        const uint32_t x = c & 15u;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) buf[8 * c + (i ^ x)] = out[q][i];
+        for (int i = 0; i < 16; ++i) buf[16 * c + (i ^ x)] = out[q][i];
       }
     }
     __syncthreads();
@@ -320,7 +331,7 @@ sort_segments_kernel(const Segment* __restrict__ queue, const uint32_t* __restri
     const uint32_t start = sg.start, n = sg.count;
     for (uint32_t t = threadIdx.x; t < n; t += THREADS) sbuf[swz(t)] = keys[start + t];
     __syncthreads();
-    smem_merge_sort<THREADS, CAP / (8 * THREADS)>(sbuf, n);
+    smem_merge_sort<THREADS, CAP / (16 * THREADS)>(sbuf, n);
     for (uint32_t t = threadIdx.x; t < n; t += THREADS) keys[start + t] = sbuf[swz(t)];
     sidx = s_next;    // written before the barriers inside the sort
     __syncthreads();  // buffer (and s_next) are reused by the next segment of this CTA
@@ -563,9 +574,9 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
                                                                       w.status.as<long long>());
   refine_big_bins_kernel<<<148 * 2, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
                                                  w.status.as<long long>());
-  sort_segments_kernel<kSortSmemKeys, 512><<<148 * 3, 512, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
+  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 4, 256, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
                                                                         w.keys.as<unsigned long long>(), ticket);
-  sort_segments_kernel<kSmallKeys, 128><<<148 * 12, 128, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
+  sort_segments_kernel<kSmallKeys, 64><<<148 * 16, 64, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
                                                                       w.keys.as<unsigned long long>(), ticket + 1);
   count_launches(4);
   GSW_CUDA(cudaGetLastError());
