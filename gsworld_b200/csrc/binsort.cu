@@ -283,16 +283,19 @@ gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_
   }
 }
 
-// Work classification: every non-empty bin goes to one of three queues by size, so that the sort CTAs
-// are sized for their segments and no CTA is launched for an empty bin.
-//   queue 0 (small):  n <= kSmallKeys          -> 128-thread CTAs, 16 KB shared memory
-//   queue 1 (medium): n <= kSortSmemKeys       -> 256-thread CTAs, 64 KB
-//   queue 2 (huge):   larger                   -> refine_big_bins_kernel splits by depth into medium segments
+// Work classification: every non-empty bin goes to one of four queues by size, so that the sort CTAs
+// are sized for their segments (a thread sorts 16 keys; idle threads only wait at the barriers of the merge
+// rounds and hold warp slots) and no CTA is launched for an empty bin.
+//   queue 0 (small):  n <= kSmallKeys (1024)   ->  64-thread CTAs,  8 KB shared memory
+//   queue 3 (mid):    n <= kMidKeys (2048)     -> 128-thread CTAs, 16 KB
+//   queue 1 (medium): n <= kSortSmemKeys       -> 256-thread CTAs, 32 KB
+//   queue 2 (huge):   larger                   -> refine_big_bins_kernel splits by depth into mid/medium segments
 constexpr int kSmallKeys = 1024;
+constexpr int kMidKeys = 2048;
 struct Queues {
-  Segment* q[3];
-  uint32_t* count;  // [3]
-  uint32_t cap[3];
+  Segment* q[4];
+  uint32_t* count;  // [4]
+  uint32_t cap[4];
 };
 
 __global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int64_t cap, Queues Q,
@@ -302,7 +305,7 @@ __global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64
   const uint32_t start = bin_off[bin], end = bin_off[bin + 1];
   if (end <= start || (int64_t)end > cap) return;
   const uint32_t n = end - start;
-  const int k = n <= (uint32_t)kSmallKeys ? 0 : (n <= (uint32_t)kSortSmemKeys ? 1 : 2);
+  const int k = n <= (uint32_t)kSmallKeys ? 0 : (n <= (uint32_t)kMidKeys ? 3 : (n <= (uint32_t)kSortSmemKeys ? 1 : 2));
   const uint32_t slot = atomicAdd(&Q.count[k], 1u);
   if (slot < Q.cap[k]) {
     Segment sg;
@@ -448,14 +451,15 @@ refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ spl
           }
           return;
         }
-        const uint32_t q = atomicAdd(&Q.count[1], 1u);
-        if (q < Q.cap[1]) {
+        const int k = hi - lo <= (uint32_t)kMidKeys ? 3 : 1;
+        const uint32_t q = atomicAdd(&Q.count[k], 1u);
+        if (q < Q.cap[k]) {
           Segment sg;
           sg.start = start + lo;
           sg.count = hi - lo;
           sg.bin = bin;
           sg.pad = 0;
-          Q.q[1][q] = sg;
+          Q.q[k][q] = sg;
         } else {
           status[2] = 3;
         }
@@ -558,7 +562,8 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
   constexpr size_t smem_m = (size_t)kSortSmemKeys * sizeof(unsigned long long);  // 32 KB
   constexpr size_t smem_s = (size_t)kSmallKeys * sizeof(unsigned long long);     // 8 KB
   (void)V; (void)Ns; (void)Nm; (void)g;
-  // queue storage: [small: nbins][huge: nbins][medium: the rest]
+  // queue storage: [small: nbins][huge: nbins][medium: half of the rest][mid: the other half]; a queued
+  // mid/medium segment that is not a whole bin pairs with a neighbour to more than kMidKeys entries
   Queues Q;
   Segment* base = w.seg_queue.as<Segment>();
   const uint32_t total = (uint32_t)(w.seg_queue.bytes / sizeof(Segment));
@@ -566,19 +571,22 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
   Q.cap[0] = (uint32_t)nbins;
   Q.q[2] = base + nbins;
   Q.cap[2] = (uint32_t)nbins;
+  Q.cap[1] = Q.cap[3] = (total - 2 * (uint32_t)nbins) / 2;
   Q.q[1] = base + 2 * nbins;
-  Q.cap[1] = total - 2 * (uint32_t)nbins;
-  Q.count = w.status.as<uint32_t>() + 12;  // three words of the status block (zeroed every launch)
-  uint32_t* ticket = w.status.as<uint32_t>() + 16;  // two more: work tickets of the medium / small sort
+  Q.q[3] = Q.q[1] + Q.cap[1];
+  Q.count = w.status.as<uint32_t>() + 12;  // four words of the status block (zeroed every launch)
+  uint32_t* ticket = w.status.as<uint32_t>() + 16;  // three more: work tickets of the medium / small / mid sort
   classify_bins_kernel<<<(unsigned)((nbins + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, cap, Q,
                                                                       w.status.as<long long>());
   refine_big_bins_kernel<<<148 * 2, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
                                                  w.status.as<long long>());
   sort_segments_kernel<kSortSmemKeys, 256><<<148 * 4, 256, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
                                                                         w.keys.as<unsigned long long>(), ticket);
+  sort_segments_kernel<kMidKeys, 128><<<148 * 8, 128, 2 * smem_s, s>>>(Q.q[3], Q.count + 3, Q.cap[3],
+                                                                      w.keys.as<unsigned long long>(), ticket + 2);
   sort_segments_kernel<kSmallKeys, 64><<<148 * 16, 64, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
                                                                       w.keys.as<unsigned long long>(), ticket + 1);
-  count_launches(4);
+  count_launches(5);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }

@@ -118,8 +118,9 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(128))) return rc;
-  // every queued sub-segment but the last of a bin pairs with a neighbour to more than kSortSmemKeys entries
-  if ((rc = w.seg_queue.reserve((size_t)(2 * (cap / kSortSmemKeys) + 3 * nbins + 16) * 16))) return rc;
+  // medium and mid queue (half each): whole bins (<= nbins each) plus sub-segments of huge bins, of which
+  // every one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries
+  if ((rc = w.seg_queue.reserve((size_t)(8 * (cap / kSortSmemKeys) + 6 * nbins + 32) * 16))) return rc;
 
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
@@ -756,7 +757,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.keys, (size_t)kNaMaxEntries * 8);
   carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
   carve(w.status, 128);
-  carve(w.seg_queue, (size_t)(2 * (kNaMaxEntries / kSortSmemKeys) + 3 * nbins + 16) * 16);
+  carve(w.seg_queue, (size_t)(8 * (kNaMaxEntries / kSortSmemKeys) + 6 * nbins + 32) * 16);
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view
   if (off > kNaBytes) {
