@@ -54,6 +54,31 @@ except Exception:  # pragma: no cover - gymnasium absent in this image
             return getattr(self.env, "unwrapped", self.env)
 
 
+class _HostStage:
+    """Pinned staging for per-step HOST inputs (link / object / camera poses of a CPU simulator).
+
+    The step fills views of a pinned arena and pushes it with ONE asynchronous H2D copy, instead of one
+    synchronous pageable copy per tensor.  Two arenas alternate, each guarded by an event recorded after its
+    copy, so the host may prepare step k+1 while step k's copy is still in flight.  Device-resident inputs
+    (GPU simulation) never come here."""
+
+    def __init__(self, n_floats: int, device):
+        self.h = [torch.empty(n_floats, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.d = torch.empty(n_floats, dtype=torch.float32, device=device)
+        self.ev = [torch.cuda.Event(), torch.cuda.Event()]
+        self.i = 0
+
+    def begin(self) -> torch.Tensor:
+        self.i ^= 1
+        self.ev[self.i].synchronize()  # the copy that last read this arena has completed
+        return self.h[self.i]
+
+    def push(self) -> torch.Tensor:
+        self.d.copy_(self.h[self.i], non_blocking=True)
+        self.ev[self.i].record()
+        return self.d
+
+
 class GSWorldWrapper(_Base):
     def __init__(self, env, robot_pipe, scene_gs_cfg_name: str = "franka_merger",
                  device: Union[str, torch.device] = "cuda", log_state: bool = False,
@@ -165,6 +190,7 @@ class GSWorldWrapper(_Base):
         self._rigid_host = self.rigid_sim2real.detach().to("cpu", torch.float32).contiguous()
         self._scale_host = float(self.scale_sim2real)
         self._cam_bufs = {}
+        self._stages = {}  # pinned staging arenas for host-resident per-step inputs
 
     # ------------------------------------------------------------------ per step
     def transform_gs_perlink(self, splats=None, gs_init_qpos=None, target_mat=None, eef_pos=None):
@@ -174,7 +200,30 @@ class GSWorldWrapper(_Base):
         part (gs_utils.transform_gaussians) is fused into the rasterizer's preprocess kernel."""
         be, dev = self.base_env, self.device
         links = be.agent.robot.get_links()
-        M = torch.stack([l.pose.to_transformation_matrix() for l in links], 1)  # (B,L,4,4)
+        mats = [l.pose.to_transformation_matrix() for l in links]
+        if self.fused_host and mats[0].device.type == "cpu" and torch.device(dev).type == "cuda":
+            # host simulator: one pinned arena, one asynchronous H2D copy for all link and object poses
+            B, L, K = self.num_envs, len(mats), len(self._obj_names)
+            st = self._stages.get("pose")
+            if st is None:
+                st = self._stages["pose"] = _HostStage(B * L * 16 + B * K * 7, dev)
+            h = st.begin()
+            hM = h[:B * L * 16].view(B, L, 4, 4)
+            if all(m.dtype == torch.float32 for m in mats):
+                torch.stack(mats, 1, out=hM)
+            else:
+                for j, m in enumerate(mats):
+                    hM[:, j].copy_(m)
+            if K:
+                actors = be.get_state_dict()["actors"]
+                hO = h[B * L * 16:].view(B, K, 7)
+                for k, n in enumerate(self._obj_names):
+                    hO[:, k].copy_(actors[n][:, :7])
+                    self.gs_semantics[n] = self.obj_gs_semantics[n]
+            d = st.push()
+            return self._engine.compose_poses(d[:B * L * 16].view(B, L, 4, 4),
+                                              d[B * L * 16:].view(B, K, 7) if K else None, self._pose)
+        M = torch.stack(mats, 1)  # (B,L,4,4)
         M = M.to(dev, torch.float32, non_blocking=True).contiguous()
         if self.fused_host:
             obj = None
@@ -296,11 +345,32 @@ class GSWorldWrapper(_Base):
             self._cam_bufs[key] = dict(counts=counts, view=z(V, 16), proj=z(V, 16), campos=z(V, 3), tanfov=z(V, 2),
                                        fv=torch.cat(fv).to(dev))
         cb = self._cam_bufs[key]
+        staged = None
+        first = params[cam_names[0]]["extrinsic_cv"]
+        if first.device.type == "cpu" and torch.device(dev).type == "cuda":
+            # host simulator: all cameras' extrinsics and intrinsics through one pinned arena / one H2D copy
+            ne = first.shape[-2] * first.shape[-1]
+            tot = sum(cb["counts"]) * (ne + 9)
+            st = self._stages.get(("cam",) + key)
+            if st is None:
+                st = self._stages[("cam",) + key] = _HostStage(tot, dev)
+            h = st.begin()
+            o, spans = 0, []
+            for c, n in zip(cam_names, cb["counts"]):
+                h[o:o + n * ne].view(n, *first.shape[-2:]).copy_(params[c]["extrinsic_cv"][:n])
+                h[o + n * ne:o + n * (ne + 9)].view(n, 3, 3).copy_(params[c]["intrinsic_cv"][:n])
+                spans.append((o, o + n * ne, o + n * (ne + 9)))
+                o += n * (ne + 9)
+            d = st.push()
+            staged = [(d[a:b].view(-1, *first.shape[-2:]), d[b:e].view(-1, 3, 3)) for a, b, e in spans]
         base = 0
-        for c, n in zip(cam_names, cb["counts"]):
+        for ci, (c, n) in enumerate(zip(cam_names, cb["counts"])):
             H, W = self._sensor_hw(c)
-            ext = params[c]["extrinsic_cv"][:n].to(dev, torch.float32, non_blocking=True).contiguous()
-            K = params[c]["intrinsic_cv"][:n].to(dev, torch.float32, non_blocking=True).contiguous()
+            if staged is not None:
+                ext, K = staged[ci]
+            else:
+                ext = params[c]["extrinsic_cv"][:n].to(dev, torch.float32, non_blocking=True).contiguous()
+                K = params[c]["intrinsic_cv"][:n].to(dev, torch.float32, non_blocking=True).contiguous()
             sl = slice(base, base + n)
             self._engine.compose_cameras(ext, K, H, W, self._rigid_host, self._scale_host, cb["view"][sl],
                                          cb["proj"][sl], cb["campos"][sl], cb["tanfov"][sl])

@@ -212,3 +212,60 @@ def test_segmentation_observation_matches_oracle_argmax(strict):
             assert (got[ok] == exp[ok]).all()
             checked += int(ok.sum())
     assert checked > 0.9 * 2 * 3 * 64 * 64
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("strict", [True, False])
+def test_host_simulator_inputs_match_device_inputs(strict):
+    """A CPU simulator hands the wrapper host tensors (link / object / camera poses): they go through the pinned
+    staging arenas and one asynchronous copy each.  Same seed on a device-resident env must give the same pose
+    table, the same cameras and byte-identical observations, over several steps (both arenas get reused)."""
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200.gaussian_renderer import PipelineParams
+    from gsworld_b200.gs_world_wrapper import GSWorldWrapper
+    dev = torch.device("cuda:0")
+    objects = ("006_mustard_bottle", "snack_box")
+    scene = fx.make_scene(fx.SceneSpec(robot="fr3_umi", n_total=20_000, per_link=200, objects=objects, per_object=900,
+                                       seed=31)).to(dev)
+    scan = fx.forward_kinematics("fr3_umi", fx.rt.ROBOT_SCAN_QPOS["fr3_umi"][None])[0]
+    from types import SimpleNamespace
+
+    class HostView:
+        """The same FakeEnv numbers, handed out as CPU tensors (what a CPU simulator would give)."""
+
+        def __init__(self, env):
+            self._e = env
+            links = env.agent.robot.get_links()
+            mk = lambda l: SimpleNamespace(name=l.name, pose=SimpleNamespace(
+                to_transformation_matrix=lambda: l.pose.to_transformation_matrix().cpu()))
+            self.agent = SimpleNamespace(uid=env.agent.uid, robot=SimpleNamespace(
+                name=env.agent.robot.name, get_links=lambda: [mk(l) for l in links]))
+
+        def __getattr__(self, name):
+            return getattr(self._e, name)
+
+        @property
+        def unwrapped(self):
+            return self
+
+        def get_state_dict(self):
+            return {"actors": {k: v.cpu() for k, v in self._e.get_state_dict()["actors"].items()}}
+
+        def get_sensor_params(self):
+            return {c: {k: v.cpu() for k, v in p.items()} for c, p in self._e.get_sensor_params().items()}
+
+    wraps = []
+    for host in (True, False):
+        env = fx.FakeEnv("fr3_umi", num_envs=3, hw=(48, 64), objects=objects, seed=31, device=dev)
+        wraps.append(GSWorldWrapper(HostView(env) if host else env, PipelineParams(), "fr3_pnp_box", device=dev,
+                                    merged_model=scene, scan_link_mats=list(scan), strict_reference=strict))
+    obs = [w.reset(seed=5)[0] for w in wraps]
+    for step in range(4):
+        if step:
+            obs = [w.step(None)[0] for w in wraps]
+        torch.cuda.synchronize()
+        assert "pose" in wraps[0]._stages and "pose" not in wraps[1]._stages
+        assert torch.equal(wraps[0]._pose, wraps[1]._pose)
+        for name in wraps[0].base_env.cameras:
+            a, b = obs[0]["sensor_data"][name]["rgb"], obs[1]["sensor_data"][name]["rgb"]
+            assert a.device.type == "cuda" and torch.equal(a, b)

@@ -1,0 +1,26 @@
+"""e2e leg only (host inputs, pinned host observations, sync every step), for experiments on the delivery path."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch, bench
+from gsworld_b200 import fixtures as fx, rig_tables as rt
+from gsworld_b200.gaussian_renderer import PipelineParams
+from gsworld_b200.gs_world_wrapper import GSWorldWrapper
+dev = torch.device("cuda:0")
+scene = bench.make_scene().to(dev)
+base = fx.FakeEnv(bench.ROBOT, num_envs=64, cameras=bench.CAMERAS, hw=(256, 256), objects=bench.OBJECTS, seed=1)
+scan = fx.forward_kinematics(bench.ROBOT, rt.ROBOT_SCAN_QPOS[bench.ROBOT][None])[0]
+env = bench.ReplayEnv(base, 8, dev, False)
+wrap = GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene, scan_link_mats=list(scan))
+pinned = torch.empty((2, 64, 256, 256, 3), dtype=torch.uint8).pin_memory()
+def step():
+    env.advance(); wrap.transform_gs_perlink(None); return wrap._render_gsworld()
+for mode in ("none", "library", "torch"):
+    wrap.obs_host = pinned if mode == "library" else None
+    for _ in range(10): step()
+    torch.cuda.synchronize(); t = time.perf_counter()
+    for _ in range(50):
+        out = step()
+        if mode == "torch":
+            for i, c in enumerate(bench.CAMERAS): pinned[i].copy_(out[c], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    print(f"{mode}: {1e3 * (time.perf_counter() - t) / 50:.3f} ms/step")
