@@ -118,6 +118,11 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(128))) return rc;
+  const size_t chs = cta_hist_words(Ns, V, g), chd = dyn ? cta_hist_words(Nm, F, g) : 0;
+  if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
+  uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;
+  uint32_t* const ch_d = chd ? w.cta_hist.as<uint32_t>() + chs : nullptr;
+  int kept_s = 0, kept_d = 0;
   // medium and mid queue (half each): whole bins (<= nbins each) plus sub-segments of huge bins, of which
   // every one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries
   if ((rc = w.seg_queue.reserve((size_t)(8 * (cap / kSortSmemKeys) + 6 * nbins + 32) * 16))) return rc;
@@ -131,21 +136,22 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
 
   mark(0);
   if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
-                              pose, num_slots, s)))
+                              pose, num_slots, ch_s, &kept_s, s)))
     return rc;
   mark(1);
   if (dyn && Nm > 0)
     if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, view, proj, campos, tanfov, frame_env,
-                                frame_view, pose, num_slots, s)))
+                                frame_view, pose, num_slots, ch_d, &kept_d, s)))
       return rc;
   mark(2);
   if ((rc = launch_scan_u32(w.bin_count.as<uint32_t>(), w.bin_off.as<uint32_t>(), nbins, w.scan_tmp.as<uint32_t>(),
                             s)))
     return rc;
   mark(3);
-  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, s))) return rc;
+  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, s))) return rc;
   if (dyn && Nm > 0)
-    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, s))) return rc;
+    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, s)))
+      return rc;
   mark(4);
   if ((rc = w.view_cnt.reserve((size_t)V * 4 + 16))) return rc;
   if ((rc = launch_count_views(ctx, V, F, frame_view, s))) return rc;
@@ -227,7 +233,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
@@ -760,6 +766,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.seg_queue, (size_t)(8 * (kNaMaxEntries / kSortSmemKeys) + 6 * nbins + 32) * 16);
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view
+  carve(w.cta_hist, (size_t)((kNaMaxP + 2047) / 2048) * (kNaMaxTiles + 1) * 4 + 16);
   if (off > kNaBytes) {
     set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);
     return GSW_E_NOMEM;

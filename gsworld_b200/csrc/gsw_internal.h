@@ -109,6 +109,7 @@ struct Workspace {
   DevBuf seg_queue;             // Segment[]: depth sub-ranges of bins too large for one shared-memory sort
   DevBuf view_cnt, st_u8, st_color, st_invd, st_seg;  // frames per view; static-only image of each shared view
   DevBuf lab_stream;            // int32 [cap_entries]: label of every stream entry (segmentation observation only)
+  DevBuf cta_hist;  // u32: per preprocess CTA {live flag, per-bin entry counts}, consumed by the scatter pass
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -174,9 +175,11 @@ namespace gsw {
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
-                      const float* pose, int32_t num_slots, cudaStream_t s);
+                      const float* pose, int32_t num_slots, uint32_t* cta_hist, int* kept_hist, cudaStream_t s);
+size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g);
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
-                   int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, cudaStream_t s);
+                   int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
+                   cudaStream_t s);
 int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,
                        float* xy, float* conic_opacity, float* rgb, cudaStream_t s);
 int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s);

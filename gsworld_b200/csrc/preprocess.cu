@@ -350,6 +350,8 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   rad[item] = radius;
 
   // ---- count this Gaussian into every (tile, depth bucket) bin it touches ----
+  // (per-thread loop: here the imbalance between one-tile and hundred-tile Gaussians hides behind the other
+  // warps' arithmetic; the warp-cooperative form measured slower in this kernel, faster in the scatter)
   const uint32_t bk = depth_bucket(pvz, g);
   if (hist != nullptr) {
     for (int y = rc.y0; y < rc.y1; ++y)
@@ -359,6 +361,38 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
     for (int y = rc.y0; y < rc.y1; ++y)
       for (int x = rc.x0; x < rc.x1; ++x)
         atomicAdd(&bin_count[(lbase + (uint32_t)(y * g.gx + x)) * (uint32_t)g.NB + bk], 1u);
+  }
+}
+
+// Tiles per Gaussian above which the whole warp expands its rectangle.  Close to a camera (wrist view) one
+// Gaussian covers a hundred tiles and more while its neighbours cover one or two: a per-thread tile loop
+// leaves 31 lanes waiting, and whole CTAs trail the kernel (ncu: SMs active 30 % of the scatter's duration).
+// Used by the scatter pass.
+constexpr int kCoopTiles = 8;
+
+// Calls f(bin_in_list, p0, p1) once per (tile, bucket) bin of every lane's rectangle; p0/p1 are the owning
+// lane's payload words (broadcast when the warp expands the rectangle).  Must be reached by all 32 lanes.
+template <class F>
+__device__ __forceinline__ void warp_for_each_bin(const Rect rc, uint32_t bk, uint32_t p0, uint32_t p1, int gx, int NB,
+                                                  F&& f) {
+  const int w = rc.x1 - rc.x0, n = w * (rc.y1 - rc.y0);
+  const bool coop = n > kCoopTiles;
+  if (!coop)
+    for (int y = rc.y0; y < rc.y1; ++y)
+      for (int x = rc.x0; x < rc.x1; ++x) f((uint32_t)(y * gx + x) * (uint32_t)NB + bk, p0, p1);
+  unsigned m = __ballot_sync(0xffffffffu, coop);
+  const int lane = threadIdx.x & 31;
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    const int x0 = __shfl_sync(0xffffffffu, rc.x0, src), y0 = __shfl_sync(0xffffffffu, rc.y0, src);
+    const int ww = __shfl_sync(0xffffffffu, w, src), nn = __shfl_sync(0xffffffffu, n, src);
+    const uint32_t b = __shfl_sync(0xffffffffu, bk, src);
+    const uint32_t q0 = __shfl_sync(0xffffffffu, p0, src), q1 = __shfl_sync(0xffffffffu, p1, src);
+    for (int t = lane; t < nn; t += 32) {
+      const int dy = t / ww;
+      f((uint32_t)((y0 + dy) * gx + x0 + (t - dy * ww)) * (uint32_t)NB + b, q0, q1);
+    }
   }
 }
 
@@ -459,7 +493,7 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
                   const int32_t* __restrict__ frame_env, const int32_t* __restrict__ frame_view,
                   const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
                   float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
-                  uint32_t* __restrict__ bin_count, int use_hist) {
+                  uint32_t* __restrict__ bin_count, int use_hist, uint32_t* __restrict__ cta_hist) {
   constexpr int use_tma = TMA ? 1 : 0;
   __shared__ ViewSmem vs;
   __shared__ __align__(8) unsigned long long mbar_s;
@@ -568,6 +602,8 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
       const int64_t i = base + it * 256 + threadIdx.x;
       if (i < n_items) rad[item_base + (int64_t)list * n_items + i] = 0;
     }
+    if (cta_hist != nullptr && threadIdx.x == 0)
+      cta_hist[((size_t)list * gridDim.x + blockIdx.x) * (size_t)(g.T * g.NB + 1)] = 0u;  // scatter skips the chunk
     return;
   }
   if (staged && threadIdx.x == 0) {
@@ -626,9 +662,13 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
   if (use_hist) {
     __syncthreads();
     const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
+    // the per-CTA counts are kept for the scatter pass, which walks the same chunk: word 0 = chunk is live
+    uint32_t* keep = cta_hist ? cta_hist + ((size_t)list * gridDim.x + blockIdx.x) * (size_t)(nbl + 1) : nullptr;
+    if (keep != nullptr && threadIdx.x == 0) keep[0] = 1u;
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
       const uint32_t c = hist[k];
       if (c) atomicAdd(&bin_count[gb + k], c);
+      if (keep != nullptr) keep[1 + k] = c;
     }
   }
 }
@@ -636,8 +676,9 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
 // Second pass: write (depth bits << 32 | original index) into the bin's slice.  Order inside a bin is
 // arbitrary here; the per-bin sort orders by the full 64-bit key, which reproduces the reference's
 // stable (tile, depth) radix sort exactly (ties on depth fall back to ascending Gaussian index).
-// With use_hist the CTA first counts its own entries per bin in shared memory, reserves one contiguous
-// range per non-empty bin with a single global atomic, then hands out slots with shared-memory atomics.
+// With use_hist the CTA takes its own per-bin entry counts (kept by the preprocess CTA of the same chunk in
+// cta_hist; counted again here only if that is unavailable), reserves one contiguous range per non-empty bin
+// with a single global atomic, then hands out slots with shared-memory atomics.
 // Item handled by thread t in iteration it of a 2048-item chunk.  Items are spatially ordered, so the 256
 // items of a group fall into very few tile bins; letting the 32 lanes of a warp take 4 items from each of
 // the chunk's 8 groups (instead of 32 neighbours) cuts same-address shared-memory atomic conflicts 8-fold.
@@ -648,7 +689,8 @@ __global__ void __launch_bounds__(256)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                const float4* __restrict__ recA, const float4* __restrict__ recC, const int32_t* __restrict__ rad,
                const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
-               unsigned long long* __restrict__ keys, int64_t cap, int use_hist) {
+               unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
+               const uint32_t* __restrict__ cta_hist) {
   extern __shared__ uint32_t dsm[];
   const int nbl = g.T * g.NB;
   uint32_t* hist = dsm;         // counts, then running slot counters
@@ -656,7 +698,17 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   const int list = blockIdx.y;
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
   const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
-  if (use_hist) {
+  if (use_hist && cta_hist != nullptr) {
+    // the preprocess CTA that walked this chunk left its per-bin counts: no second counting pass
+    const uint32_t* keep = cta_hist + ((size_t)list * gridDim.x + blockIdx.x) * (size_t)(nbl + 1);
+    if (keep[0] == 0u) return;  // whole chunk culled
+    for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
+      const uint32_t c = keep[1 + k];
+      if (c) hbase[k] = bin_off[gb + k] + atomicAdd(&bin_cursor[gb + k], c);
+      hist[k] = 0u;
+    }
+    __syncthreads();
+  } else if (use_hist) {
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
     __syncthreads();
 #pragma unroll 1
@@ -672,7 +724,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
       const uint32_t bk = depth_bucket(depth, g);
       for (int y = rc.y0; y < rc.y1; ++y)
         for (int x = rc.x0; x < rc.x1; ++x) atomicAdd(&hist[(uint32_t)(y * g.gx + x) * (uint32_t)g.NB + bk], 1u);
-    }
+    }  // (per-thread loops: this pass only runs when the preprocess kept no counts)
     __syncthreads();
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
       const uint32_t c = hist[k];
@@ -681,29 +733,45 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     }
     __syncthreads();
   }
-#pragma unroll 1
+  // all loads of the thread's 8 items are issued before the first dependent use (8 independent DRAM round trips
+  // in flight per thread instead of one), then the tile loops run from registers
+  int radius[kItemsPerThread];
+  float ax[kItemsPerThread], ay[kItemsPerThread], dep[kItemsPerThread];
+#pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
     const int64_t i = base + scatter_slot(it, threadIdx.x);
-    if (i >= n_items) continue;
-    const int64_t item = item_base + (int64_t)list * n_items + i;
-    const int radius = rad[item];
-    if (radius <= 0) continue;
-    const float4 a = recA[4 * item];
-    const float depth = recC[4 * item].w;
-    const Rect rc = tile_rect(a.x, a.y, radius, g.gx, g.gy);
-    const uint32_t idx = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
-    const unsigned long long key = ((unsigned long long)__float_as_uint(depth) << 32) | idx;
-    const uint32_t bk = depth_bucket(depth, g);
-    for (int y = rc.y0; y < rc.y1; ++y)
-      for (int x = rc.x0; x < rc.x1; ++x) {
-        const uint32_t b = (uint32_t)(y * g.gx + x) * (uint32_t)g.NB + bk;
-        uint32_t pos;
-        if (use_hist)
-          pos = hbase[b] + atomicAdd(&hist[b], 1u);
-        else
-          pos = bin_off[gb + b] + atomicAdd(&bin_cursor[gb + b], 1u);
-        if ((int64_t)pos < cap) keys[pos] = key;
-      }
+    radius[it] = i < n_items ? rad[item_base + (int64_t)list * n_items + i] : 0;
+  }
+#pragma unroll
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    ax[it] = ay[it] = dep[it] = 0.f;
+    if (radius[it] > 0) {
+      const int64_t item = item_base + (int64_t)list * n_items + base + scatter_slot(it, threadIdx.x);
+      const float4 a = recA[4 * item];
+      ax[it] = a.x;
+      ay[it] = a.y;
+      dep[it] = recC[4 * item].w;
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    Rect rc{0, 0, 0, 0};
+    uint32_t bk = 0, klo = 0, khi = 0;
+    if (radius[it] > 0) {
+      const int64_t i = base + scatter_slot(it, threadIdx.x);
+      rc = tile_rect(ax[it], ay[it], radius[it], g.gx, g.gy);
+      klo = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
+      khi = __float_as_uint(dep[it]);
+      bk = depth_bucket(dep[it], g);
+    }
+    warp_for_each_bin(rc, bk, klo, khi, g.gx, g.NB, [&](uint32_t b, uint32_t lo, uint32_t hi) {
+      uint32_t pos;
+      if (use_hist)
+        pos = hbase[b] + atomicAdd(&hist[b], 1u);
+      else
+        pos = bin_off[gb + b] + atomicAdd(&bin_cursor[gb + b], 1u);
+      if ((int64_t)pos < cap) keys[pos] = ((unsigned long long)hi << 32) | lo;
+    });
   }
 }
 
@@ -923,7 +991,8 @@ constexpr int kIpbStatic = 2048, kIpbDynamic = 2048;
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
-                      const float* pose, int32_t num_slots, cudaStream_t s) {
+                      const float* pose, int32_t num_slots, uint32_t* cta_hist, int* kept_hist, cudaStream_t s) {
+  if (kept_hist) *kept_hist = 0;
   if (n_items <= 0 || n_lists <= 0) return 0;
   auto& w = ctx->ws;
   const size_t hist_b = (size_t)g.T * g.NB * 4;
@@ -952,7 +1021,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     preprocess_kernel<DYN_, IPB_, TMA_><<<grid, 256, sm, s>>>(                                                    \
         ga, n_items, list_base, item_base, g, view, proj, campos, tanfov, frame_env, frame_view, pose, num_slots, \
         w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
-        w.bin_count.as<uint32_t>(), use_hist);                                                                    \
+        w.bin_count.as<uint32_t>(), use_hist, use_hist ? cta_hist : nullptr);                                     \
   } while (0)
   if (dynamic)
     GSW_LAUNCH_PRE(true, kIpbDynamic, false);
@@ -961,14 +1030,23 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
   else
     GSW_LAUNCH_PRE(false, kIpbStatic, false);
 #undef GSW_LAUNCH_PRE
+  if (kept_hist) *kept_hist = use_hist && cta_hist != nullptr;
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
 }
 
+// words of cta_hist one layer needs (0: the bins do not fit a shared-memory histogram, nothing is kept)
+size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g) {
+  if (n_items <= 0 || n_lists <= 0 || (size_t)g.T * g.NB * 4 > kMaxHistBytes) return 0;
+  return (size_t)n_lists * (size_t)((n_items + kItemsPerBlock - 1) / kItemsPerBlock) * (size_t)(g.T * g.NB + 1);
+}
+
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
-                   int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, cudaStream_t s) {
+                   int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
+                   cudaStream_t s) {
   if (n_items <= 0 || n_lists <= 0) return 0;
+  static_assert(kIpbStatic == kItemsPerBlock && kIpbDynamic == kItemsPerBlock, "cta_hist: same chunks in both passes");
   dim3 grid((unsigned)((n_items + kItemsPerBlock - 1) / kItemsPerBlock), (unsigned)n_lists);
   auto& w = ctx->ws;
   const size_t hist_b = (size_t)g.T * g.NB * 8;
@@ -980,13 +1058,13 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
     scatter_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
                                                w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
-                                               use_hist);
+                                               use_hist, cta_hist);
   } else {
     if ((rc = ensure_smem<scatter_kernel<false>>(sm, ctx->device))) return rc;
     scatter_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
                                                 w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
                                                 w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
-                                                use_hist);
+                                                use_hist, cta_hist);
   }
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
