@@ -134,24 +134,46 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     if (ctx->profile) cudaEventRecord(ctx->stage_evt[k], s);
   };
 
+  // The static and the dynamic layer are independent up to the scan and again up to the sort; each kernel alone
+  // leaves SMs idle towards its end (ncu: SMs active 32-59 % of the static kernels' duration), so the static
+  // ones run on a side stream.  With stage profiling on everything stays on `s` so that the stage events
+  // bracket one layer each (the stage times then add up to more than the step).
+  const bool two = ctx->side_stream != nullptr && !ctx->profile && dyn != nullptr && Nm > 0 && Ns > 0;
+  cudaStream_t ss = two ? ctx->side_stream : s;
+  auto fork = [&]() -> int {
+    if (!two) return 0;
+    GSW_CUDA(cudaEventRecord(ctx->fork_evt, s));
+    GSW_CUDA(cudaStreamWaitEvent(ss, ctx->fork_evt, 0));
+    return 0;
+  };
+  auto join = [&]() -> int {
+    if (!two) return 0;
+    GSW_CUDA(cudaEventRecord(ctx->join_evt, ss));
+    GSW_CUDA(cudaStreamWaitEvent(s, ctx->join_evt, 0));
+    return 0;
+  };
   mark(0);
+  if ((rc = fork())) return rc;
   if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
-                              pose, num_slots, ch_s, &kept_s, s)))
+                              pose, num_slots, ch_s, &kept_s, ss)))
     return rc;
   mark(1);
   if (dyn && Nm > 0)
     if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, view, proj, campos, tanfov, frame_env,
                                 frame_view, pose, num_slots, ch_d, &kept_d, s)))
       return rc;
+  if ((rc = join())) return rc;
   mark(2);
   if ((rc = launch_scan_u32(w.bin_count.as<uint32_t>(), w.bin_off.as<uint32_t>(), nbins, w.scan_tmp.as<uint32_t>(),
                             s)))
     return rc;
   mark(3);
-  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, s))) return rc;
+  if ((rc = fork())) return rc;
+  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, ss))) return rc;
   if (dyn && Nm > 0)
     if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, s)))
       return rc;
+  if ((rc = join())) return rc;
   mark(4);
   if ((rc = w.view_cnt.reserve((size_t)V * 4 + 16))) return rc;
   if ((rc = launch_count_views(ctx, V, F, frame_view, s))) return rc;
@@ -217,6 +239,9 @@ int gsw_create(int device, gsw_ctx** out) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
   for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->grp_evt[k], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->copy_evt, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->fork_evt, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->join_evt, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_error("gsw_create: %s", cudaGetErrorString(e));
     delete c;
@@ -244,6 +269,9 @@ int gsw_destroy(gsw_ctx* c) {
     if (c->grp_evt[k]) cudaEventDestroy(c->grp_evt[k]);
   if (c->copy_evt) cudaEventDestroy(c->copy_evt);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->fork_evt) cudaEventDestroy(c->fork_evt);
+  if (c->join_evt) cudaEventDestroy(c->join_evt);
+  if (c->side_stream) cudaStreamDestroy(c->side_stream);
   for (int k = 0; k <= kNumStages; ++k)
     if (c->stage_evt[k]) cudaEventDestroy(c->stage_evt[k]);
   delete c;

@@ -165,6 +165,10 @@ struct gsw_ctx {
   cudaStream_t copy_stream = nullptr;  // device->host delivery of finished frame groups (host_rgb_u8)
   cudaEvent_t grp_evt[4] = {};
   cudaEvent_t copy_evt = nullptr;
+  // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are
+  // independent until the scan / the sort, and each leaves a good part of the SMs idle on its own
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t fork_evt = nullptr, join_evt = nullptr;
   int64_t launches = 0;
 };
 
