@@ -578,14 +578,25 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
   uint32_t* ticket = w.status.as<uint32_t>() + 16;  // three more: work tickets of the medium / small / mid sort
   classify_bins_kernel<<<(unsigned)((nbins + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, cap, Q,
                                                                       w.status.as<long long>());
-  refine_big_bins_kernel<<<148 * 2, 512, 0, s>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
-                                                 w.status.as<long long>());
+  // the depth partition of the huge bins (one CTA per bin, half the SMs idle) runs on the side stream next to
+  // the small-class sort, which does not depend on it; the mid / medium queues it appends to are sorted after
+  cudaStream_t ss = ctx->side_stream ? ctx->side_stream : s;
+  if (ss != s) {
+    GSW_CUDA(cudaEventRecord(ctx->fork_evt, s));
+    GSW_CUDA(cudaStreamWaitEvent(ss, ctx->fork_evt, 0));
+  }
+  refine_big_bins_kernel<<<148 * 2, 512, 0, ss>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
+                                                  w.status.as<long long>());
+  sort_segments_kernel<kSmallKeys, 64><<<148 * 16, 64, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
+                                                                      w.keys.as<unsigned long long>(), ticket + 1);
+  if (ss != s) {
+    GSW_CUDA(cudaEventRecord(ctx->join_evt, ss));
+    GSW_CUDA(cudaStreamWaitEvent(s, ctx->join_evt, 0));
+  }
   sort_segments_kernel<kSortSmemKeys, 256><<<148 * 4, 256, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
                                                                         w.keys.as<unsigned long long>(), ticket);
   sort_segments_kernel<kMidKeys, 128><<<148 * 8, 128, 2 * smem_s, s>>>(Q.q[3], Q.count + 3, Q.cap[3],
                                                                       w.keys.as<unsigned long long>(), ticket + 2);
-  sort_segments_kernel<kSmallKeys, 64><<<148 * 16, 64, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
-                                                                      w.keys.as<unsigned long long>(), ticket + 1);
   count_launches(5);
   GSW_CUDA(cudaGetLastError());
   return 0;
