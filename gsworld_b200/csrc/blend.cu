@@ -240,26 +240,29 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
         const float4 b = lds128(ra + 16);
         const float dx = xy.x - pxf, dy = xy.y - pyf;
         const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
-        if (p2 > 0.0f) continue;
-        const float alpha = fminf(0.99f, b.w * ex2_approx(p2));
-        if (alpha < 1.0f / 255.0f) continue;
-        const float test_T = Tacc * (1 - alpha);
-        if (test_T < 0.0001f) {  // saturated (or already saturated: Tacc == 0)
-          Tacc = 0.0f;
-          continue;
-        }
+        // Branch-free form of the reference's three tests (power > 0 -> skip; alpha < 1/255 -> skip;
+        // T(1-alpha) < 1e-4 -> done): a skipped record takes alpha = 0, which leaves T unchanged bit for bit,
+        // and the accumulation is predicated.  The warp executes the union of its lanes' paths either way, so
+        // the divergent branches only cost issue slots (ncu source view: 16 % of the kernel's instructions).
         const float4 c = lds128(ra + 32);
+        float alpha = fminf(0.99f, b.w * ex2_approx(p2));
+        const bool skip = (p2 > 0.0f) || (alpha < 1.0f / 255.0f);
+        alpha = skip ? 0.0f : alpha;
+        const float test_T = Tacc * (1 - alpha);
+        const bool sat = test_T < 0.0001f;  // saturated now, or already (Tacc == 0)
         const float wgt = alpha * Tacc;
-        C0 += c.x * wgt;
-        C1 += c.y * wgt;
-        C2 += c.z * wgt;
-        invd += c.w * wgt;
-        if (SEG && wgt > best_w) {
-          best_w = wgt;
-          best_lab = sLab[qi];
+        if (!skip && !sat) {
+          C0 += c.x * wgt;
+          C1 += c.y * wgt;
+          C2 += c.z * wgt;
+          invd += c.w * wgt;
+          if (SEG && wgt > best_w) {
+            best_w = wgt;
+            best_lab = sLab[qi];
+          }
+          Tout = test_T;
         }
-        Tacc = test_T;
-        Tout = test_T;
+        Tacc = sat ? 0.0f : test_T;
       }
     }
   }
