@@ -55,8 +55,8 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
 }
 
 template <bool SEG>
-__global__ void __launch_bounds__(256)
-blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
+__device__ __forceinline__ void
+blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
              int32_t f_begin,
              const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats, int64_t cap, FrameGeom g,
              float bg0, float bg1, float bg2, const float* __restrict__ bg_dev, uint8_t* __restrict__ out_u8,
@@ -294,6 +294,41 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   }
 }
 
+// The kernel proper: blend_body, then (delivery to the host only) the group-completion signal.
+template <bool SEG>
+__global__ void __launch_bounds__(256, 5)  // 48 registers: five CTAs per SM
+blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
+             int32_t f_begin, const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats,
+             int64_t cap, FrameGeom g, float bg0, float bg1, float bg2, const float* __restrict__ bg_dev,
+             uint8_t* __restrict__ out_u8, float* __restrict__ out_color, float* __restrict__ out_invd,
+             long long* __restrict__ status, int mode, const uint32_t* __restrict__ view_cnt,
+             const uint8_t* __restrict__ st_u8, const float* __restrict__ st_color,
+             const float* __restrict__ st_invd, const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg,
+             const int32_t* __restrict__ st_seg, int use_view_images, const float4* __restrict__ rec,
+             const int32_t* __restrict__ pos_of, int64_t Ns, const int32_t* __restrict__ labels, int64_t Nm,
+             DoneSig sig) {
+  blend_body<SEG>(bin_off, nbins, frame_view, V, f_begin, keys, splats, cap, g, bg0, bg1, bg2, bg_dev, out_u8,
+                  out_color, out_invd, status, mode, view_cnt, st_u8, st_color, st_invd, lab_stream, out_seg, st_seg,
+                  use_view_images, rec, pos_of, Ns, labels, Nm);
+  if (sig.cnt != nullptr) {
+    // every thread's pixel stores precede the barrier; thread 0's fence makes them visible device-wide (and to
+    // the copy engine) before the counter moves; the CTA that completes a group publishes the epoch
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int f = (int)(((int64_t)f_begin * g.T + blockIdx.x) / g.T);
+      int k = 0;
+      while (k + 1 < sig.n && f >= sig.cut(k + 1)) ++k;
+      const uint32_t ctas = (uint32_t)(sig.cut(k + 1) - sig.cut(k)) * (uint32_t)g.T;
+      __threadfence();
+      if (atomicAdd(&sig.cnt[k], 1u) == ctas - 1u) {
+        __threadfence();
+        *reinterpret_cast<volatile uint32_t*>(&sig.flag[k]) = sig.epoch;
+      }
+    }
+  }
+}
+
+
 __global__ void count_view_frames_kernel(int32_t F, const int32_t* __restrict__ frame_view, uint32_t* view_cnt) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f < F) atomicAdd(&view_cnt[frame_view[f]], 1u);
@@ -326,7 +361,7 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
       want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
       w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
       want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr, 0, w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns,    \
-      ctx->labels, ctx->last.Nm)
+      ctx->labels, ctx->last.Nm, DoneSig{})
   if (want_seg)
     GSW_VIEW_PASS(true);
   else
@@ -341,17 +376,19 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
 // `share`: the view pass ran for this launch set, static-only tiles of shared views are copied from it
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view,
                  int64_t cap, const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8,
-                 float* out_color, float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s) {
+                 float* out_color, float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s,
+                 const DoneSig* sig) {
   const int64_t FT = (int64_t)F * g.T;
   if (FT <= 0) return 0;
   auto& w = ctx->ws;
+  const DoneSig sg = sig ? *sig : DoneSig{};
 #define GSW_BLEND(SEG_)                                                                                            \
   blend_kernel<SEG_><<<(unsigned)FT, 256, 0, s>>>(                                                                   \
       w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), \
       cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
       w.status.as<long long>(), 0, w.view_cnt.as<uint32_t>(), w.st_u8.as<uint8_t>(), w.st_color.as<float>(),          \
       w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>(), share ? 1 : 0,              \
-      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm)
+      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm, sg)
   if (out_seg)
     GSW_BLEND(true);
   else

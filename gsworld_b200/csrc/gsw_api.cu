@@ -1,4 +1,5 @@
 // gsw_api.cu — extern "C" entry points of libgsw.so and launch orchestration.  See include/gsw.h.
+#include <cuda.h>  // types of the one driver entry point used (cuStreamWaitValue32); libcuda is not linked
 #include <algorithm>
 #include <atomic>
 #include <cstdarg>
@@ -237,8 +238,20 @@ int gsw_create(int device, gsw_ctx** out) {
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->done_evt, cudaEventDisableTiming);
   for (int k = 0; k <= kNumStages && e == cudaSuccess; ++k) e = cudaEventCreate(&c->stage_evt[k]);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
-  for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->grp_evt[k], cudaEventDisableTiming);
+  for (int k = 0; k < 5 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->grp_evt[k], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->copy_evt, cudaEventDisableTiming);
+  if (e == cudaSuccess) {
+    // stream memory operation used for in-kernel completion signals (no link-time dependency on libcuda)
+    cudaDriverEntryPointQueryResult qr = cudaDriverEntryPointSymbolNotFound;
+    void* fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess && getenv("GSW_NO_WAIT_VALUE") == nullptr)
+      c->wait_value32 = fn;
+    else
+      (void)cudaGetLastError();
+    if (c->sig.reserve(2 * kMaxSigGroups * sizeof(uint32_t)) != 0) c->wait_value32 = nullptr;
+    else e = cudaMemset(c->sig.p, 0, 2 * kMaxSigGroups * sizeof(uint32_t));
+  }
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->fork_evt, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->join_evt, cudaEventDisableTiming);
@@ -258,14 +271,14 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
   for (DevBuf* b : bufs) b->release();
   if (c->h_status) cudaFreeHost(c->h_status);
   if (c->done_evt) cudaEventDestroy(c->done_evt);
-  for (int k = 0; k < 4; ++k)
+  for (int k = 0; k < 5; ++k)
     if (c->grp_evt[k]) cudaEventDestroy(c->grp_evt[k]);
   if (c->copy_evt) cudaEventDestroy(c->copy_evt);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
@@ -515,13 +528,54 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                                      d->out_invdepth != nullptr, d->out_seg != nullptr, s)))
       return rc;
   }
-  if (d->host_rgb_u8 && d->out_rgb_u8) {
-    // blend in up to 4 frame groups; each group's uint8 frames go to the pinned host buffer on the copy stream
-    // as soon as that group is done, while the next group is being composited
-    const int G = d->num_frames < 4 ? d->num_frames : 4;
+  if (d->host_rgb_u8 && d->out_rgb_u8 && c->wait_value32 != nullptr) {
+    // ONE blend launch; the frames are cut into groups, the last CTA of a group to finish publishes the launch
+    // epoch in the group's flag, and the copy stream waits on that flag (stream memory operation) before it
+    // sends the group's uint8 frames to the pinned host buffer.  Delivery overlaps the compositing of the later
+    // frames without splitting the launch (every extra launch costs a tail of half-empty SMs).
+    typedef CUresult (*wait_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+    const wait_fn wait32 = reinterpret_cast<wait_fn>(c->wait_value32);
+    DoneSig sg;
+    sg.n = d->num_frames < 8 ? d->num_frames : 8;
+    sg.cnt = c->sig.as<uint32_t>();
+    sg.flag = c->sig.as<uint32_t>() + kMaxSigGroups;
+    sg.epoch = ++c->sig_epoch;
+    sg.F = d->num_frames;
+    GSW_CUDA(cudaMemsetAsync(sg.cnt, 0, kMaxSigGroups * sizeof(uint32_t), s));
+    if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
+                           nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s, &sg)))
+      return rc;
+    const size_t frame_bytes = (size_t)d->height * d->width * 3;
+    for (int k = 0; k < sg.n; ++k) {
+      const CUresult wr = c->wait_value32 == nullptr
+                              ? CUDA_SUCCESS
+                              : wait32((CUstream)c->copy_stream, (CUdeviceptr)(uintptr_t)(sg.flag + k), sg.epoch,
+                                       CU_STREAM_WAIT_VALUE_GEQ);
+      if (wr != CUDA_SUCCESS && c->wait_value32 != nullptr) {
+        // not supported here (e.g. a restricted driver mode): order the remaining copies after the whole blend
+        // launch instead, and use the grouped launches from the next call on
+        c->wait_value32 = nullptr;
+        GSW_CUDA(cudaEventRecord(c->grp_evt[0], s));
+        GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[0], 0));
+      }
+      GSW_CUDA(cudaMemcpyAsync(d->host_rgb_u8 + (size_t)sg.cut(k) * frame_bytes,
+                               d->out_rgb_u8 + (size_t)sg.cut(k) * frame_bytes,
+                               (size_t)(sg.cut(k + 1) - sg.cut(k)) * frame_bytes, cudaMemcpyDeviceToHost,
+                               c->copy_stream));
+    }
+    GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
+    GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+  } else if (d->host_rgb_u8 && d->out_rgb_u8) {
+    // blend in up to 5 frame groups; each group's uint8 frames go to the pinned host buffer on the copy stream
+    // as soon as that group is done, while the next group is being composited.  The last groups are small:
+    // only the final group's copy is not hidden behind a blend launch.
+    static const int kCut[6] = {0, 32, 64, 96, 116, 128};  // of 128
+    const int G = d->num_frames < 5 ? d->num_frames : 5;
     const size_t frame_bytes = (size_t)d->height * d->width * 3;
     for (int k = 0; k < G; ++k) {
-      const int f0 = (int)((int64_t)d->num_frames * k / G), f1 = (int)((int64_t)d->num_frames * (k + 1) / G);
+      const int f0 = G < 5 ? k : (int)((int64_t)d->num_frames * kCut[k] / 128);
+      const int f1 = G < 5 ? k + 1 : (int)((int64_t)d->num_frames * kCut[k + 1] / 128);
+      if (f1 <= f0) continue;
       if ((rc = launch_blend(c, d->num_views, f0, f1 - f0, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
                              nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s)))
         return rc;

@@ -46,6 +46,20 @@ struct Splat {
   float4 a, b, c;
 };
 
+// Completion signals of the blend launch, for delivering finished frame groups to the host while later
+// frames are still being composited (gsw_render_frames with host_rgb_u8).  The F frames are cut into n groups,
+// group k = frames [cut(k), cut(k+1)); the last CTA of a group to finish publishes `epoch` in flag[group], on
+// which the copy stream waits with a stream memory operation.  cnt == nullptr: no signalling.
+// (No array member: a dynamically indexed kernel parameter is copied to local memory by every thread.)
+constexpr int kMaxSigGroups = 16;
+struct DoneSig {
+  uint32_t* cnt = nullptr;   // [n] finished CTAs per group (zeroed before the launch)
+  uint32_t* flag = nullptr;  // [n] last epoch whose group is complete
+  uint32_t epoch = 0;
+  int32_t n = 0, F = 0;
+  __host__ __device__ int32_t cut(int k) const { return (int32_t)((int64_t)F * k / n); }
+};
+
 #ifdef __CUDACC__
 // Preprocess record (64 B item slot {px,py,hx,hy | conic,opacity | r,g,b,depth}) -> blend record.  The conic is
 // pre-scaled so the blend evaluates alpha = o * 2^(A' dx^2 + B' dx dy + C' dy^2) with A' = -0.5 log2(e) A,
@@ -163,7 +177,10 @@ struct gsw_ctx {
   cudaEvent_t stage_evt[gsw::kNumStages + 1] = {};
   cudaEvent_t done_evt = nullptr;
   cudaStream_t copy_stream = nullptr;  // device->host delivery of finished frame groups (host_rgb_u8)
-  cudaEvent_t grp_evt[4] = {};
+  cudaEvent_t grp_evt[5] = {};
+  void* wait_value32 = nullptr;  // cuStreamWaitValue32 (driver entry point; null: grouped blend launches instead)
+  gsw::DevBuf sig;               // DoneSig counters [16] + flags [16]
+  uint32_t sig_epoch = 0;
   cudaEvent_t copy_evt = nullptr;
   // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are
   // independent until the scan / the sort, and each leaves a good part of the SMs idle on its own
@@ -209,7 +226,7 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
 // blend.cu
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
                  const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
-                 float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s);
+                 float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s, const DoneSig* sig = nullptr);
 int launch_count_views(const gsw_ctx* ctx, int32_t V, int32_t F, const int32_t* frame_view, cudaStream_t s);
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
