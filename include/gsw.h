@@ -103,10 +103,14 @@ typedef struct gsw_frames_desc {
   float* out_color;          /* [F,3,H,W] or NULL: un-clamped C + T*bg as the rasterizer returns it */
   float* out_invdepth;       /* [F,1,H,W] or NULL */
   int32_t* out_radii;        /* [F,N] or NULL */
-  uint8_t* host_rgb_u8;      /* HOST pinned [F,H,W,3] or NULL: needs out_rgb_u8; the frames are blended in up to 4
-                              * groups and each group is copied device->host on the context's copy stream as soon
-                              * as it is done, overlapping the copy with the blending of the next group.  `stream`
-                              * waits for the last copy, so synchronising `stream` makes the host buffer valid. */
+  uint8_t* host_rgb_u8;      /* HOST pinned [F,H,W,3] or NULL: needs out_rgb_u8.  The frames are delivered device->host
+                              * in up to 8 groups on the context's copy stream while later frames are still being
+                              * composited: the blend stays one launch, the last CTA of a group publishes a flag and
+                              * the copy stream waits on it with a stream memory operation (cuStreamWaitValue32).
+                              * Where the driver refuses that operation, or with GSW_NO_WAIT_VALUE set in the
+                              * environment at gsw_create, the frames are blended in up to 5 launches with an event per
+                              * group instead.  `stream` waits for the last copy, so synchronising `stream` makes the
+                              * host buffer valid. */
   int32_t* out_seg;          /* [F,H,W] or NULL: label (gsw_scene_set_labels) of the Gaussian with the largest blending
                               * weight alpha*T at each pixel, GSW_SEG_NONE where nothing was composited.  No counterpart
                               * in the reference (its segmentation comes from SAPIEN's Vulkan renderer, unavailable

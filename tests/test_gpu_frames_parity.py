@@ -149,20 +149,29 @@ def test_wrapper_from_ply_config_and_inverse_depth_obs(tmp_path):
         assert d.shape == (2, 48, 48, 1) and d.dtype == torch.float32 and float(d.min()) >= 0.0 and float(d.max()) > 0.0
 
 
-def test_host_delivery_matches_device_output():
-    """gsw_frames_desc.host_rgb_u8: the grouped blend + overlapped device->host copies must deliver exactly the
-    frames the single-launch path leaves on the device (also with a frame count that does not divide by 4)."""
-    scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", 3, (64, 48), ("006_mustard_bottle",), True)
-    obs, _ = wrap.reset(seed=5)
-    torch.cuda.synchronize()
-    want = {c: obs["sensor_data"][c]["rgb"].clone() for c in env.cameras}
-    pinned = torch.zeros((len(env.cameras), 3, 64, 48, 3), dtype=torch.uint8).pin_memory()
-    wrap.obs_host = pinned
-    out = wrap._render_gsworld()
-    torch.cuda.current_stream().synchronize()
-    for i, c in enumerate(env.cameras):
-        assert torch.equal(out[c].cpu(), want[c].cpu())
-        assert torch.equal(pinned[i], want[c].cpu())
+@pytest.mark.parametrize("B,wait_value", [(3, True), (3, False), (11, True)])
+def test_host_delivery_matches_device_output(B, wait_value, monkeypatch):
+    """gsw_frames_desc.host_rgb_u8: delivery overlapped with the blend must hand the host exactly the frames the
+    plain path leaves on the device.  wait_value=True: one blend launch + in-kernel group flags + a stream memory
+    wait on the copy stream (frame counts below and above the 8 groups); False: the fallback, grouped launches
+    with events.  Several steps in a row, so the epoch / counters are reused."""
+    if not wait_value:
+        monkeypatch.setenv("GSW_NO_WAIT_VALUE", "1")  # read by gsw_create
+    scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", B, (64, 48), ("006_mustard_bottle",), True)
+    wrap.reset(seed=5)
+    pinned = torch.zeros((len(env.cameras), B, 64, 48, 3), dtype=torch.uint8).pin_memory()
+    for _ in range(3):
+        wrap.obs_host = None
+        obs = wrap.step(None)[0]
+        torch.cuda.synchronize()
+        want = {c: obs["sensor_data"][c]["rgb"].clone() for c in env.cameras}
+        pinned.zero_()
+        wrap.obs_host = pinned
+        out = wrap._render_gsworld()
+        torch.cuda.current_stream().synchronize()
+        for i, c in enumerate(env.cameras):
+            assert torch.equal(out[c].cpu(), want[c].cpu())
+            assert torch.equal(pinned[i], want[c].cpu())
 
 
 def test_cfg4_like_pour_mustard_objects_128():
