@@ -192,6 +192,29 @@ def traffic_of(stage):
         return None
 
 
+def issue_roofline(stage_ms, sm_mhz):
+    """The blend against the bound it actually has: warp instructions issued per second vs the SMs' issue
+    capacity (148 SMs x 4 schedulers x 1 warp instruction per clock).  Instruction count per step from the
+    committed ncu capture (same command, same workload), kernel time measured live."""
+    try:
+        inst = 0.0
+        with open(os.path.join(ROOT, "profiles", "r01_ncu_full_strict.txt")) as f:
+            hdr = [h.split("[")[0].strip() for h in f.readline().split("|")]
+            for ln in f:
+                c = [x.strip() for x in ln.split("|")]
+                if c and c[0].startswith("blend_kernel"):
+                    inst += float(c[hdr.index("warp_inst")])
+        if inst <= 0 or stage_ms <= 0:
+            return None
+        peak = 148 * 4 * (sm_mhz or 1965.0) * 1e6 / 1e9
+        ach = inst / (stage_ms * 1e-3) / 1e9
+        return {"bound": "sm_issue", "kernel": "blend", "achieved": ach, "peak": peak, "unit": "G warp-inst/s",
+                "frac": ach / peak, "warp_inst_per_step": inst,
+                "source": "instruction count: profiles/r01_ncu_full_strict.txt; time: live stage events"}
+    except Exception:
+        return None
+
+
 def hbm_roofline(stages, alg, peak):
     """The largest HBM-facing stage (the dominant kernel, blend, is bound by the SM issue rate instead)."""
     cands = {k: stages[k] for k in ("gather", "scatter", "preprocess_static", "preprocess_dynamic") if stages.get(k, 0) > 0}
@@ -449,6 +472,8 @@ def run_ours(args):
         eng = wrap._engine
         if os.environ.get("GSW_NB"):
             eng.set_depth_buckets(int(os.environ["GSW_NB"]))
+        if os.environ.get("GSW_TILE_CULL"):
+            eng.set_tile_culling(os.environ["GSW_TILE_CULL"] == "1")
         if mode == "strict":
             sampler = ClockSampler(local) if rank == 0 else None
             timed(env, wrap, 0, args.warmup)
@@ -562,6 +587,7 @@ def run_ours(args):
                                   "not by HBM; its HBM fraction is low by construction (profiles/README.md)")
                          if dom == "blend" else None},
             "roofline_hbm_kernel": hbm_roofline(stages, alg, peak),
+            "roofline_issue": issue_roofline(stages.get("blend", 0.0), (r["clocks"] or {}).get("sm_mhz")),
             "stages_ms": {k: round(v, 4) for k, v in stages.items()},
             "stages_note": "measured with the stages serialised on one stream; the timed step runs the static-layer "
                            "kernels on a side stream next to the dynamic-layer ones, so the sum exceeds ms_per_step",

@@ -40,6 +40,7 @@ SYMBOLS = {
     "gsw_finish": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64 * 4)]),
     "gsw_reserve_entries": (C.c_int, [_vp, _i64]),
     "gsw_set_depth_buckets": (C.c_int, [_vp, C.c_int]),
+    "gsw_set_tile_culling": (C.c_int, [_vp, C.c_int]),
     "gsw_rasterize_forward": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f, _vp,
                                         _vp, _vp, _vp, _vp, _f, _f, _i32, _i32, _f, _vp, _vp, _vp, _vp]),
     "gsw_rasterize_forward_static": (C.c_int, [_i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp,

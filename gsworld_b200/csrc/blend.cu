@@ -80,8 +80,9 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
   __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
   __shared__ int32_t sLab[SEG ? kChunk : 1];
-  const int64_t ft = (int64_t)f_begin * g.T + blockIdx.x;
-  const int f = (int)(ft / g.T), tile = (int)(ft % g.T);
+  // 32-bit unsigned division (the grid is f-major: blockIdx.x = (f - f_begin) * T + tile)
+  const uint32_t fl = blockIdx.x / (uint32_t)g.T;
+  const int f = f_begin + (int)fl, tile = (int)(blockIdx.x - fl * (uint32_t)g.T);
   const int tx = tile % g.gx, ty = tile / g.gx;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int wx = tx * kTile + (w & 1) * 8, wy = ty * kTile + (w >> 1) * 4;
@@ -92,12 +93,14 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
 
   const int v = mode == 1 ? f : (frame_view ? frame_view[f] : 0);
   if (mode == 1 && view_cnt[v] < 2u) return;  // view used by a single frame: nothing to share
-  const int64_t sb = ((int64_t)v * g.T + tile) * g.NB, db = ((int64_t)(V + f) * g.T + tile) * g.NB;
+  // bin indices fit 32 bits (run_pipeline rejects launches with 2^31 bins or more)
+  const uint32_t sb = ((uint32_t)v * (uint32_t)g.T + (uint32_t)tile) * (uint32_t)g.NB;
+  const uint32_t db = ((uint32_t)(V + f) * (uint32_t)g.T + (uint32_t)tile) * (uint32_t)g.NB;
   const uint32_t s0 = bin_off[sb], d0 = mode == 1 ? 0u : bin_off[db];
   uint32_t ns = bin_off[sb + g.NB] - s0, nd = mode == 1 ? 0u : bin_off[db + g.NB] - d0;
   const uint32_t D = bin_off[nbins];
   if ((int64_t)D > cap) ns = nd = 0;  // workspace overflow: lists are incomplete; the launch is flagged invalid
-  if (mode == 0 && ft == 0 && threadIdx.x == 0) {
+  if (mode == 0 && f == 0 && tile == 0 && threadIdx.x == 0) {
     status[0] = (long long)D;
     if ((int64_t)D > cap) status[2] = 1;
   }
@@ -315,7 +318,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
     // the copy engine) before the counter moves; the CTA that completes a group publishes the epoch
     __syncthreads();
     if (threadIdx.x == 0) {
-      const int f = (int)(((int64_t)f_begin * g.T + blockIdx.x) / g.T);
+      const int f = f_begin + (int)(blockIdx.x / (uint32_t)g.T);
       int k = 0;
       while (k + 1 < sig.n && f >= sig.cut(k + 1)) ++k;
       const uint32_t ctas = (uint32_t)(sig.cut(k + 1) - sig.cut(k)) * (uint32_t)g.T;

@@ -72,6 +72,7 @@ FrameGeom make_geom(int H, int W, int nb, int antialiasing, float scale_modifier
   g.nb_shift = kDepthSpanLog2 - ilog2(nb);
   g.antialiasing = antialiasing;
   g.prefiltered = 0;
+  g.tile_cull = 0;
   g.scale_modifier = scale_modifier;
   g.near_plane = near_plane;
   return g;
@@ -455,6 +456,15 @@ int gsw_set_depth_buckets(gsw_ctx* c, int nb) {
   return GSW_OK;
 }
 
+int gsw_set_tile_culling(gsw_ctx* c, int on) {
+  if (!c) {
+    set_error("gsw_set_tile_culling: NULL ctx");
+    return GSW_E_INVALID;
+  }
+  c->tile_cull = on ? 1 : 0;
+  return GSW_OK;
+}
+
 int gsw_reserve_entries(gsw_ctx* c, int64_t entries) {
   if (!c || entries < 0) {
     set_error("gsw_reserve_entries: invalid argument");
@@ -491,7 +501,8 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   Guard gd(c->device);
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = c->nb_user > 0 ? c->nb_user : 1;
-  const FrameGeom g = make_geom(d->height, d->width, nb, d->antialiasing, d->scale_modifier, d->near_plane);
+  FrameGeom g = make_geom(d->height, d->width, nb, d->antialiasing, d->scale_modifier, d->near_plane);
+  g.tile_cull = c->tile_cull;
 
   GaussArrays dyn{};
   dyn.xyz = c->mov_xyz.as<float>();
@@ -737,7 +748,8 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   Guard gd(c->device);
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = c->nb_user > 0 ? c->nb_user : 1;
-  const FrameGeom g = make_geom(height, width, nb, antialiasing, scale_modifier, near_plane);
+  FrameGeom g = make_geom(height, width, nb, antialiasing, scale_modifier, near_plane);
+  g.tile_cull = c->tile_cull;
   GaussArrays st{};
   st.xyz = means3D;
   st.scale_act = scales;

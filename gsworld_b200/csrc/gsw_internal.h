@@ -103,6 +103,7 @@ struct FrameGeom {
   int32_t NB, nb_shift;     // depth sub-buckets per tile, shift applied to (depth_bits - kDepthLo)
   int32_t antialiasing;
   int32_t prefiltered;
+  int32_t tile_cull;  // drop (Gaussian, tile) entries that provably stay below alpha 1/255 on the whole tile
   float scale_modifier;
   float near_plane;
 };
@@ -158,6 +159,7 @@ struct gsw_ctx {
   gsw::Workspace ws;
   int64_t cap_entries = 0;  // capacity of [sorted lists | merged lists] combined
   int nb_user = 0;
+  int tile_cull = 0;  // gsw_set_tile_culling
   // last launch
   struct {
     bool valid = false;

@@ -67,6 +67,69 @@ __device__ __forceinline__ Rect tile_rect(float px, float py, int radius, int gx
   return q;
 }
 
+// ---- exact tile culling (FrameGeom::tile_cull) ----
+// The reference duplicates a Gaussian into every tile of the bounding square of its 3-sigma radius.  Many of
+// those (Gaussian, tile) entries never do anything: on all 256 pixels of the tile alpha stays below 1/255 (or
+// power > 0), and the reference's blend loop `continue`s past them without touching any state.  Dropping such
+// an entry before it is binned therefore leaves every pixel bit-identical, and saves its scatter, sort,
+// staging and cull work.  The test is the one the blend applies per warp (blend.cu), on the whole tile:
+// the largest power over the tile's pixel centres is reached at the centre if it is inside, else on one of
+// the two tile edges facing it (moving any tile point towards the centre along its ray lowers the convex
+// form and stays in the tile until one of those edges is hit).  Margins (0.2 % + 0.02 on the log side) keep
+// it conservative against ex2.approx / FMA differences in the blend; any NaN keeps the entry.
+struct Foot {
+  float px, py, hx, hy;  // centre (pixels), half extents of the alpha >= 1/255 box (-1: never visible, 3e38: unknown)
+  float A, B, C;         // conic: power = -0.5 (A dx^2 + C dy^2) - B dx dy
+  float kyx, kxy;        // -B/C, -B/A: the y (x) that maximises the power on a line of fixed x (y)
+  float t;               // ln(255 opacity) with margin: entries with max power < -t are dead
+};
+
+// (make_foot is evaluated with identical inputs and code by the preprocess and the scatter pass.)
+__device__ __forceinline__ Foot make_foot(float px, float py, float hx, float hy, float A, float B, float C,
+                                          float opac) {
+  Foot f;
+  f.px = px; f.py = py; f.hx = hx; f.hy = hy; f.A = A; f.B = B; f.C = C;
+  f.kyx = -B / C;
+  f.kxy = -B / A;
+  f.t = logf(255.0f * opac) * 1.002f + 0.02f;
+  return f;
+}
+
+__device__ __forceinline__ bool tile_alive(const Foot& f, int tx, int ty) {
+  if (f.hx < 0.f) return false;
+  const float bx0 = (float)(tx * kTile), bx1 = bx0 + (float)(kTile - 1);
+  const float by0 = (float)(ty * kTile), by1 = by0 + (float)(kTile - 1);
+  if (f.px + f.hx < bx0 || f.px - f.hx > bx1 || f.py + f.hy < by0 || f.py - f.hy > by1) return false;
+  if (f.hx >= 1.0e30f) return true;
+  const float x0 = bx0 - f.px, x1 = bx1 - f.px, y0 = by0 - f.py, y1 = by1 - f.py;
+  const float xe = fminf(fmaxf(0.f, x0), x1), ye = fminf(fmaxf(0.f, y0), y1);
+  const float ys = fminf(fmaxf(f.kyx * xe, y0), y1);
+  const float xs = fminf(fmaxf(f.kxy * ye, x0), x1);
+  const float p1 = -0.5f * (f.A * xe * xe + f.C * ys * ys) - f.B * xe * ys;
+  const float p2 = -0.5f * (f.A * xs * xs + f.C * ye * ye) - f.B * xs * ye;
+  return !(fmaxf(p1, p2) < -f.t);
+}
+
+// Tiles of rc that can pass tile_alive's box test (the alpha >= 1/255 box is usually much smaller than the
+// bounding square of the 3-sigma radius that rc comes from): the loops below only visit these.  Part of the
+// decision (both passes call it), not just a shortcut.
+__device__ __forceinline__ Rect alive_rect(const Foot& f, const Rect rc) {
+  Rect q = rc;
+  if (f.hx < 0.f) {
+    q.x1 = q.x0;
+    q.y1 = q.y0;
+  } else if (f.hx < 1.0e30f) {
+    const float s = 1.0f / (float)kTile;  // exact scaling
+    q.x0 = max(rc.x0, (int)ceilf((f.px - f.hx - (float)(kTile - 1)) * s));
+    q.x1 = min(rc.x1, (int)floorf((f.px + f.hx) * s) + 1);
+    q.y0 = max(rc.y0, (int)ceilf((f.py - f.hy - (float)(kTile - 1)) * s));
+    q.y1 = min(rc.y1, (int)floorf((f.py + f.hy) * s) + 1);
+    if (q.x1 < q.x0) q.x1 = q.x0;
+    if (q.y1 < q.y0) q.y1 = q.y0;
+  }
+  return q;
+}
+
 __device__ __forceinline__ uint32_t depth_bucket(float depth, const FrameGeom& g) {
   const uint32_t bits = __float_as_uint(depth);
   if (bits <= kDepthLo) return 0u;
@@ -108,12 +171,15 @@ constexpr size_t kMaxHistBytes = 160 * 1024;         // per-CTA shared histogram
 
 // Per-item body.  `hist` (shared, one counter per (tile, bucket) of this list) may be null, in which case
 // the global bin counters are hit directly.
-template <bool DYN>
+template <bool DYN, bool CULL>
 __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const GaussArrays& la, int64_t i, int64_t il, int64_t item, int list_global,
                                                 const FrameGeom& g, const ViewSmem& vs, const float* pose_s,
                                                 float4* __restrict__ recA, float4* __restrict__ recB,
                                                 float4* __restrict__ recC, int32_t* __restrict__ rad,
-                                                uint32_t* __restrict__ bin_count, uint32_t* hist) {
+                                                uint32_t* __restrict__ bin_count, uint32_t* hist, Rect& out_rc,
+                                                uint32_t& out_bk, Foot& out_ft) {
+  // CULL: the caller counts the Gaussian into its bins (warp-cooperatively, with the exact tile test) from
+  // out_rc / out_bk / out_ft, which stay empty on every early return
   if (!DYN && la.slot != nullptr && la.slot[il] >= 0) {  // movable: handled by the dynamic layer
     rad[item] = 0;
     return;
@@ -353,6 +419,13 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   // (per-thread loop: here the imbalance between one-tile and hundred-tile Gaussians hides behind the other
   // warps' arithmetic; the warp-cooperative form measured slower in this kernel, faster in the scatter)
   const uint32_t bk = depth_bucket(pvz, g);
+  if (CULL) {
+    const Foot ft = make_foot(px, py, hx, hy, conx, cony, conz, opac);
+    out_rc = rc;
+    out_bk = bk;
+    out_ft = ft;
+    return;
+  }
   if (hist != nullptr) {
     for (int y = rc.y0; y < rc.y1; ++y)
       for (int x = rc.x0; x < rc.x1; ++x) atomicAdd(&hist[(uint32_t)(y * g.gx + x) * (uint32_t)g.NB + bk], 1u);
@@ -369,6 +442,8 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
 // leaves 31 lanes waiting, and whole CTAs trail the kernel (ncu: SMs active 30 % of the scatter's duration).
 // Used by the scatter pass.
 constexpr int kCoopTiles = 8;
+constexpr int kCoopTilesCull = 32;  // exact-tile-culling count pass
+constexpr int kCoopBitsCull = 16;   // exact-tile-culling scatter pass (alive tiles of a mask)
 
 // Calls f(bin_in_list, p0, p1) once per (tile, bucket) bin of every lane's rectangle; p0/p1 are the owning
 // lane's payload words (broadcast when the warp expands the rectangle).  Must be reached by all 32 lanes.
@@ -394,6 +469,67 @@ __device__ __forceinline__ void warp_for_each_bin(const Rect rc, uint32_t bk, ui
       f((uint32_t)((y0 + dy) * gx + x0 + (t - dy * ww)) * (uint32_t)NB + b, q0, q1);
     }
   }
+}
+
+// Exact-tile-culling form of the count (preprocess pass): calls f(bin_in_list) for every tile of the lane's
+// rectangle that passes alive_rect + tile_alive and returns the lane's mask of alive tiles (bit = row-major
+// position inside the rectangle, first 64 tiles only: larger rectangles are tested again by the scatter pass).
+// Candidate sets of more than kCoopTilesCull tiles are expanded by the whole warp.  Must be reached by all 32
+// lanes.
+template <class F>
+__device__ __forceinline__ unsigned long long warp_cull_count(const Rect rc, uint32_t bk, const Foot& ft, int gx,
+                                                              int NB, F&& f) {
+  const int w = rc.x1 - rc.x0;
+  const Rect q = alive_rect(ft, rc);
+  const int qw = q.x1 - q.x0, n = qw * (q.y1 - q.y0);
+  unsigned long long mask = 0ull;
+  // neighbours in Morton order have similar footprints, so per-thread loops stay balanced up to a full warp's
+  // worth of tiles; the broadcast of a whole Foot only pays beyond that
+  const bool coop = n > kCoopTilesCull;
+  if (!coop) {
+    for (int y = q.y0; y < q.y1; ++y)
+      for (int x = q.x0; x < q.x1; ++x)
+        if (tile_alive(ft, x, y)) {
+          f((uint32_t)(y * gx + x) * (uint32_t)NB + bk);
+          const int bit = (y - rc.y0) * w + (x - rc.x0);
+          if (bit < 64) mask |= 1ull << bit;
+        }
+  }
+  unsigned m = __ballot_sync(0xffffffffu, coop);
+  const int lane = threadIdx.x & 31;
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    const int x0 = __shfl_sync(0xffffffffu, q.x0, src), y0 = __shfl_sync(0xffffffffu, q.y0, src);
+    const int ww = __shfl_sync(0xffffffffu, qw, src), nn = __shfl_sync(0xffffffffu, n, src);
+    const int rx0 = __shfl_sync(0xffffffffu, rc.x0, src), ry0 = __shfl_sync(0xffffffffu, rc.y0, src);
+    const int rw = __shfl_sync(0xffffffffu, w, src);
+    const uint32_t b = __shfl_sync(0xffffffffu, bk, src);
+    Foot fs;
+    fs.px = __shfl_sync(0xffffffffu, ft.px, src); fs.py = __shfl_sync(0xffffffffu, ft.py, src);
+    fs.hx = __shfl_sync(0xffffffffu, ft.hx, src); fs.hy = __shfl_sync(0xffffffffu, ft.hy, src);
+    fs.A = __shfl_sync(0xffffffffu, ft.A, src);   fs.B = __shfl_sync(0xffffffffu, ft.B, src);
+    fs.C = __shfl_sync(0xffffffffu, ft.C, src);   fs.t = __shfl_sync(0xffffffffu, ft.t, src);
+    fs.kyx = __shfl_sync(0xffffffffu, ft.kyx, src); fs.kxy = __shfl_sync(0xffffffffu, ft.kxy, src);
+    unsigned long long mine = 0ull;  // alive tiles this lane found, as bits of the owner's mask
+    for (int t = lane; t < nn; t += 32) {
+      const int dy = t / ww;
+      const int x = x0 + (t - dy * ww), y = y0 + dy;
+      if (tile_alive(fs, x, y)) {
+        f((uint32_t)(y * gx + x) * (uint32_t)NB + b);
+        const int bit = (y - ry0) * rw + (x - rx0);
+        if (bit < 64) mine |= 1ull << bit;
+      }
+    }
+    uint32_t lo = (uint32_t)mine, hi = (uint32_t)(mine >> 32);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo |= __shfl_xor_sync(0xffffffffu, lo, o);
+      hi |= __shfl_xor_sync(0xffffffffu, hi, o);
+    }
+    if (lane == src) mask = ((unsigned long long)hi << 32) | lo;
+  }
+  return mask;
 }
 
 // ---- group-level frustum culling ----
@@ -485,7 +621,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
 
 // grid: (ceil(n_items / IPB), n_lists); list = view (static layer) or frame (dynamic layer).
 // Dynamic shared memory: [staged arrays (if use_tma)] [hist: T*NB u32 (if use_hist)] [pose table (DYN)].
-template <bool DYN, int IPB, bool TMA>
+template <bool DYN, int IPB, bool TMA, bool CULL>
 __global__ void __launch_bounds__(256, TMA ? 2 : 3)
 preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                   const float* __restrict__ views, const float* __restrict__ projs,
@@ -641,22 +777,37 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
       if (ga.slot != nullptr) la.slot = slot_s;
     }
   }
+  const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)nbl;
 #pragma unroll 1
   for (int it = 0; it < IPT; ++it) {
     const int il = it * 256 + threadIdx.x;
     const int64_t i = base + il;
+    Rect rc{0, 0, 0, 0};
+    uint32_t bk = 0;
+    Foot ft{};
     if (i < n_items) {
       const int64_t item = item_base + (int64_t)list * n_items + i;
       if (grp_culled[it]) {
         rad[item] = 0;
-        continue;
+      } else if (TMA) {
+        preprocess_item<DYN, CULL>(ga, la, i, staged ? (int64_t)il : i, item, list_base + list, g, vs, pose_s, recA,
+                                   recB, recC, rad, bin_count, hist, rc, bk, ft);
+      } else {  // same object for both roles: every load stays a read-only global load
+        preprocess_item<DYN, CULL>(ga, ga, i, i, item, list_base + list, g, vs, pose_s, recA, recB, recC, rad,
+                                   bin_count, hist, rc, bk, ft);
       }
-      if (TMA)
-        preprocess_item<DYN>(ga, la, i, staged ? (int64_t)il : i, item, list_base + list, g, vs, pose_s, recA, recB,
-                             recC, rad, bin_count, hist);
-      else  // same object for both roles: every load stays a read-only global load
-        preprocess_item<DYN>(ga, ga, i, i, item, list_base + list, g, vs, pose_s, recA, recB, recC, rad, bin_count,
-                             hist);
+    }
+    if (CULL) {  // count into the bins of the tiles that pass the exact test (all 32 lanes arrive here)
+      unsigned long long alive;
+      if (use_hist)
+        alive = warp_cull_count(rc, bk, ft, g.gx, g.NB, [&](uint32_t b) { atomicAdd(&hist[b], 1u); });
+      else
+        alive = warp_cull_count(rc, bk, ft, g.gx, g.NB, [&](uint32_t b) { atomicAdd(&bin_count[lbase + b], 1u); });
+      // recD (4th float4 of the 64 B slot): mask of the alive tiles among the first 64 of the rectangle,
+      // row-major; the scatter pass walks the set bits instead of repeating the test
+      if (rc.x1 > rc.x0)
+        recA[4 * (item_base + (int64_t)list * n_items + i) + 3] =
+            make_float4(__uint_as_float((uint32_t)alive), __uint_as_float((uint32_t)(alive >> 32)), 0.f, 0.f);
     }
   }
   if (use_hist) {
@@ -687,7 +838,8 @@ __device__ __forceinline__ int scatter_slot(int it, int t) { return ((t & 7) << 
 template <bool DYN>
 __global__ void __launch_bounds__(256)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
-               const float4* __restrict__ recA, const float4* __restrict__ recC, const int32_t* __restrict__ rad,
+               const float4* __restrict__ recA, const float4* __restrict__ /*recB*/,
+               const float4* __restrict__ recC, const int32_t* __restrict__ rad,
                const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
                unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
                const uint32_t* __restrict__ cta_hist) {
@@ -772,6 +924,141 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
         pos = bin_off[gb + b] + atomicAdd(&bin_cursor[gb + b], 1u);
       if ((int64_t)pos < cap) keys[pos] = ((unsigned long long)hi << 32) | lo;
     });
+  }
+}
+
+// Scatter with exact tile culling: the preprocess pass left, per visible Gaussian, the mask of its alive tiles
+// (first 64 tiles of the rectangle, recD); this pass walks the set bits.  Masks with more than kCoopTiles bits
+// (kCoopBitsCull) and rectangles of more than 64 tiles (tested again, same make_foot / tile_alive on the same bits) are
+// expanded by the whole warp.  Needs the preprocess CTA's bin counts (cta_hist) for the shared-memory slot
+// counters; without them it falls back to global cursors.
+template <bool DYN>
+__global__ void __launch_bounds__(256)
+scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
+                    const float4* __restrict__ recA, const float4* __restrict__ recB,
+                    const float4* __restrict__ recC, const int32_t* __restrict__ rad,
+                    const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
+                    unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
+                    const uint32_t* __restrict__ cta_hist) {
+  extern __shared__ uint32_t dsm[];
+  const int nbl = g.T * g.NB;
+  uint32_t* hist = dsm;         // running slot counters
+  uint32_t* hbase = dsm + nbl;  // absolute start of this CTA's range in each bin
+  const int list = blockIdx.y;
+  const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
+  const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
+  if (use_hist) {
+    const uint32_t* keep = cta_hist + ((size_t)list * gridDim.x + blockIdx.x) * (size_t)(nbl + 1);
+    if (keep[0] == 0u) return;  // whole chunk culled
+    for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
+      const uint32_t c = keep[1 + k];
+      if (c) hbase[k] = bin_off[gb + k] + atomicAdd(&bin_cursor[gb + k], c);
+      hist[k] = 0u;
+    }
+    __syncthreads();
+  }
+  auto emit = [&](uint32_t b, uint32_t lo, uint32_t hi) {
+    uint32_t pos;
+    if (use_hist)
+      pos = hbase[b] + atomicAdd(&hist[b], 1u);
+    else
+      pos = bin_off[gb + b] + atomicAdd(&bin_cursor[gb + b], 1u);
+    if ((int64_t)pos < cap) keys[pos] = ((unsigned long long)hi << 32) | lo;
+  };
+  const int lane = threadIdx.x & 31;
+  int radius[kItemsPerThread];
+#pragma unroll
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    const int64_t i = base + scatter_slot(it, threadIdx.x);
+    radius[it] = i < n_items ? rad[item_base + (int64_t)list * n_items + i] : 0;
+  }
+  // all record loads of the thread's 8 items are in flight before the first use; the loop below is not unrolled
+  // (its body holds the whole-warp paths), so these arrays live in L1-resident local memory
+  float4 ra[kItemsPerThread];
+  uint32_t ml[kItemsPerThread], mh[kItemsPerThread];
+  float dp[kItemsPerThread];
+#pragma unroll
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    ra[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+    ml[it] = mh[it] = 0u;
+    dp[it] = 0.f;
+    if (radius[it] > 0) {
+      const int64_t item = item_base + (int64_t)list * n_items + base + scatter_slot(it, threadIdx.x);
+      ra[it] = recA[4 * item];
+      const float4 d = recA[4 * item + 3];
+      ml[it] = __float_as_uint(d.x);
+      mh[it] = __float_as_uint(d.y);
+      dp[it] = recC[4 * item].w;
+    }
+  }
+#pragma unroll 1
+  for (int it = 0; it < kItemsPerThread; ++it) {
+    const int64_t i = base + scatter_slot(it, threadIdx.x);
+    const int64_t item = item_base + (int64_t)list * n_items + i;
+    Rect rc{0, 0, 0, 0};
+    uint32_t bk = 0, klo = 0, khi = 0, mlo = 0, mhi = 0;
+    const float4 a = ra[it];
+    if (radius[it] > 0) {
+      const float depth = dp[it];
+      rc = tile_rect(a.x, a.y, radius[it], g.gx, g.gy);
+      klo = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
+      khi = __float_as_uint(depth);
+      bk = depth_bucket(depth, g);
+      mlo = ml[it];
+      mhi = mh[it];
+    }
+    const int w = rc.x1 - rc.x0, n = w * (rc.y1 - rc.y0);
+    const bool huge = n > 64;                                          // test again, whole warp
+    const bool wide = !huge && __popc(mlo) + __popc(mhi) > kCoopBitsCull;  // walk the mask, whole warp
+    if (!huge && !wide) {
+      unsigned long long mask = ((unsigned long long)mhi << 32) | mlo;
+      while (mask) {
+        const int bit = __ffsll((long long)mask) - 1;
+        mask &= mask - 1;
+        const int dy = bit / w;
+        emit((uint32_t)((rc.y0 + dy) * g.gx + rc.x0 + (bit - dy * w)) * (uint32_t)g.NB + bk, klo, khi);
+      }
+    }
+    unsigned m = __ballot_sync(0xffffffffu, huge || wide);
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const int x0 = __shfl_sync(0xffffffffu, rc.x0, src), y0 = __shfl_sync(0xffffffffu, rc.y0, src);
+      const int ww = __shfl_sync(0xffffffffu, w, src), nn = __shfl_sync(0xffffffffu, n, src);
+      const uint32_t b = __shfl_sync(0xffffffffu, bk, src);
+      const uint32_t lo = __shfl_sync(0xffffffffu, klo, src), hi = __shfl_sync(0xffffffffu, khi, src);
+      if (nn <= 64) {  // warp-uniform
+        const uint32_t q0 = __shfl_sync(0xffffffffu, mlo, src), q1 = __shfl_sync(0xffffffffu, mhi, src);
+        for (int t0 = 0; t0 < nn; t0 += 32) {
+          const int t = t0 + lane;
+          if (t < nn && (((t0 ? q1 : q0) >> lane) & 1u)) {
+            const int dy = t / ww;
+            emit((uint32_t)((y0 + dy) * g.gx + x0 + (t - dy * ww)) * (uint32_t)g.NB + b, lo, hi);
+          }
+        }
+      } else {
+        Foot fo{};
+        if (lane == src) {
+          const float4 cb = recB[4 * item];
+          fo = make_foot(a.x, a.y, a.z, a.w, cb.x, cb.y, cb.z, cb.w);
+        }
+        Foot fs;
+        fs.px = __shfl_sync(0xffffffffu, fo.px, src); fs.py = __shfl_sync(0xffffffffu, fo.py, src);
+        fs.hx = __shfl_sync(0xffffffffu, fo.hx, src); fs.hy = __shfl_sync(0xffffffffu, fo.hy, src);
+        fs.A = __shfl_sync(0xffffffffu, fo.A, src);   fs.B = __shfl_sync(0xffffffffu, fo.B, src);
+        fs.C = __shfl_sync(0xffffffffu, fo.C, src);   fs.t = __shfl_sync(0xffffffffu, fo.t, src);
+        fs.kyx = __shfl_sync(0xffffffffu, fo.kyx, src); fs.kxy = __shfl_sync(0xffffffffu, fo.kxy, src);
+        Rect full;
+        full.x0 = x0; full.y0 = y0; full.x1 = x0 + ww; full.y1 = y0 + nn / ww;
+        const Rect q = alive_rect(fs, full);
+        const int qw = q.x1 - q.x0, qn = qw * (q.y1 - q.y0);
+        for (int t = lane; t < qn; t += 32) {
+          const int dy = t / qw;
+          const int x = q.x0 + (t - dy * qw), y = q.y0 + dy;
+          if (tile_alive(fs, x, y)) emit((uint32_t)(y * g.gx + x) * (uint32_t)g.NB + b, lo, hi);
+        }
+      }
+    }
   }
 }
 
@@ -1014,21 +1301,23 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
   }
   const size_t sm = (use_tma ? stage_b : 0) + (use_hist ? hist_b : 0) + pose_b;
   int rc;
-#define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_)                                                                          \
+#define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_, CULL_)                                                                   \
   do {                                                                                                            \
     dim3 grid((unsigned)((n_items + IPB_ - 1) / IPB_), (unsigned)n_lists);                                        \
-    if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_>>(sm, ctx->device))) return rc;                                   \
-    preprocess_kernel<DYN_, IPB_, TMA_><<<grid, 256, sm, s>>>(                                                    \
+    if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_, CULL_>>(sm, ctx->device))) return rc;               \
+    preprocess_kernel<DYN_, IPB_, TMA_, CULL_><<<grid, 256, sm, s>>>(                                             \
         ga, n_items, list_base, item_base, g, view, proj, campos, tanfov, frame_env, frame_view, pose, num_slots, \
         w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
         w.bin_count.as<uint32_t>(), use_hist, use_hist ? cta_hist : nullptr);                                     \
   } while (0)
-  if (dynamic)
-    GSW_LAUNCH_PRE(true, kIpbDynamic, false);
-  else if (use_tma)
-    GSW_LAUNCH_PRE(false, kIpbStatic, true);
-  else
-    GSW_LAUNCH_PRE(false, kIpbStatic, false);
+  const bool cull = g.tile_cull != 0;
+  if (dynamic) {
+    if (cull) GSW_LAUNCH_PRE(true, kIpbDynamic, false, true); else GSW_LAUNCH_PRE(true, kIpbDynamic, false, false);
+  } else if (use_tma) {
+    if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, true, true); else GSW_LAUNCH_PRE(false, kIpbStatic, true, false);
+  } else {
+    if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true); else GSW_LAUNCH_PRE(false, kIpbStatic, false, false);
+  }
 #undef GSW_LAUNCH_PRE
   if (kept_hist) *kept_hist = use_hist && cta_hist != nullptr;
   count_launches(1);
@@ -1051,21 +1340,24 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   auto& w = ctx->ws;
   const size_t hist_b = (size_t)g.T * g.NB * 8;
   const int use_hist = hist_b <= kMaxHistBytes;
-  const size_t sm = use_hist ? hist_b : 0;
   int rc;
-  if (dynamic) {
-    if ((rc = ensure_smem<scatter_kernel<true>>(sm, ctx->device))) return rc;
-    scatter_kernel<true><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
-                                               w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
-                                               w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
-                                               use_hist, cta_hist);
+#define GSW_LAUNCH_SCATTER(KERNEL_, HIST_, CH_)                                                                     \
+  do {                                                                                                            \
+    if ((rc = ensure_smem<KERNEL_>((HIST_) ? hist_b : 0, ctx->device))) return rc;                                \
+    KERNEL_<<<grid, 256, (HIST_) ? hist_b : 0, s>>>(                                                              \
+        ga, n_items, list_base, item_base, g, w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, \
+        w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(), w.bin_cursor.as<uint32_t>(),                               \
+        w.keys.as<unsigned long long>(), cap, (HIST_) ? 1 : 0, CH_);                                              \
+  } while (0)
+  if (g.tile_cull != 0) {  // the culling form has no counting pass of its own: shared counters need cta_hist
+    const bool h = use_hist && cta_hist != nullptr;
+    if (dynamic) GSW_LAUNCH_SCATTER(scatter_cull_kernel<true>, h, cta_hist);
+    else GSW_LAUNCH_SCATTER(scatter_cull_kernel<false>, h, cta_hist);
   } else {
-    if ((rc = ensure_smem<scatter_kernel<false>>(sm, ctx->device))) return rc;
-    scatter_kernel<false><<<grid, 256, sm, s>>>(ga, n_items, list_base, item_base, g, w.rec.as<float4>(),
-                                                w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(),
-                                                w.bin_cursor.as<uint32_t>(), w.keys.as<unsigned long long>(), cap,
-                                                use_hist, cta_hist);
+    if (dynamic) GSW_LAUNCH_SCATTER(scatter_kernel<true>, use_hist, cta_hist);
+    else GSW_LAUNCH_SCATTER(scatter_kernel<false>, use_hist, cta_hist);
   }
+#undef GSW_LAUNCH_SCATTER
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

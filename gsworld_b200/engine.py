@@ -89,6 +89,11 @@ class Engine:
     def set_depth_buckets(self, nb: int):
         _lib.check(self.lib.gsw_set_depth_buckets(self._h, int(nb)))
 
+    def set_tile_culling(self, on: bool):
+        """Exact tile culling (include/gsw.h): drop tile entries that provably stay below alpha 1/255 on the
+        whole tile.  Images and radii are unchanged bit for bit; the tile lists become sub-lists."""
+        _lib.check(self.lib.gsw_set_tile_culling(self._h, 1 if on else 0))
+
     def reserve_entries(self, n: int):
         _lib.check(self.lib.gsw_reserve_entries(self._h, int(n)))
 

@@ -129,6 +129,14 @@ int gsw_finish(gsw_ctx* ctx, int64_t* needed_entries, int64_t stats[4]);
 int gsw_reserve_entries(gsw_ctx* ctx, int64_t entries);
 /* depth sub-buckets per tile list (power of two, 1..64); 0 = automatic */
 int gsw_set_depth_buckets(gsw_ctx* ctx, int nb);
+/* Exact tile culling (default off = the reference's tile lists).  The reference duplicates a Gaussian into every
+ * tile of the bounding square of its 3-sigma radius (rasterizer forward.cu getRect / duplicateWithKeys); its
+ * blend loop then skips, without touching any state, every entry whose alpha stays below 1/255 on the pixel.
+ * With culling on, a (Gaussian, tile) entry that provably stays below 1/255 on all 256 pixels of the tile is
+ * not created: images, radii and the per-Gaussian tile count tap stay bit-identical, the per-tile lists
+ * (gsw_debug_frame_lists, stats D) become order-preserving sub-lists of the reference's.  No counterpart in
+ * the reference. */
+int gsw_set_tile_culling(gsw_ctx* ctx, int on);
 
 /* Single-frame forward with the upstream argument list (drop-in for GaussianRasterizer.forward).
  * Exactly one of shs / colors_precomp and exactly one of (scales, rotations) / cov3D_precomp.

@@ -92,6 +92,21 @@ def test_idempotent_and_shared_static_lists_change_nothing(rig):
     assert torch.equal(a["rgb_u8"], c["rgb_u8"]) and torch.equal(a["radii"], c["radii"])
 
 
+def test_exact_tile_culling_changes_no_byte_at_full_size(rig):
+    """gsw_set_tile_culling at 1M Gaussians: uint8 frames, float colour and radii byte-identical, fewer entries."""
+    scene, env, mk = rig
+    for strict in (True, False):
+        wrap = mk(strict)
+        a, _ = _render(wrap, want_u8=True, want_color=True, want_radii=True)
+        Da = wrap._engine.last_stats["D"]
+        wrap._engine.set_tile_culling(True)
+        b, _ = _render(wrap, want_u8=True, want_color=True, want_radii=True)
+        Db = wrap._engine.last_stats["D"]
+        assert Db < 0.9 * Da
+        assert torch.equal(a["rgb_u8"], b["rgb_u8"]) and torch.equal(a["radii"], b["radii"])
+        assert torch.equal(a["color"].view(torch.int32), b["color"].view(torch.int32))
+
+
 def test_entry_checksum_and_sorted_lists(rig):
     scene, env, mk = rig
     wrap = mk(True)
