@@ -515,6 +515,14 @@ def run_ours(args):
         d_shared = int(sum(int(off[(v + 1) * Tn]) - int(off[v * Tn]) for v in shared))
         results[mode] = dict(ms=ms, fps=world * F * args.steps / (ms * 1e-3), stages=acc, stats=st, V=Vn,
                              D_shared_static=d_shared)
+        if mode == "strict" and not args.quick and not os.environ.get("GSW_TILE_CULL"):
+            # the same step with the reference's full tile lists (exact tile culling off); same pixels
+            eng.set_tile_culling(False)
+            ms_full = timed(env, wrap, args.steps, args.warmup)
+            results[mode]["reference_tile_lists"] = {
+                "value": world * F * args.steps / (ms_full * 1e-3), "ms_per_step": ms_full / args.steps,
+                "D": int(eng.last_stats["D"])}
+            eng.set_tile_culling(True)
         if mode == "strict":
             results[mode].update(clocks=clocks, launches=launches)
             if args.quick:
@@ -574,6 +582,9 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "envs_per_gpu": B, "frames_per_step_per_gpu": F, "views": V,
                        "cameras": "strict (env-0 camera for every env = reference behaviour, gs_world_wrapper.py:280-281)",
+                       "tile_lists": "exact tile culling on (wrapper default): entries that stay below alpha 1/255 on a "
+                                     "whole tile are never binned; pixels and radii bit-identical to the "
+                                     "reference's full lists (reference_tile_lists = the same step with it off)",
                        "l2": "inputs larger than L2 (236 MB scene + GB-scale workspace per step), no explicit flush",
                        "parallelism": f"env-sharded x{world}, scene replicated, uint8 all-gather"},
             "e2e": {"value": results["e2e"]["fps"], "unit": "frames/s", "h2d_bytes_per_step": results["e2e"]["h2d"],
@@ -594,6 +605,7 @@ def run_ours(args):
             "stage_gbs": {k: round(alg[k] / (stages[k] * 1e-3) / 1e9, 1) for k in alg if stages.get(k, 0) > 0},
             "counts": {"N": N_GAUSS, "movable": Nm, "D": D, "D_shared_static": r["D_shared_static"],
                        "blend_staged": R},
+            "reference_tile_lists": r.get("reference_tile_lists"),
             "per_env_cameras": {"value": results["per_env"]["fps"], "ms_per_step": results["per_env"]["ms"] / args.steps,
                                 "views": results["per_env"]["V"],
                                 "stages_ms": {k: round(v, 4) for k, v in results["per_env"]["stages"].items()},

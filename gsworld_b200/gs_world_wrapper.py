@@ -85,7 +85,7 @@ class GSWorldWrapper(_Base):
                  state_log_path: str = "./exp_log", cam_randomization: bool = False, *, merged_model=None,
                  scan_link_mats=None, strict_reference: bool = True, engine: Optional[Engine] = None,
                  fused_host: bool = True, cfg_dir: Optional[str] = None, asset_dir: Optional[str] = None,
-                 inv_depth_obs: bool = False, segmentation_obs: bool = False):
+                 inv_depth_obs: bool = False, segmentation_obs: bool = False, tile_culling: bool = True):
         super().__init__(env)
         self.num_envs = env.num_envs
         self.robot_pipe = robot_pipe
@@ -136,6 +136,9 @@ class GSWorldWrapper(_Base):
                                   for m in scan_link_mats]
         self.gs_movable_pts = dict()
         self._engine = engine if engine is not None else Engine(self.device)
+        # exact tile culling (include/gsw.h): observations are bit-identical with it on or off; off keeps the
+        # reference's tile lists for the parity taps
+        self._engine.set_tile_culling(bool(tile_culling))
         self._setup_rig()
 
     # ------------------------------------------------------------------ set-up (once)

@@ -23,7 +23,7 @@ def _make(robot, cfg_name, B, hw, objects, strict, n_total=24_000, seed=11, nb=0
     env = fx.FakeEnv(robot, num_envs=B, hw=hw, objects=objects, seed=seed, device=dev)
     scan = fx.forward_kinematics(robot, fx.rt.ROBOT_SCAN_QPOS[robot][None])[0]
     wrap = GSWorldWrapper(env, PipelineParams(), cfg_name, device=dev, merged_model=scene.to(dev),
-                          scan_link_mats=list(scan), strict_reference=strict)
+                          scan_link_mats=list(scan), strict_reference=strict, tile_culling=False)  # reference lists
     if nb:
         wrap._engine.set_depth_buckets(nb)
     return scene, env, wrap

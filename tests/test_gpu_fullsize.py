@@ -35,7 +35,7 @@ def rig():
     scan = fx.forward_kinematics("fr3_umi", fx.rt.ROBOT_SCAN_QPOS["fr3_umi"][None])[0]
     scene_dev = scene.to(dev)
     mk = lambda strict: GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene_dev,
-                                       scan_link_mats=list(scan), strict_reference=strict)
+                                       scan_link_mats=list(scan), strict_reference=strict, tile_culling=False)
     return scene, env, mk
 
 

@@ -109,4 +109,13 @@ def test_very_large_image_uses_global_atomic_binning_path():
     assert lists["D"] == want["D"]
     np.testing.assert_array_equal(lists["vals"].cpu().numpy().view(np.uint32), want["vals"])
     assert_image_close(color.cpu().numpy(), want["color"], want["fragile"].astype(bool))
+    # exact tile culling on the same global-atomic path: same pixels, fewer entries
+    eng.set_tile_culling(True)
+    color2, radii2, invd2 = eng.rasterize_forward(
+        g["xyz"].to(dev), g["opacities"].to(dev), cam["view"].to(dev), cam["proj"].to(dev), cam["campos"].to(dev),
+        cam["tanfovx"], cam["tanfovy"], H, W, torch.zeros(3, device=dev), shs=g["shs"].to(dev),
+        scales=g["scales"].to(dev), rotations=g["rotations"].to(dev))
+    torch.cuda.synchronize()
+    assert torch.equal(color.view(torch.int32), color2.view(torch.int32)) and torch.equal(radii, radii2)
+    assert eng.debug_frame_lists(0, T)["D"] < want["D"]
     eng.close()

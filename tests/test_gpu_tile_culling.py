@@ -130,8 +130,7 @@ def test_wrapper_observations_identical_with_culling(strict):
         env = fx.FakeEnv("fr3_umi", num_envs=4, hw=(128, 128), objects=objects, seed=41, device=dev)
         w = GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene,
                            scan_link_mats=list(scan), strict_reference=strict, inv_depth_obs=True,
-                           segmentation_obs=True)
-        w._engine.set_tile_culling(cull)
+                           segmentation_obs=True, tile_culling=cull)
         wraps.append(w)
     obs = [w.reset(seed=3)[0] for w in wraps]
     for step in range(3):
