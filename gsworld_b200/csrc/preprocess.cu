@@ -95,13 +95,12 @@ __device__ __forceinline__ Foot make_foot(float px, float py, float hx, float hy
   return f;
 }
 
+// For tiles inside alive_rect(f, .) only: the box test against the alpha >= 1/255 extents is done there, once per
+// Gaussian, by shrinking the candidate rectangle.
 __device__ __forceinline__ bool tile_alive(const Foot& f, int tx, int ty) {
-  if (f.hx < 0.f) return false;
-  const float bx0 = (float)(tx * kTile), bx1 = bx0 + (float)(kTile - 1);
-  const float by0 = (float)(ty * kTile), by1 = by0 + (float)(kTile - 1);
-  if (f.px + f.hx < bx0 || f.px - f.hx > bx1 || f.py + f.hy < by0 || f.py - f.hy > by1) return false;
   if (f.hx >= 1.0e30f) return true;
-  const float x0 = bx0 - f.px, x1 = bx1 - f.px, y0 = by0 - f.py, y1 = by1 - f.py;
+  const float x0 = (float)(tx * kTile) - f.px, x1 = x0 + (float)(kTile - 1);
+  const float y0 = (float)(ty * kTile) - f.py, y1 = y0 + (float)(kTile - 1);
   const float xe = fminf(fmaxf(0.f, x0), x1), ye = fminf(fmaxf(0.f, y0), y1);
   const float ys = fminf(fmaxf(f.kyx * xe, y0), y1);
   const float xs = fminf(fmaxf(f.kxy * ye, x0), x1);
@@ -110,7 +109,7 @@ __device__ __forceinline__ bool tile_alive(const Foot& f, int tx, int ty) {
   return !(fmaxf(p1, p2) < -f.t);
 }
 
-// Tiles of rc that can pass tile_alive's box test (the alpha >= 1/255 box is usually much smaller than the
+// Tiles of rc that overlap the alpha >= 1/255 box of the Gaussian (usually much smaller than the
 // bounding square of the 3-sigma radius that rc comes from): the loops below only visit these.  Part of the
 // decision (both passes call it), not just a shortcut.
 __device__ __forceinline__ Rect alive_rect(const Foot& f, const Rect rc) {
