@@ -373,18 +373,45 @@ def run_ours(args):
     # into one of two buffers, so the exchange of step k overlaps the rendering of step k+1; a buffer is
     # only reused after the collective that read/wrote it has completed.
     nbuf = 2
-    GATHER = os.environ.get("GSW_BENCH_GATHER", "all")
+    # "peer" (default where torch symmetric memory works): libgsw's copy stream pushes every finished frame group
+    # into every rank's buffer with the copy engines, overlapped with the blend, + one device-side barrier per
+    # step; "all": NCCL all-gather; "root": NCCL gather to rank 0; "none": no exchange
+    GATHER = os.environ.get("GSW_BENCH_GATHER", "peer")
     build.calls = 0
+    xchg = None
+    if world > 1 and GATHER == "peer":
+        from gsworld_b200.dist import PeerObservationExchange
+        ok = 0
+        try:
+            if PeerObservationExchange.available():
+                xchg = PeerObservationExchange((len(CAMERAS), B, H, W, 3), dev, nbuf=nbuf)
+                ok = 1
+        except Exception as e:  # noqa: BLE001
+            log(f"[rank {rank}] symmetric memory unavailable ({e!r}); falling back to the NCCL all-gather")
+        flag = torch.tensor([ok], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            xchg, GATHER = None, "all"
     gathered = [torch.empty((world, len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(nbuf)] \
-        if world > 1 else None
+        if world > 1 and GATHER in ("all", "root") else None
     pending = [None] * nbuf
     counter = [0]
 
     def step(env, wrap):
         env.advance()
         wrap.transform_gs_perlink(None)
+        if xchg is not None:
+            k = counter[0]
+            counter[0] += 1
+            xchg.begin(k)
+            wrap.obs_out = xchg.local_out(k)  # composite straight into this rank's slot of its own buffer
+            wrap.obs_peers = xchg.destinations(k)
+            wrap.defer_delivery_join = not wrap.sync_each_step
+            out = wrap._render_gsworld()
+            xchg.publish(k, wrap._engine)  # after xchg.wait_ready(k), xchg.gathered(k) holds every rank's frames
+            return out
         out = wrap._render_gsworld()
-        if world > 1 and GATHER != "none":
+        if world > 1 and GATHER in ("all", "root"):
             k = counter[0] % nbuf
             counter[0] += 1
             if pending[k] is not None:
@@ -399,6 +426,8 @@ def run_ours(args):
         return out
 
     def drain():
+        if xchg is not None:
+            xchg.stream.synchronize()
         for k in range(nbuf):
             if pending[k] is not None:
                 pending[k].wait()
@@ -586,7 +615,9 @@ def run_ours(args):
                                      "whole tile are never binned; pixels and radii bit-identical to the "
                                      "reference's full lists (reference_tile_lists = the same step with it off)",
                        "l2": "inputs larger than L2 (236 MB scene + GB-scale workspace per step), no explicit flush",
-                       "parallelism": f"env-sharded x{world}, scene replicated, uint8 all-gather"},
+                       "parallelism": f"env-sharded x{world}, scene replicated, uint8 observations exchanged by "
+                                      + ("copy-engine pushes into peer memory (NVLink), overlapped with the blend"
+                                         if xchg is not None else f"NCCL ({GATHER})")},
             "e2e": {"value": results["e2e"]["fps"], "unit": "frames/s", "h2d_bytes_per_step": results["e2e"]["h2d"],
                     "d2h_bytes_per_step": results["e2e"]["d2h"], "ms_per_step": results["e2e"]["ms"] / args.steps},
             "gpu_launches": r["launches"],

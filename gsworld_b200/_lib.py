@@ -24,6 +24,7 @@ class FramesDesc(C.Structure):
         ("tanfov", C.c_void_p), ("frame_env", C.c_void_p), ("frame_view", C.c_void_p),
         ("out_rgb_u8", C.c_void_p), ("out_color", C.c_void_p), ("out_invdepth", C.c_void_p),
         ("out_radii", C.c_void_p), ("host_rgb_u8", C.c_void_p), ("out_seg", C.c_void_p),
+        ("peer_rgb_u8", C.POINTER(C.c_void_p)), ("num_peer_rgb_u8", C.c_int32), ("deliver_flags", C.c_int32),
     ]
 
 
@@ -38,6 +39,7 @@ SYMBOLS = {
     "gsw_scene_set_labels": (C.c_int, [_vp, _vp]),
     "gsw_render_frames": (C.c_int, [_vp, C.POINTER(FramesDesc), _vp]),
     "gsw_finish": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64 * 4)]),
+    "gsw_delivery_wait": (C.c_int, [_vp, _vp]),
     "gsw_reserve_entries": (C.c_int, [_vp, _i64]),
     "gsw_set_depth_buckets": (C.c_int, [_vp, C.c_int]),
     "gsw_set_tile_culling": (C.c_int, [_vp, C.c_int]),

@@ -539,10 +539,29 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                                      d->out_invdepth != nullptr, d->out_seg != nullptr, s)))
       return rc;
   }
-  if (d->host_rgb_u8 && d->out_rgb_u8 && c->wait_value32 != nullptr) {
+  const int n_peer = d->peer_rgb_u8 ? d->num_peer_rgb_u8 : 0;
+  if (n_peer < 0 || n_peer > 16 || ((d->host_rgb_u8 || n_peer > 0) && !d->out_rgb_u8)) {
+    set_error("gsw_render_frames: host_rgb_u8 / peer_rgb_u8 need out_rgb_u8; at most 16 peers");
+    return GSW_E_INVALID;
+  }
+  const bool deliver = d->host_rgb_u8 != nullptr || n_peer > 0;
+  // one group of finished frames to every destination (pinned host and / or peer GPUs), on the copy stream
+  auto send_group = [&](int f0, int f1) -> int {
+    const size_t frame_bytes = (size_t)d->height * d->width * 3;
+    const size_t off = (size_t)f0 * frame_bytes, bytes = (size_t)(f1 - f0) * frame_bytes;
+    if (d->host_rgb_u8)
+      GSW_CUDA(cudaMemcpyAsync(d->host_rgb_u8 + off, d->out_rgb_u8 + off, bytes, cudaMemcpyDeviceToHost,
+                               c->copy_stream));
+    for (int p = 0; p < n_peer; ++p)
+      if (d->peer_rgb_u8[p] != nullptr && d->peer_rgb_u8[p] != d->out_rgb_u8)
+        GSW_CUDA(cudaMemcpyAsync(d->peer_rgb_u8[p] + off, d->out_rgb_u8 + off, bytes, cudaMemcpyDeviceToDevice,
+                                 c->copy_stream));
+    return 0;
+  };
+  if (deliver && c->wait_value32 != nullptr) {
     // ONE blend launch; the frames are cut into groups, the last CTA of a group to finish publishes the launch
     // epoch in the group's flag, and the copy stream waits on that flag (stream memory operation) before it
-    // sends the group's uint8 frames to the pinned host buffer.  Delivery overlaps the compositing of the later
+    // sends the group's uint8 frames to the pinned host buffer and / or the peer GPUs.  Delivery overlaps the compositing of the later
     // frames without splitting the launch (every extra launch costs a tail of half-empty SMs).
     typedef CUresult (*wait_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
     const wait_fn wait32 = reinterpret_cast<wait_fn>(c->wait_value32);
@@ -556,7 +575,6 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
                            nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s, &sg)))
       return rc;
-    const size_t frame_bytes = (size_t)d->height * d->width * 3;
     for (int k = 0; k < sg.n; ++k) {
       const CUresult wr = c->wait_value32 == nullptr
                               ? CUDA_SUCCESS
@@ -569,20 +587,18 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
         GSW_CUDA(cudaEventRecord(c->grp_evt[0], s));
         GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[0], 0));
       }
-      GSW_CUDA(cudaMemcpyAsync(d->host_rgb_u8 + (size_t)sg.cut(k) * frame_bytes,
-                               d->out_rgb_u8 + (size_t)sg.cut(k) * frame_bytes,
-                               (size_t)(sg.cut(k + 1) - sg.cut(k)) * frame_bytes, cudaMemcpyDeviceToHost,
-                               c->copy_stream));
+      if ((rc = send_group(sg.cut(k), sg.cut(k + 1)))) return rc;
     }
     GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
-    GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
-  } else if (d->host_rgb_u8 && d->out_rgb_u8) {
+    c->delivered = true;
+    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN))
+      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+  } else if (deliver) {
     // blend in up to 5 frame groups; each group's uint8 frames go to the pinned host buffer on the copy stream
     // as soon as that group is done, while the next group is being composited.  The last groups are small:
     // only the final group's copy is not hidden behind a blend launch.
     static const int kCut[6] = {0, 32, 64, 96, 116, 128};  // of 128
     const int G = d->num_frames < 5 ? d->num_frames : 5;
-    const size_t frame_bytes = (size_t)d->height * d->width * 3;
     for (int k = 0; k < G; ++k) {
       const int f0 = G < 5 ? k : (int)((int64_t)d->num_frames * kCut[k] / 128);
       const int f1 = G < 5 ? k + 1 : (int)((int64_t)d->num_frames * kCut[k + 1] / 128);
@@ -592,11 +608,12 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
         return rc;
       GSW_CUDA(cudaEventRecord(c->grp_evt[k], s));
       GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[k], 0));
-      GSW_CUDA(cudaMemcpyAsync(d->host_rgb_u8 + (size_t)f0 * frame_bytes, d->out_rgb_u8 + (size_t)f0 * frame_bytes,
-                               (size_t)(f1 - f0) * frame_bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+      if ((rc = send_group(f0, f1))) return rc;
     }
     GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
-    GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+    c->delivered = true;
+    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN))
+      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
   } else if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
                                 nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s))) {
     return rc;
@@ -606,6 +623,17 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     if ((rc = launch_radii(c, d->out_radii, s))) return rc;
   if (c->profile) cudaEventRecord(c->stage_evt[8], s);
   return finish_launch(c, s);
+}
+
+int gsw_delivery_wait(gsw_ctx* c, gsw_stream stream) {
+  if (!c) {
+    set_error("gsw_delivery_wait: NULL ctx");
+    return GSW_E_INVALID;
+  }
+  if (!c->delivered) return GSW_OK;
+  Guard gd(c->device);
+  GSW_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->copy_evt, 0));
+  return GSW_OK;
 }
 
 int gsw_finish(gsw_ctx* c, int64_t* needed_entries, int64_t stats[4]) {

@@ -184,6 +184,7 @@ struct gsw_ctx {
   gsw::DevBuf sig;               // DoneSig counters [16] + flags [16]
   uint32_t sig_epoch = 0;
   cudaEvent_t copy_evt = nullptr;
+  bool delivered = false;  // copy_evt has been recorded by a delivery
   // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are
   // independent until the scan / the sort, and each leaves a good part of the SMs idle on its own
   cudaStream_t side_stream = nullptr;

@@ -52,3 +52,77 @@ def gather_observations(local: Dict[str, torch.Tensor], num_envs: int, group=Non
             parts.append(recv[r, i, : rhi - rlo])
         out[c] = torch.cat(parts, 0)
     return out
+
+
+class PeerObservationExchange:
+    """Every rank's uint8 observations in every rank's memory WITHOUT a collective kernel.
+
+    Each rank owns `nbuf` symmetric buffers [world, *shard_shape] (torch symmetric memory: the same allocation
+    on every GPU of the box, each mapped into every process over NVLink / NVSwitch).  Step k of rank r:
+
+        begin(k)            the render stream waits until buffer k % nbuf may be written again
+        local_out(k)        slot r of the rank's own buffer: the renderer composites straight into it (obs_out)
+        destinations(k)     slot r of the same buffer on every OTHER rank: libgsw's copy stream pushes each finished
+                            frame group there with the copy engines (no SMs, no NCCL kernel) while later frames
+                            are still being composited (gsw_frames_desc.peer_rgb_u8, GSW_DELIVER_NO_JOIN)
+        publish(k, engine)  on the exchange's own stream: wait for this rank's pushes, then a device-side barrier
+                            over all ranks; the render stream is not involved and goes on with step k + 1
+        wait_ready(k)       the calling stream waits for that barrier: gathered(k) then holds every rank's frames
+
+    One-step slack, like a double-buffered all-gather: a rank may render step k + 1 while step k is still being
+    exchanged, and starts step k + nbuf only after the barrier of step k + nbuf - 1... of the buffer's previous
+    use has passed on this rank.  Whoever reads gathered(k) must have its reads enqueued (on a stream ordered
+    before the rank's next publish) before step k + 1 is published: the barrier of step k + 1 is what separates
+    those reads from the writes of step k + nbuf.  The reference has no multi-GPU path; this
+    replaces the NCCL all-gather of §8(e) where symmetric memory is available (`available()`),
+    `gather_observations` stays as the fallback."""
+
+    @staticmethod
+    def available() -> bool:
+        try:
+            import torch.distributed._symmetric_memory  # noqa: F401
+            return torch.cuda.is_available() and dist.is_initialized() and dist.get_backend() == "nccl"
+        except Exception:
+            return False
+
+    def __init__(self, shard_shape, device, group=None, nbuf: int = 2):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        self.shard_shape = tuple(int(x) for x in shard_shape)
+        self.nbuf = nbuf
+        full = (self.world,) + self.shard_shape
+        self._local, self._hdl, self._dst = [], [], []
+        for _ in range(nbuf):
+            t = symm_mem.empty(full, dtype=torch.uint8, device=device)
+            h = symm_mem.rendezvous(t, self.group)
+            self._local.append(t)
+            self._hdl.append(h)
+            self._dst.append([h.get_buffer(p, full, torch.uint8)[self.rank] for p in range(self.world)
+                              if p != self.rank])
+        self.stream = torch.cuda.Stream(device=device)
+        self._ready = [torch.cuda.Event() for _ in range(nbuf)]
+        self._used = [False] * nbuf
+
+    def begin(self, k: int):
+        if self._used[k % self.nbuf]:  # barrier of the buffer's previous use
+            torch.cuda.current_stream().wait_event(self._ready[k % self.nbuf])
+
+    def local_out(self, k: int) -> torch.Tensor:
+        return self._local[k % self.nbuf][self.rank]
+
+    def destinations(self, k: int):
+        return self._dst[k % self.nbuf]
+
+    def publish(self, k: int, engine):
+        engine.delivery_wait(self.stream)
+        with torch.cuda.stream(self.stream):
+            self._hdl[k % self.nbuf].barrier()
+            self._ready[k % self.nbuf].record()
+        self._used[k % self.nbuf] = True
+
+    def wait_ready(self, k: int):
+        torch.cuda.current_stream().wait_event(self._ready[k % self.nbuf])
+
+    def gathered(self, k: int) -> torch.Tensor:
+        return self._local[k % self.nbuf]

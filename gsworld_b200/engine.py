@@ -131,6 +131,7 @@ class Engine:
                       num_envs, bg=(0.0, 0.0, 0.0), antialiasing=False, scale_modifier=1.0, near=NEAR_GSWORLD,
                       out_rgb_u8=None, out_color=None, out_invdepth=None, out_radii=None, want_u8=True,
                       want_color=False, want_invdepth=False, want_radii=False, finish=True, host_rgb_u8=None,
+                      peer_rgb_u8=None, defer_delivery_join=False,
                       want_seg=False):
         """Enqueue one batched transform+rasterize launch set.  Returns dict of output tensors.
 
@@ -184,6 +185,20 @@ class Engine:
             desc.host_rgb_u8 = host_rgb_u8.data_ptr()
         else:
             desc.host_rgb_u8 = None
+        if peer_rgb_u8:
+            # device buffers (F,H,W,3) uint8 on this or on peer GPUs (mapped into this process): every finished frame
+            # group is pushed to each of them on the copy stream (gsw_frames_desc.peer_rgb_u8)
+            for t in peer_rgb_u8:
+                if not (t.is_cuda and t.is_contiguous() and t.dtype == torch.uint8 and t.numel() == F * H * W * 3):
+                    raise ValueError("peer_rgb_u8 entries must be contiguous uint8 (F,H,W,3) CUDA tensors")
+            arr = (C.c_void_p * len(peer_rgb_u8))(*[t.data_ptr() for t in peer_rgb_u8])
+            desc.peer_rgb_u8 = C.cast(arr, C.POINTER(C.c_void_p))
+            desc.num_peer_rgb_u8 = len(peer_rgb_u8)
+            self._peer_keep = (arr, list(peer_rgb_u8))
+        else:
+            desc.peer_rgb_u8 = None
+            desc.num_peer_rgb_u8 = 0
+        desc.deliver_flags = 1 if defer_delivery_join else 0  # GSW_DELIVER_NO_JOIN
         self._last_inputs = (pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view)
         self._dbg_N = None
         for _attempt in range(4):
@@ -195,6 +210,11 @@ class Engine:
         else:
             raise _lib.GswError(_lib.GSW_E_CAPACITY, "tile-entry workspace kept overflowing")
         return dict(rgb_u8=out_rgb_u8, color=out_color, invdepth=out_invdepth, radii=out_radii, seg=out_seg)
+
+    def delivery_wait(self, stream=None):
+        """Make `stream` (a torch stream; default: the current one) wait for the last delivery to host / peers."""
+        st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
+        _lib.check(self.lib.gsw_delivery_wait(self._h, st))
 
     def finish(self, raise_on_overflow=True) -> bool:
         """Wait for the last launch.  Returns True if it was valid; on overflow grows the workspace

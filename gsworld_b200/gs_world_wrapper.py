@@ -119,6 +119,13 @@ class GSWorldWrapper(_Base):
         # Optional PINNED HOST tensor (n_cams, B, H, W, 3) uint8: the observations are also delivered there, copied
         # group by group while later frames are still being blended (gsw_frames_desc.host_rgb_u8).
         self.obs_host = None
+        # Optional list of device tensors (n_cams, B, H, W, 3) uint8 on this or on peer GPUs (mapped into this
+        # process, e.g. dist.PeerObservationExchange.destinations()): the observations are also pushed there group
+        # by group on the copy stream while later frames are still being blended (gsw_frames_desc.peer_rgb_u8).
+        self.obs_peers = None
+        # With obs_host / obs_peers: do not make the render stream wait for the delivery (GSW_DELIVER_NO_JOIN); the
+        # caller orders consumers with engine.delivery_wait() and must give a persistent obs_out.
+        self.defer_delivery_join = False
         if merged_model is None and cfg_dir is not None:
             # reference path: GaussianModelMerger().load_models_from_config(CFG_DIR/<name>.json) + merge_models()
             # (gs_world_wrapper.py:75-79)
@@ -424,7 +431,10 @@ class GSWorldWrapper(_Base):
                 antialiasing=bool(self.robot_pipe.antialiasing), want_u8=True, want_invdepth=self.inv_depth_obs,
                 want_seg=self.segmentation_obs, out_rgb_u8=dst, finish=self.sync_each_step,
                 host_rgb_u8=None if (self.obs_host is None or len(groups) != 1) else
-                self.obs_host.view(len(names) * self.num_envs, H, W, 3))
+                self.obs_host.view(len(names) * self.num_envs, H, W, 3),
+                peer_rgb_u8=None if (not self.obs_peers or len(groups) != 1) else
+                [t.view(len(names) * self.num_envs, H, W, 3) for t in self.obs_peers],
+                defer_delivery_join=bool(self.defer_delivery_join and dst is not None))
             rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
             for i, c in enumerate(names):
                 gs_renders[c] = rgb[i]

@@ -115,7 +115,22 @@ typedef struct gsw_frames_desc {
                               * weight alpha*T at each pixel, GSW_SEG_NONE where nothing was composited.  No counterpart
                               * in the reference (its segmentation comes from SAPIEN's Vulkan renderer, unavailable
                               * here): SURVEY.md §8(f) row 3. */
+  /* Peer delivery (multi-GPU): HOST array of num_peer_rgb_u8 (<= 16) DEVICE pointers, each a [F,H,W,3] uint8 buffer
+   * in this or another GPU's memory that is mapped into this process (peer access / symmetric memory), or NULL.
+   * Needs out_rgb_u8.  Every finished frame group is pushed to each of them on the context's copy stream
+   * (copy engines over NVLink / NVSwitch, no SMs), overlapped with the compositing of the later frames, exactly
+   * like host_rgb_u8: this is the observation exchange of SURVEY.md §8(e) without a collective kernel.  `stream`
+   * waits for the last push; cross-rank ordering (a barrier before the data is read on the other GPU) is the
+   * caller's.  No counterpart in the reference (single GPU). */
+  uint8_t* const* peer_rgb_u8;
+  int32_t num_peer_rgb_u8;
+  /* GSW_DELIVER_NO_JOIN: `stream` does NOT wait for the last host copy / peer push of this call, so the next step
+   * can start while the delivery drains; the caller orders whoever consumes the delivered frames (and whoever
+   * overwrites out_rgb_u8) with gsw_delivery_wait.  out_rgb_u8 must then stay untouched until that wait. */
+  int32_t deliver_flags;
 } gsw_frames_desc;
+
+#define GSW_DELIVER_NO_JOIN 1
 
 /* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous. */
 int gsw_render_frames(gsw_ctx* ctx, const gsw_frames_desc* desc, gsw_stream stream);
@@ -126,6 +141,9 @@ int gsw_render_frames(gsw_ctx* ctx, const gsw_frames_desc* desc, gsw_stream stre
  * [0] = D tile entries written (static per view + dynamic per frame), [1] = entries the blend staged
  * (<= sum of per-frame list lengths; early termination reads less), [2] = entry capacity, [3] = launches. */
 int gsw_finish(gsw_ctx* ctx, int64_t* needed_entries, int64_t stats[4]);
+/* Make `stream` wait for the delivery (host_rgb_u8 / peer_rgb_u8) of the last gsw_render_frames call; a no-op if
+ * that call delivered nothing.  Needed only with GSW_DELIVER_NO_JOIN.  No counterpart in the reference. */
+int gsw_delivery_wait(gsw_ctx* ctx, gsw_stream stream);
 int gsw_reserve_entries(gsw_ctx* ctx, int64_t entries);
 /* depth sub-buckets per tile list (power of two, 1..64); 0 = automatic */
 int gsw_set_depth_buckets(gsw_ctx* ctx, int nb);
