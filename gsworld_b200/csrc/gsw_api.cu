@@ -241,6 +241,8 @@ int gsw_create(int device, gsw_ctx** out) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
   for (int k = 0; k < 5 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->grp_evt[k], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->copy_evt, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->peer_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->peer_evt, cudaEventDisableTiming);
   if (e == cudaSuccess) {
     // stream memory operation used for in-kernel completion signals (no link-time dependency on libcuda)
     cudaDriverEntryPointQueryResult qr = cudaDriverEntryPointSymbolNotFound;
@@ -283,6 +285,8 @@ int gsw_destroy(gsw_ctx* c) {
     if (c->grp_evt[k]) cudaEventDestroy(c->grp_evt[k]);
   if (c->copy_evt) cudaEventDestroy(c->copy_evt);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->peer_evt) cudaEventDestroy(c->peer_evt);
+  if (c->peer_stream) cudaStreamDestroy(c->peer_stream);
   if (c->fork_evt) cudaEventDestroy(c->fork_evt);
   if (c->join_evt) cudaEventDestroy(c->join_evt);
   if (c->side_stream) cudaStreamDestroy(c->side_stream);
@@ -555,7 +559,19 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     for (int p = 0; p < n_peer; ++p)
       if (d->peer_rgb_u8[p] != nullptr && d->peer_rgb_u8[p] != d->out_rgb_u8)
         GSW_CUDA(cudaMemcpyAsync(d->peer_rgb_u8[p] + off, d->out_rgb_u8 + off, bytes, cudaMemcpyDeviceToDevice,
-                                 c->copy_stream));
+                                 c->peer_stream));
+    return 0;
+  };
+  // the copy stream's completion event covers both delivery streams
+  auto close_delivery = [&]() -> int {
+    if (n_peer > 0) {
+      GSW_CUDA(cudaEventRecord(c->peer_evt, c->peer_stream));
+      GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->peer_evt, 0));
+    }
+    GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
+    c->delivered = true;
+    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN))
+      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
     return 0;
   };
   if (deliver && c->wait_value32 != nullptr) {
@@ -576,23 +592,25 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                            nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s, &sg)))
       return rc;
     for (int k = 0; k < sg.n; ++k) {
-      const CUresult wr = c->wait_value32 == nullptr
-                              ? CUDA_SUCCESS
-                              : wait32((CUstream)c->copy_stream, (CUdeviceptr)(uintptr_t)(sg.flag + k), sg.epoch,
-                                       CU_STREAM_WAIT_VALUE_GEQ);
+      CUresult wr = CUDA_SUCCESS;
+      if (c->wait_value32 != nullptr) {
+        wr = wait32((CUstream)c->copy_stream, (CUdeviceptr)(uintptr_t)(sg.flag + k), sg.epoch,
+                    CU_STREAM_WAIT_VALUE_GEQ);
+        if (wr == CUDA_SUCCESS && n_peer > 0)
+          wr = wait32((CUstream)c->peer_stream, (CUdeviceptr)(uintptr_t)(sg.flag + k), sg.epoch,
+                      CU_STREAM_WAIT_VALUE_GEQ);
+      }
       if (wr != CUDA_SUCCESS && c->wait_value32 != nullptr) {
         // not supported here (e.g. a restricted driver mode): order the remaining copies after the whole blend
         // launch instead, and use the grouped launches from the next call on
         c->wait_value32 = nullptr;
         GSW_CUDA(cudaEventRecord(c->grp_evt[0], s));
         GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[0], 0));
+        GSW_CUDA(cudaStreamWaitEvent(c->peer_stream, c->grp_evt[0], 0));
       }
       if ((rc = send_group(sg.cut(k), sg.cut(k + 1)))) return rc;
     }
-    GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
-    c->delivered = true;
-    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN))
-      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+    if ((rc = close_delivery())) return rc;
   } else if (deliver) {
     // blend in up to 5 frame groups; each group's uint8 frames go to the pinned host buffer on the copy stream
     // as soon as that group is done, while the next group is being composited.  The last groups are small:
@@ -608,12 +626,10 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
         return rc;
       GSW_CUDA(cudaEventRecord(c->grp_evt[k], s));
       GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[k], 0));
+      if (n_peer > 0) GSW_CUDA(cudaStreamWaitEvent(c->peer_stream, c->grp_evt[k], 0));
       if ((rc = send_group(f0, f1))) return rc;
     }
-    GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
-    c->delivered = true;
-    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN))
-      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+    if ((rc = close_delivery())) return rc;
   } else if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
                                 nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s))) {
     return rc;

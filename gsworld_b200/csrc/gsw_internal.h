@@ -183,6 +183,8 @@ struct gsw_ctx {
   void* wait_value32 = nullptr;  // cuStreamWaitValue32 (driver entry point; null: grouped blend launches instead)
   gsw::DevBuf sig;               // DoneSig counters [16] + flags [16]
   uint32_t sig_epoch = 0;
+  cudaStream_t peer_stream = nullptr;  // pushes to peer GPUs (NVLink), so that they do not queue behind PCIe copies
+  cudaEvent_t peer_evt = nullptr;
   cudaEvent_t copy_evt = nullptr;
   bool delivered = false;  // copy_evt has been recorded by a delivery
   // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are

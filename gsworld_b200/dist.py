@@ -2,9 +2,10 @@
 
 The observation path has no cross-env dependency (reference loop body gs_world_wrapper.py:242 touches only
 row i), so rank r of G simply owns a contiguous block of envs and renders it with its own libgsw context;
-the scene is replicated.  The single exchange is an all-gather of the uint8 observations so that the
-policy sees the whole batch (NCCL over NVLink on GPUs; the same code runs over gloo on CPU tensors, which
-is how tests/test_dist_gloo.py covers it).  The reference has no distributed code at all.
+the scene is replicated.  The single exchange is that of the uint8 observations so that the policy sees the
+whole batch: on GPUs through peer memory (PeerObservationExchange: copy-engine pushes over NVLink, overlapped
+with the blend), else an all-gather (gather_observations: NCCL, or gloo on CPU tensors, which is how
+tests/test_dist_gloo.py covers it).  The reference has no distributed code at all.
 """
 from __future__ import annotations
 
@@ -70,8 +71,7 @@ class PeerObservationExchange:
         wait_ready(k)       the calling stream waits for that barrier: gathered(k) then holds every rank's frames
 
     One-step slack, like a double-buffered all-gather: a rank may render step k + 1 while step k is still being
-    exchanged, and starts step k + nbuf only after the barrier of step k + nbuf - 1... of the buffer's previous
-    use has passed on this rank.  Whoever reads gathered(k) must have its reads enqueued (on a stream ordered
+    exchanged; it rewrites a buffer only after the barrier of the buffer's previous use has passed.  Whoever reads gathered(k) must have its reads enqueued (on a stream ordered
     before the rank's next publish) before step k + 1 is published: the barrier of step k + 1 is what separates
     those reads from the writes of step k + nbuf.  The reference has no multi-GPU path; this
     replaces the NCCL all-gather of §8(e) where symmetric memory is available (`available()`),
