@@ -443,6 +443,8 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    timed_launches = [0]
+
     def timed(env, wrap, steps, warmup, d2h=None):
         for _attempt in range(4):
             ms = timed_once(env, wrap, steps, warmup, d2h)
@@ -467,6 +469,7 @@ def run_ours(args):
         if prof:
             torch.cuda.profiler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        launches_before = wrap._engine.kernel_launches()
         e0.record()
         h0 = time.perf_counter()
         for _ in range(steps):
@@ -477,6 +480,7 @@ def run_ours(args):
                         d2h[i].copy_(out[c], non_blocking=True)
                 torch.cuda.current_stream().synchronize()  # the caller reads the observation every step
         host_ms = (time.perf_counter() - h0) * 1e3
+        timed_launches[0] = wrap._engine.kernel_launches() - launches_before  # kernels of the timed region only
         if world > 1:
             drain()  # the last exchanges belong to the timed steps
         e1.record()
@@ -513,12 +517,11 @@ def run_ours(args):
         if mode == "strict":
             sampler = ClockSampler(local) if rank == 0 else None
             timed(env, wrap, 0, args.warmup)
-            l_w = eng.kernel_launches()
             if sampler is not None:
                 sampler.start()
             ms = timed(env, wrap, args.steps, 0)
             clocks = sampler.stop() if sampler is not None else None
-            launches = eng.kernel_launches() - l_w
+            launches = timed_launches[0]
         else:
             ms = timed(env, wrap, args.steps, args.warmup)
         # stage breakdown + traffic counts (outside the timed region)
