@@ -40,6 +40,7 @@ SYMBOLS = {
     "gsw_render_frames": (C.c_int, [_vp, C.POINTER(FramesDesc), _vp]),
     "gsw_finish": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64 * 4)]),
     "gsw_delivery_wait": (C.c_int, [_vp, _vp]),
+    "gsw_delivery_gate": (C.c_int, [_vp, _vp]),
     "gsw_reserve_entries": (C.c_int, [_vp, _i64]),
     "gsw_set_depth_buckets": (C.c_int, [_vp, C.c_int]),
     "gsw_set_tile_culling": (C.c_int, [_vp, C.c_int]),

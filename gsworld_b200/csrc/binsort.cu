@@ -537,6 +537,13 @@ size_t scan_tmp_elems(int64_t n) {
   return (size_t)((n + per - 1) / per) + 2;
 }
 
+// medium and mid queue (half each): whole bins (<= nbins each) plus sub-segments of huge bins, of which every
+// one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries; small and huge
+// queues: one slot per bin each
+size_t seg_queue_bytes(int64_t cap, int64_t nbins) {
+  return (size_t)(8 * (cap / kSortSmemKeys) + 6 * nbins + 32) * sizeof(Segment);
+}
+
 // out_excl must hold n+1 elements (out[n] = total).  tmp: scan_tmp_elems(n) u32.
 int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s) {
   if (n <= 0) {

@@ -314,7 +314,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
                   out_color, out_invd, status, mode, view_cnt, st_u8, st_color, st_invd, lab_stream, out_seg, st_seg,
                   use_view_images, rec, pos_of, Ns, labels, Nm);
   if (sig.cnt != nullptr) {
-    // every thread's pixel stores precede the barrier; thread 0's fence makes them visible device-wide (and to
+    // every thread's pixel stores precede the barrier; thread 0's release makes them visible device-wide (and to
     // the copy engine) before the counter moves; the CTA that completes a group publishes the epoch
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -322,10 +322,15 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
       int k = 0;
       while (k + 1 < sig.n && f >= sig.cut(k + 1)) ++k;
       const uint32_t ctas = (uint32_t)(sig.cut(k + 1) - sig.cut(k)) * (uint32_t)g.T;
-      __threadfence();
-      if (atomicAdd(&sig.cnt[k], 1u) == ctas - 1u) {
-        __threadfence();
-        *reinterpret_cast<volatile uint32_t*>(&sig.flag[k]) = sig.epoch;
+      // Release-only ordering: the counter increment is a gpu-scope release (cumulative over the CTA's stores
+      // through the barrier above), the flag store a system-scope release.  __threadfence() would do, but it also
+      // carries acquire semantics, for which ptxas emits CCTL.IVALL: every one of the F*T CTAs would invalidate
+      // its SM's L1 under the co-resident CTAs' record gathers (measured: +9 % blend time with signalling on).
+      uint32_t old;
+      asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(sig.cnt + k) : "memory");
+      if (old == ctas - 1u) {
+        __threadfence();  // acquire side, once per group: the other CTAs' releases on the counter happen-before the flag
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sig.flag + k), "r"(sig.epoch) : "memory");
       }
     }
   }

@@ -27,6 +27,10 @@ void set_error(const char* fmt, ...) {
 
 int DevBuf::reserve(size_t need) {
   if (need <= bytes) return 0;
+  if (fixed) {  // carved out of a fixed array (gsw_rasterize_forward_static): growing would mean allocating
+    set_error("fixed workspace slice of %zu bytes cannot hold %zu bytes", bytes, need);
+    return GSW_E_NOMEM;
+  }
   if (p) {
     cudaError_t e = cudaFree(p);  // synchronises: no kernel still uses the old block afterwards
     p = nullptr;
@@ -48,12 +52,28 @@ int DevBuf::reserve(size_t need) {
 }
 
 void DevBuf::release() {
-  if (p) cudaFree(p);
+  if (p && !fixed) cudaFree(p);
   p = nullptr;
   bytes = 0;
 }
 
 namespace {
+
+// tan(fov/2) and the trivial frame maps of the single-frame entry points: [tanx, tany, env 0, view 0].  Written by
+// a one-thread kernel from by-value arguments, so those calls read no host memory after they return.
+__global__ void set_single_cam_kernel(float* cam, float tanx, float tany) {
+  cam[0] = tanx;
+  cam[1] = tany;
+  reinterpret_cast<int32_t*>(cam)[2] = 0;
+  reinterpret_cast<int32_t*>(cam)[3] = 0;
+}
+
+int stage_single_cam(DevBuf& cam, float tanx, float tany, cudaStream_t s) {
+  set_single_cam_kernel<<<1, 1, 0, s>>>(cam.as<float>(), tanx, tany);
+  count_launches(1);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
 
 int ilog2(int v) {
   int l = 0;
@@ -127,7 +147,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   int kept_s = 0, kept_d = 0;
   // medium and mid queue (half each): whole bins (<= nbins each) plus sub-segments of huge bins, of which
   // every one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries
-  if ((rc = w.seg_queue.reserve((size_t)(8 * (cap / kSortSmemKeys) + 6 * nbins + 32) * 16))) return rc;
+  if ((rc = w.seg_queue.reserve(seg_queue_bytes(cap, nbins)))) return rc;
 
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
@@ -243,6 +263,7 @@ int gsw_create(int device, gsw_ctx** out) {
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->copy_evt, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->peer_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->peer_evt, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->gate_evt, cudaEventDisableTiming);
   if (e == cudaSuccess) {
     // stream memory operation used for in-kernel completion signals (no link-time dependency on libcuda)
     cudaDriverEntryPointQueryResult qr = cudaDriverEntryPointSymbolNotFound;
@@ -286,6 +307,7 @@ int gsw_destroy(gsw_ctx* c) {
   if (c->copy_evt) cudaEventDestroy(c->copy_evt);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->peer_evt) cudaEventDestroy(c->peer_evt);
+  if (c->gate_evt) cudaEventDestroy(c->gate_evt);
   if (c->peer_stream) cudaStreamDestroy(c->peer_stream);
   if (c->fork_evt) cudaEventDestroy(c->fork_evt);
   if (c->join_evt) cudaEventDestroy(c->join_evt);
@@ -502,6 +524,12 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     set_error("gsw_render_frames: missing camera / frame map / pose pointer");
     return GSW_E_INVALID;
   }
+  // delivery arguments are checked before anything is enqueued
+  const int n_peer = d->peer_rgb_u8 ? d->num_peer_rgb_u8 : 0;
+  if (n_peer < 0 || n_peer > 16 || ((d->host_rgb_u8 || n_peer > 0) && !d->out_rgb_u8)) {
+    set_error("gsw_render_frames: host_rgb_u8 / peer_rgb_u8 need out_rgb_u8; at most 16 peers");
+    return GSW_E_INVALID;
+  }
   Guard gd(c->device);
   cudaStream_t s = (cudaStream_t)stream;
   const int nb = c->nb_user > 0 ? c->nb_user : 1;
@@ -542,11 +570,6 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                                      d->bg, d->out_rgb_u8 != nullptr, d->out_color != nullptr,
                                      d->out_invdepth != nullptr, d->out_seg != nullptr, s)))
       return rc;
-  }
-  const int n_peer = d->peer_rgb_u8 ? d->num_peer_rgb_u8 : 0;
-  if (n_peer < 0 || n_peer > 16 || ((d->host_rgb_u8 || n_peer > 0) && !d->out_rgb_u8)) {
-    set_error("gsw_render_frames: host_rgb_u8 / peer_rgb_u8 need out_rgb_u8; at most 16 peers");
-    return GSW_E_INVALID;
   }
   const bool deliver = d->host_rgb_u8 != nullptr || n_peer > 0;
   // one group of finished frames to every destination (pinned host and / or peer GPUs), on the copy stream
@@ -649,6 +672,18 @@ int gsw_delivery_wait(gsw_ctx* c, gsw_stream stream) {
   if (!c->delivered) return GSW_OK;
   Guard gd(c->device);
   GSW_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->copy_evt, 0));
+  return GSW_OK;
+}
+
+int gsw_delivery_gate(gsw_ctx* c, gsw_stream stream) {
+  if (!c) {
+    set_error("gsw_delivery_gate: NULL ctx");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  GSW_CUDA(cudaEventRecord(c->gate_evt, (cudaStream_t)stream));
+  GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->gate_evt, 0));
+  GSW_CUDA(cudaStreamWaitEvent(c->peer_stream, c->gate_evt, 0));
   return GSW_OK;
 }
 
@@ -808,11 +843,7 @@ int gsw_rasterize_forward(gsw_ctx* c, int32_t P, int32_t sh_degree, int32_t M, c
   // tan(fov) and the trivial frame maps live in a small staging block: [tanx, tany, 0(int), 0(int)]
   int rc;
   if ((rc = c->ws.cam.reserve(64))) return rc;
-  struct {
-    float tx, ty;
-    int32_t e, v;
-  } hs{tan_fovx, tan_fovy, 0, 0};
-  GSW_CUDA(cudaMemcpyAsync(c->ws.cam.p, &hs, sizeof hs, cudaMemcpyHostToDevice, s));  // pageable: staged by the driver
+  if ((rc = stage_single_cam(c->ws.cam, tan_fovx, tan_fovy, s))) return rc;
   const float* tanfov = c->ws.cam.as<float>();
   const int32_t* fe = c->ws.cam.as<int32_t>() + 2;
   const int32_t* fv = c->ws.cam.as<int32_t>() + 3;
@@ -884,6 +915,7 @@ int na_setup(int device, NaDevice& nd) {
     bytes = (bytes + 255) & ~(size_t)255;
     b.p = base + off;
     b.bytes = bytes;
+    b.fixed = true;  // reserve() beyond the slice fails with GSW_E_NOMEM instead of freeing / allocating
     off += bytes;
   };
   gsw_ctx& c = nd.ctx;
@@ -901,10 +933,15 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.keys, (size_t)kNaMaxEntries * 8);
   carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
   carve(w.status, 128);
-  carve(w.seg_queue, (size_t)(8 * (kNaMaxEntries / kSortSmemKeys) + 6 * nbins + 32) * 16);
+  carve(w.seg_queue, seg_queue_bytes(kNaMaxEntries, nbins));
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view
-  carve(w.cta_hist, (size_t)((kNaMaxP + 2047) / 2048) * (kNaMaxTiles + 1) * 4 + 16);
+  {  // the largest per-CTA histogram block run_pipeline can ask for within the limits: kNaMaxP items, kNaMaxTiles tiles
+    FrameGeom gmax{};
+    gmax.T = kNaMaxTiles;
+    gmax.NB = 1;
+    carve(w.cta_hist, cta_hist_words(kNaMaxP, 1, gmax) * 4 + 16);
+  }
   if (off > kNaBytes) {
     set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);
     return GSW_E_NOMEM;
@@ -984,19 +1021,16 @@ int gsw_rasterize_forward_static(int32_t P, int32_t sh_degree, int32_t M, const 
   st.slot = nullptr;
   st.sh_degree = sh_degree;
   st.M = M;
-  struct {
-    float tx, ty;
-    int32_t e, v;
-  } hs{tan_fovx, tan_fovy, 0, 0};
-  GSW_CUDA(cudaMemcpyAsync(c->ws.cam.p, &hs, sizeof hs, cudaMemcpyHostToDevice, s));
+  int rc;
+  if ((rc = stage_single_cam(c->ws.cam, tan_fovx, tan_fovy, s))) return rc;
   const float* tanfov = c->ws.cam.as<float>();
   const int32_t* fe = c->ws.cam.as<int32_t>() + 2;
   const int32_t* fv = c->ws.cam.as<int32_t>() + 3;
   // Every workspace request below fits its slice (sizes were checked against the maxima above), so the
   // grow-only buffers never reach their allocation branch; the zero-initialised state is set by
   // run_pipeline's memsets on the stream.
-  int rc = run_pipeline(c, st, P, P, nullptr, nullptr, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe,
-                        fv, nullptr, 0, s);
+  rc = run_pipeline(c, st, P, P, nullptr, nullptr, nullptr, 0, 1, 1, g, viewmatrix, projmatrix, campos, tanfov, fe, fv,
+                    nullptr, 0, s);
   if (rc) return rc;
   c->last.single = true;
   if ((rc = launch_blend(c, 1, 0, 1, c->last.nbins, fv, c->last.cap, g, nullptr, bg, nullptr, out_color, out_invdepth, nullptr, false, s)))

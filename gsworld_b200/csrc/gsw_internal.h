@@ -32,7 +32,8 @@ constexpr int kNumStages = 8;  // preprocess_static, preprocess_dynamic, scan, s
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
-  int reserve(size_t need);  // returns 0 / cudaError
+  bool fixed = false;  // a slice of memory owned by someone else: never grown, never freed (GSW_E_NOMEM instead)
+  int reserve(size_t need);  // returns 0 / cudaError / GSW_E_NOMEM
   void release();
   template <typename T>
   T* as() const { return reinterpret_cast<T*>(p); }
@@ -185,6 +186,7 @@ struct gsw_ctx {
   uint32_t sig_epoch = 0;
   cudaStream_t peer_stream = nullptr;  // pushes to peer GPUs (NVLink), so that they do not queue behind PCIe copies
   cudaEvent_t peer_evt = nullptr;
+  cudaEvent_t gate_evt = nullptr;  // gsw_delivery_gate
   cudaEvent_t copy_evt = nullptr;
   bool delivered = false;  // copy_evt has been recorded by a delivery
   // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are
@@ -238,5 +240,6 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
                            bool want_invd, bool want_seg, cudaStream_t s);
 
 size_t scan_tmp_elems(int64_t n);
+size_t seg_queue_bytes(int64_t cap, int64_t nbins);  // sort work queues (launch_sort_bins) for `cap` entries in `nbins` bins
 
 }  // namespace gsw

@@ -56,26 +56,38 @@ def gather_observations(local: Dict[str, torch.Tensor], num_envs: int, group=Non
 
 
 class PeerObservationExchange:
-    """Every rank's uint8 observations in every rank's memory WITHOUT a collective kernel.
+    """Every rank's uint8 observations in the memory of the ranks that consume them, WITHOUT a collective kernel.
 
     Each rank owns `nbuf` symmetric buffers [world, *shard_shape] (torch symmetric memory: the same allocation
-    on every GPU of the box, each mapped into every process over NVLink / NVSwitch).  Step k of rank r:
+    on every GPU of the box, each mapped into every process over NVLink / NVSwitch).  `roots` names the ranks
+    that need the whole batch: None = every rank (an all-gather), [0] = the policy rank only ("or
+    gather-style if only rank 0 needs it"), which cuts the NVLink traffic into every other GPU to nothing.
+    Step k of rank r:
 
-        begin(k)            the render stream waits until buffer k % nbuf may be written again
+        begin(k, engine)    the render stream waits until this rank's slot of buffer k % nbuf may be rewritten, and
+                            libgsw's delivery streams are gated (gsw_delivery_gate) behind the exchange stream, so
+                            the pushes of step k start only once the readers of the buffer's previous use are done
         local_out(k)        slot r of the rank's own buffer: the renderer composites straight into it (obs_out)
-        destinations(k)     slot r of the same buffer on every OTHER rank: libgsw's copy stream pushes each finished
+        destinations(k)     slot r of the same buffer on every OTHER root: libgsw's peer stream pushes each finished
                             frame group there with the copy engines (no SMs, no NCCL kernel) while later frames
                             are still being composited (gsw_frames_desc.peer_rgb_u8, GSW_DELIVER_NO_JOIN)
-        publish(k, engine)  on the exchange's own stream: wait for this rank's pushes, then a device-side barrier
-                            over all ranks; the render stream is not involved and goes on with step k + 1
-        wait_ready(k)       the calling stream waits for that barrier: gathered(k) then holds every rank's frames
+        publish(k, engine)  on the exchange's own stream: wait for this rank's pushes, then tell the consumers.
+                            roots=None: one device-side barrier over all ranks.  roots given: a signal to every
+                            root (symmetric-memory signal pad), and a root waits for one signal per producer.
+                            The render stream is not involved and goes on with step k + 1.
+        wait_ready(k)       the calling stream waits until gathered(k) holds every rank's frames (roots only)
+        release(k)          the calling stream's reads of gathered(k) are enqueued: the buffer may be reused
 
-    One-step slack, like a double-buffered all-gather: a rank may render step k + 1 while step k is still being
-    exchanged; it rewrites a buffer only after the barrier of the buffer's previous use has passed.  Whoever reads gathered(k) must have its reads enqueued (on a stream ordered
-    before the rank's next publish) before step k + 1 is published: the barrier of step k + 1 is what separates
-    those reads from the writes of step k + nbuf.  The reference has no multi-GPU path; this
-    replaces the NCCL all-gather of §8(e) where symmetric memory is available (`available()`),
-    `gather_observations` stays as the fallback."""
+    Reuse is enforced, not left to convention.  A buffer is rewritten by step k + nbuf.  Before that step's pushes
+    may start, every consumer's reads of step k must have completed: release(k) records an event, the exchange
+    stream waits for it before it enters the barrier (roots=None) or before it returns a credit signal to every
+    producer (roots given), and begin(k + nbuf) orders the deliveries behind that.  A consumer that called
+    wait_ready(k) and has not called release(k) when the buffer comes up for reuse makes publish() raise instead
+    of racing.  One-step slack with nbuf = 2: render step k + 1, consume step k (wait_ready, read, release), publish
+    step k + 1.  The reference has no multi-GPU path; `gather_observations` stays as the fallback."""
+
+    _CH_DATA, _CH_CREDIT = 1, 2  # signal-pad channels (0 is the barrier's)
+    _TIMEOUT_MS = 30000          # a device-side wait that outlives this traps instead of hanging the GPU
 
     @staticmethod
     def available() -> bool:
@@ -85,28 +97,48 @@ class PeerObservationExchange:
         except Exception:
             return False
 
-    def __init__(self, shard_shape, device, group=None, nbuf: int = 2):
+    def __init__(self, shard_shape, device, group=None, nbuf: int = 2, roots=None):
         import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
         self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
         self.shard_shape = tuple(int(x) for x in shard_shape)
         self.nbuf = nbuf
+        self.roots = None if roots is None else sorted(set(int(r) for r in roots))
+        if self.roots is not None and not all(0 <= r < self.world for r in self.roots):
+            raise ValueError(f"roots {roots} outside world of {self.world}")
+        self.is_root = self.roots is None or self.rank in self.roots
         full = (self.world,) + self.shard_shape
         self._local, self._hdl, self._dst = [], [], []
+        targets = range(self.world) if self.roots is None else self.roots
         for _ in range(nbuf):
             t = symm_mem.empty(full, dtype=torch.uint8, device=device)
             h = symm_mem.rendezvous(t, self.group)
             self._local.append(t)
             self._hdl.append(h)
-            self._dst.append([h.get_buffer(p, full, torch.uint8)[self.rank] for p in range(self.world)
-                              if p != self.rank])
+            self._dst.append([h.get_buffer(p, full, torch.uint8)[self.rank] for p in targets if p != self.rank])
         self.stream = torch.cuda.Stream(device=device)
         self._ready = [torch.cuda.Event() for _ in range(nbuf)]
+        self._released = [None] * nbuf   # event recorded by release() of the buffer's last use
+        self._reading = [False] * nbuf   # wait_ready() seen, release() not yet
+        self._credit_due = [False] * nbuf  # roots mode, on a root: producers still wait for this buffer's credit
         self._used = [False] * nbuf
 
-    def begin(self, k: int):
-        if self._used[k % self.nbuf]:  # barrier of the buffer's previous use
-            torch.cuda.current_stream().wait_event(self._ready[k % self.nbuf])
+    # -- producer side --
+    def begin(self, k: int, engine=None):
+        b = k % self.nbuf
+        cur = torch.cuda.current_stream()
+        if self._used[b]:  # this rank's own pushes of the buffer's previous use are done (they read local_out)
+            cur.wait_event(self._ready[b])
+        if self._released[b] is not None:  # ... and so are the local consumer's reads of it
+            cur.wait_event(self._released[b])
+        if self.roots is not None and self._used[b]:
+            # credit from every root: its consumer has released step k - nbuf (a root needs none from itself)
+            with torch.cuda.stream(self.stream):
+                for r in self.roots:
+                    if r != self.rank:
+                        self._hdl[b].wait_signal(r, self._CH_CREDIT, self._TIMEOUT_MS)
+        if engine is not None:  # the pushes of step k wait for the barrier / credits above, the compositing does not
+            engine.delivery_gate(self.stream)
 
     def local_out(self, k: int) -> torch.Tensor:
         return self._local[k % self.nbuf][self.rank]
@@ -115,14 +147,56 @@ class PeerObservationExchange:
         return self._dst[k % self.nbuf]
 
     def publish(self, k: int, engine):
+        b = k % self.nbuf
+        nxt = (k + 1) % self.nbuf  # the buffer step k + 1 rewrites
+        if self._reading[nxt]:
+            raise RuntimeError(f"PeerObservationExchange: gathered({k + 1 - self.nbuf}) was handed out by wait_ready() "
+                               f"and never release()d, but step {k + 1} is about to overwrite it")
         engine.delivery_wait(self.stream)
         with torch.cuda.stream(self.stream):
-            self._hdl[k % self.nbuf].barrier()
-            self._ready[k % self.nbuf].record()
-        self._used[k % self.nbuf] = True
+            if self.roots is None:
+                # entering barrier k certifies that this rank no longer reads the buffer step k + 1 will rewrite
+                if self._released[nxt] is not None:
+                    self.stream.wait_event(self._released[nxt])
+                self._hdl[b].barrier(0, self._TIMEOUT_MS)
+            else:
+                if self._credit_due[nxt]:  # nobody consumed that step: hand its credit back now (exactly one per use)
+                    self._send_credit(nxt)
+                for r in self.roots:
+                    if r != self.rank:
+                        self._hdl[b].put_signal(r, self._CH_DATA, self._TIMEOUT_MS)
+                if self.is_root:
+                    for p in range(self.world):
+                        if p != self.rank:
+                            self._hdl[b].wait_signal(p, self._CH_DATA, self._TIMEOUT_MS)
+                    self._credit_due[b] = True
+            self._ready[b].record()
+        self._used[b] = True
 
+    def _send_credit(self, b: int):  # on self.stream
+        for p in range(self.world):
+            if p != self.rank:
+                self._hdl[b].put_signal(p, self._CH_CREDIT, self._TIMEOUT_MS)
+        self._credit_due[b] = False
+
+    # -- consumer side --
     def wait_ready(self, k: int):
+        if not self.is_root:
+            raise RuntimeError("wait_ready: this rank is not a root of the exchange")
         torch.cuda.current_stream().wait_event(self._ready[k % self.nbuf])
+        self._reading[k % self.nbuf] = True
 
     def gathered(self, k: int) -> torch.Tensor:
         return self._local[k % self.nbuf]
+
+    def release(self, k: int):
+        """The current stream's reads of gathered(k) are all enqueued; the buffer may be rewritten after them."""
+        b = k % self.nbuf
+        ev = torch.cuda.Event()
+        ev.record()
+        self._released[b] = ev
+        self._reading[b] = False
+        if self.roots is not None and self.is_root and self._credit_due[b]:  # hand the credit back to every producer
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(ev)
+                self._send_credit(b)

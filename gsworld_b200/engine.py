@@ -216,6 +216,12 @@ class Engine:
         st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
         _lib.check(self.lib.gsw_delivery_wait(self._h, st))
 
+    def delivery_gate(self, stream=None):
+        """The next launch's host copies / peer pushes start only after the work enqueued so far on `stream`
+        (a torch stream; default: the current one) has completed."""
+        st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
+        _lib.check(self.lib.gsw_delivery_gate(self._h, st))
+
     def finish(self, raise_on_overflow=True) -> bool:
         """Wait for the last launch.  Returns True if it was valid; on overflow grows the workspace
         (caller must re-launch) and returns False, or raises."""

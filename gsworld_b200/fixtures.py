@@ -324,6 +324,16 @@ class FakeEnv:
     def _refresh(self):
         self._link_mats = torch.from_numpy(forward_kinematics(self.robot_uid, self._q)).to(self.device)
 
+    # -- what render_current_step asks of a ManiSkill BaseEnv (gs_world_wrapper.py:200-230) --
+    def get_info(self):
+        return {"success": torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)}
+
+    def get_obs(self, info=None):
+        return {"sensor_data": {c: {} for c in self.cameras}}
+
+    def get_reward(self, obs=None, action=None, info=None):
+        return torch.zeros(self.num_envs, device=self.device)
+
     # -- the calls GSWorldWrapper makes --
     def get_state_dict(self):
         return {"actors": {k: torch.from_numpy(v.astype(np.float32)).to(self.device) for k, v in self._obj.items()}}

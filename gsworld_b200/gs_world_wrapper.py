@@ -21,6 +21,7 @@ strict_reference=True reproduces reference quirk Q1: every env 
 from __future__ import annotations
 
 import math
+from collections.abc import Mapping
 from typing import Dict, List, Optional, Union
 
 import numpy as np
@@ -31,7 +32,7 @@ from . import rig_tables as rt
 from .cameras import Camera
 from .engine import Engine
 from .rigid import extract_rigid_transform, pose7_to_matrix
-from .rotation_conversions import matrix_to_quaternion
+from .rotation_conversions import matrix_to_quaternion, quaternion_multiply
 
 try:  # the reference subclasses gym.Wrapper; gymnasium is optional here
     import gymnasium as _gym
@@ -77,6 +78,63 @@ class _HostStage:
         self.d.copy_(self.h[self.i], non_blocking=True)
         self.ev[self.i].record()
         return self.d
+
+
+class _MovablePts(Mapping):
+    """The reference's `gs_movable_pts` dict (gs_world_wrapper.py:131,160): name -> (xyz (B,n,3), scaling (n,3) for
+    links / (B,n,3) for objects, rotation (B,n,4), opacity (n,1,1)), raw (un-activated) parameters in the GS frame.
+
+    The batched engine never materialises these tensors (the transform is fused into the rasterizer's preprocess
+    kernel), so this legacy view computes an entry from the current pose table with a few torch statements the first
+    time somebody reads it after a step (gs_utils.py:283-385 order: scale, rotate, translate; Q4 inverse_sigmoid
+    scaling; Q12 quaternion re-scaling).  Always batched (B, n, .), also for B == 1 (the reference's B == 1 shapes
+    are a quirk of its bmm branches).  Not on the hot path."""
+
+    def __init__(self, wrap):
+        self._w = wrap
+        self._cache = {}
+
+    def invalidate(self):
+        self._cache.clear()
+
+    def _names(self):
+        w = self._w
+        return [n for n in w._link_names if n in w.gs_semantics] + list(w._obj_names)
+
+    def __iter__(self):
+        return iter(self._names())
+
+    def __len__(self):
+        return len(self._names())
+
+    def __getitem__(self, name):
+        if name in self._cache:
+            return self._cache[name]
+        w = self._w
+        if name in w._obj_names:
+            s = len(w._link_names) + w._obj_names.index(name)
+        elif name in w._link_names and name in w.gs_semantics:
+            s = w._link_names.index(name)
+        else:
+            raise KeyError(name)
+        g = w.initial_merger_robot
+        idx = torch.where(w._slot == s)[0]
+        P = w._pose[:, s]
+        xyz, ls, q, op = (a[idx].to(P.device) for a in (g._xyz, g._scaling, g._rotation, g._opacity))
+        R, t, qR, kappa = P[:, 0:9].reshape(-1, 3, 3), P[:, 9:12], P[:, 12:16], P[:, 16]
+        B = P.shape[0]
+        if bool((P[:, 17] != 0).any()):
+            xb = xyz[None] * kappa[:, None, None]
+            u = torch.exp(ls)[None] * kappa[:, None, None]
+            scaling = torch.log(u / (1 - u))
+        else:
+            xb = xyz[None].expand(B, -1, 3)
+            scaling = ls
+        xb = torch.matmul(R[:, None], xb[..., None]).squeeze(-1) + t[:, None, :]
+        norm = q.norm(dim=-1, keepdim=True)
+        rot = quaternion_multiply(qR[:, None, :].expand(B, q.shape[0], 4), (q / norm)[None].expand(B, -1, 4)) * norm
+        self._cache[name] = (xb, scaling, rot, op)
+        return self._cache[name]
 
 
 class GSWorldWrapper(_Base):
@@ -141,7 +199,7 @@ class GSWorldWrapper(_Base):
         self.initial_merger_robot = merged_model
         self.gs_link_pose_mats = [torch.as_tensor(m, dtype=torch.float32, device=self.device).reshape(1, 4, 4)
                                   for m in scan_link_mats]
-        self.gs_movable_pts = dict()
+        self.gs_movable_pts = _MovablePts(self)  # lazy legacy view, see _MovablePts
         self._engine = engine if engine is not None else Engine(self.device)
         # exact tile culling (include/gsw.h): observations are bit-identical with it on or off; off keeps the
         # reference's tile lists for the parity taps
@@ -165,6 +223,7 @@ class GSWorldWrapper(_Base):
         g = self.initial_merger_robot
         sem = g._semantics.long().squeeze(-1)
         slot = torch.full_like(sem, -1, dtype=torch.int32)
+        self._slot = slot  # filled below; kept for the lazy gs_movable_pts view
         for i, name in enumerate(self._link_names):  # later keys overwrite earlier ones, as the write-back loop does
             if name not in self.gs_semantics:
                 continue
@@ -209,6 +268,7 @@ class GSWorldWrapper(_Base):
         Same matrix algebra as the reference (gs_world_wrapper.py:115-120, :139-156); the Gaussian-level
         part (gs_utils.transform_gaussians) is fused into the rasterizer's preprocess kernel."""
         be, dev = self.base_env, self.device
+        self.gs_movable_pts.invalidate()
         links = be.agent.robot.get_links()
         mats = [l.pose.to_transformation_matrix() for l in links]
         if self.fused_host and mats[0].device.type == "cpu" and torch.device(dev).type == "cuda":
@@ -302,10 +362,10 @@ class GSWorldWrapper(_Base):
     def _views(self, cam_names):
         """Stack the view tensors the engine consumes and the frame -> view map.
 
-        strict_reference: one view per camera from env 0's parameters through the reference's own numpy
-        path (bit-identical camera matrices).  Otherwise each env's own camera, composed batched on the
-        device in fp32 (no .cpu() round trip); a camera whose parameters are identical for every env
-        (fixed third-person mount) is collapsed to a single view so the static scene is projected once."""
+        fused_host (default): gsw_compose_cameras, one launch per camera, no host sync.  Otherwise the reference's
+        own torch / numpy statements (bit-identical camera matrices; validation path): strict_reference -> one
+        view per camera from env 0's parameters, else each env's own camera, where a camera whose parameters are
+        identical for every env (fixed third-person mount) collapses to a single view."""
         params = self.base_env.get_sensor_params()
         B = self.num_envs
         if self.fused_host:
@@ -320,22 +380,22 @@ class GSWorldWrapper(_Base):
                                   dtype=torch.float32, device=self.device)
             fv = torch.arange(len(cam_names), dtype=torch.int32, device=self.device).repeat_interleave(B)
             return view.contiguous(), proj.contiguous(), campos.contiguous(), tanfov, fv
-        views, projs, centers, tans, fvs, base = [], [], [], [], [], 0
+        # each env's own camera through the same reference statements (validation path: one small torch / numpy
+        # round trip per camera); a camera whose parameters are identical for every env collapses to one view
+        cams, fvs = [], []
         for c in cam_names:
-            ext = params[c]["extrinsic_cv"].to(self.device, torch.float32)
-            K = params[c]["intrinsic_cv"].to(self.device, torch.float32)
+            ext, K = params[c]["extrinsic_cv"], params[c]["intrinsic_cv"]
             shared = bool(((ext == ext[:1]).all() & (K == K[:1]).all()).item())
-            if shared:
-                ext, K = ext[:1], K[:1]
-            H, W = self._sensor_hw(c)
-            v, p, cc, tf = self._camera_batch(ext, K, H, W)
-            views.append(v); projs.append(p); centers.append(cc); tans.append(tf)
-            n = v.shape[0]
+            base = len(cams)
+            cams += [self._camera_for(params[c], c, e, self.device) for e in range(1 if shared else B)]
             fvs.append(torch.full((B,), base, dtype=torch.int32, device=self.device) if shared
                        else base + torch.arange(B, dtype=torch.int32, device=self.device))
-            base += n
-        return (torch.cat(views).contiguous(), torch.cat(projs).contiguous(), torch.cat(centers).contiguous(),
-                torch.cat(tans).contiguous(), torch.cat(fvs).contiguous())
+        view = torch.stack([c.world_view_transform for c in cams])
+        proj = torch.stack([c.full_proj_transform for c in cams])
+        campos = torch.stack([c.camera_center for c in cams])
+        tanfov = torch.tensor([[math.tan(c.FoVx * 0.5), math.tan(c.FoVy * 0.5)] for c in cams],
+                              dtype=torch.float32, device=self.device)
+        return view.contiguous(), proj.contiguous(), campos.contiguous(), tanfov, torch.cat(fvs).contiguous()
 
     def _views_fused(self, params, cam_names):
         """Camera matrices through gsw_compose_cameras: no host sync.  strict -> env 0's camera for every env;
@@ -386,26 +446,6 @@ class GSWorldWrapper(_Base):
                                          cb["proj"][sl], cb["campos"][sl], cb["tanfov"][sl])
             base += n
         return cb["view"], cb["proj"], cb["campos"], cb["tanfov"], cb["fv"]
-
-    def _camera_batch(self, ext, K, H, W, znear=0.01, zfar=100.0):
-        """cam_maniskill2gs + Camera.__init__ for n cameras at once, fp32 on the device."""
-        n, dev = ext.shape[0], ext.device
-        bottom = torch.tensor([0.0, 0.0, 0.0, 1.0], device=dev).expand(n, 1, 4)
-        c2w = torch.linalg.inv(torch.cat([ext, bottom], 1))
-        c2w[:, :3, 3] = c2w[:, :3, 3] * self.scale_sim2real
-        w2c = torch.linalg.inv(self.rigid_sim2real @ c2w)  # == getWorld2View2(R, T) for trans=0, scale=1
-        view = w2c.transpose(1, 2).contiguous()
-        tanx = W / (2 * K[:, 0, 0])  # tan(FoVx/2) with FoVx = 2 atan(W / 2fx)
-        tany = H / (2 * K[:, 1, 1])
-        P = torch.zeros((n, 4, 4), device=dev)
-        P[:, 0, 0] = 1.0 / tanx
-        P[:, 1, 1] = 1.0 / tany
-        P[:, 3, 2] = 1.0
-        P[:, 2, 2] = zfar / (zfar - znear)
-        P[:, 2, 3] = -(zfar * znear) / (zfar - znear)
-        proj = view.bmm(P.transpose(1, 2))
-        campos = torch.linalg.inv(view)[:, 3, :3]
-        return view, proj.contiguous(), campos.contiguous(), torch.stack([tanx, tany], 1)
 
     def _maps(self, n_cams):
         if n_cams not in self._frame_maps:  # frame = cam * B + env

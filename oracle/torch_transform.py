@@ -228,7 +228,7 @@ class RefPath:
             out[cam] = per_env
         return out
 
-    def render_gsworld(self, strict=True, return_aux=False):
+    def render_gsworld(self, strict=True, return_aux=False, debug=False):
         """{cam: uint8 (B,H,W,3)} exactly as _render_gsworld builds it (gs_world_wrapper.py:232-275)."""
         cams = self.cameras(strict)
         outs, aux = {}, {}
@@ -253,7 +253,7 @@ class RefPath:
                     gs_render = rendering.permute(1, 2, 0).unsqueeze(dim=0)
                     frames.append((gs_render * 255).clamp(0, 255).to(torch.uint8))
                     continue
-                r = render_ref(per_env[i], g)
+                r = render_ref(per_env[i], g, debug=debug)
                 frames.append(orc.to_uint8_hwc(np.clip(r["color"], 0.0, 1.0))[None])
                 auxes.append(r)
             outs[cam] = torch.vstack(frames) if self.rasterizer is not None else np.concatenate(frames, 0)

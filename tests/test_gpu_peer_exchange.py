@@ -30,28 +30,57 @@ def _worker(rank, world, port):
         wrap = GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene,
                               scan_link_mats=list(scan), strict_reference=False)
         cams = list(env.cameras)
-        xchg = PeerObservationExchange((len(cams), B, H, W, 3), dev)
         wrap.reset(seed=rank)
-        for mode in ("joined", "deferred"):
-            for k in range(5):  # both buffers are reused
-                xchg.begin(k)
-                wrap.obs_out = xchg.local_out(k)
-                wrap.obs_peers = xchg.destinations(k)
-                wrap.defer_delivery_join = mode == "deferred"
-                wrap.sync_each_step = mode != "deferred"
+        consumer = torch.cuda.Stream(device=dev)
+        for roots in (None, [0]):
+            xchg = PeerObservationExchange((len(cams), B, H, W, 3), dev, roots=roots)
+            root = roots is None or rank in roots
+            for mode in ("joined", "deferred"):
+                for k in range(5):  # both buffers are reused
+                    xchg.begin(k, wrap._engine)
+                    wrap.obs_out = xchg.local_out(k)
+                    wrap.obs_peers = xchg.destinations(k)
+                    wrap.defer_delivery_join = mode == "deferred"
+                    wrap.sync_each_step = mode != "deferred"
+                    obs = wrap.step(None)[0]
+                    xchg.publish(k, wrap._engine)
+                    mine = torch.stack([obs["sensor_data"][c]["rgb"] for c in cams])  # (C,B,H,W,3)
+                    assert obs["sensor_data"][cams[0]]["rgb"].data_ptr() == xchg.local_out(k).data_ptr()  # in place
+                    want = torch.empty((world,) + tuple(mine.shape), dtype=torch.uint8, device=dev)
+                    dist.all_gather_into_tensor(want.view(-1), mine.contiguous().view(-1))
+                    if root:
+                        xchg.wait_ready(k)
+                        torch.cuda.synchronize()
+                        wrap._engine.finish()
+                        got = xchg.gathered(k)
+                        assert torch.equal(got, want), f"rank {rank} {mode} {roots} step {k}: differs from the all-gather"
+                        assert not torch.equal(want[0], want[1])  # the shards really differ
+                        xchg.release(k)
+                    dist.barrier()
+            # a slow reader on its own stream: step k is read (after a long spin) while steps k+1, k+2 are rendered
+            # and exchanged; with two buffers step k+2 rewrites the buffer being read unless release() is honoured
+            snaps, wants = [], []
+            for k in range(5, 11):
+                xchg.begin(k, wrap._engine)
+                wrap.obs_out, wrap.obs_peers = xchg.local_out(k), xchg.destinations(k)
+                wrap.defer_delivery_join, wrap.sync_each_step = True, False
                 obs = wrap.step(None)[0]
+                if root and k > 5:  # consume step k - 1 one step behind, slowly
+                    with torch.cuda.stream(consumer):
+                        xchg.wait_ready(k - 1)
+                        torch.cuda._sleep(int(3e6))  # ~1.5 ms of spinning before the read
+                        snaps.append(xchg.gathered(k - 1).clone())
+                        xchg.release(k - 1)
                 xchg.publish(k, wrap._engine)
-                xchg.wait_ready(k)
-                mine = torch.stack([obs["sensor_data"][c]["rgb"] for c in cams])  # (C,B,H,W,3)
-                assert obs["sensor_data"][cams[0]]["rgb"].data_ptr() == xchg.local_out(k).data_ptr()  # in place
+                mine = torch.stack([obs["sensor_data"][c]["rgb"] for c in cams])
                 want = torch.empty((world,) + tuple(mine.shape), dtype=torch.uint8, device=dev)
                 dist.all_gather_into_tensor(want.view(-1), mine.contiguous().view(-1))
-                torch.cuda.synchronize()
-                wrap._engine.finish()
-                got = xchg.gathered(k)
-                assert torch.equal(got, want), f"rank {rank} {mode} step {k}: peer exchange differs from the all-gather"
-                assert not torch.equal(want[0], want[1])  # the shards really differ
-                dist.barrier()  # nobody overwrites buffer k before everyone has compared it
+                wants.append(want)
+            torch.cuda.synchronize()
+            for i, snap in enumerate(snaps):
+                assert torch.equal(snap, wants[i]), f"rank {rank} {roots}: slow reader saw step {5 + i} overwritten"
+            dist.barrier()
+            del xchg
     finally:
         dist.destroy_process_group()
 
