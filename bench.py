@@ -27,15 +27,61 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 
+# BASELINE.json configs: cfg3 is the one `metric` is quoted on and the default.  cfg1/2/4 are the other
+# named configurations (same step, other robot / sizes); cfg5 is one point of the rasterizer sweep, set with
+# --n / --res / --envs (tools/sweep.py runs the whole grid).  `envs` is the TOTAL env count BASELINE.json states.
+CONFIGS = {
+    "cfg1": dict(robot="xarm6_uf_gripper", scene_cfg="xarm6_align", family="xarm", envs=1, cams=("right_cam",),
+                 hw=128, n=200_000, per_link=500, objects=("005_tomato_soup_can", "dtc_green_can"), seed=1235),
+    "cfg2": dict(robot="xarm6_uf_gripper", scene_cfg="xarm6_align", family="xarm", envs=16, cams=("right_cam",),
+                 hw=256, n=500_000, per_link=2000, objects=("005_tomato_soup_can", "dtc_green_can"), seed=1236),
+    "cfg3": dict(robot="fr3_umi", scene_cfg="fr3_pnp_box", family="fr3", envs=64, cams=("right_cam", "wrist_cam"),
+                 hw=256, n=1_000_000, per_link=4000, objects=("006_mustard_bottle", "snack_box"), seed=1237),
+    "cfg4": dict(robot="fr3_umi", scene_cfg="fr3_pour_mustard", family="fr3", envs=256, cams=("right_cam", "wrist_cam"),
+                 hw=128, n=1_000_000, per_link=4000, objects=("006_mustard_bottle", "bread_slice"), seed=1238),
+    "cfg5": dict(robot="fr3_umi", scene_cfg="fr3_pnp_box", family="fr3", envs=64, cams=("right_cam", "wrist_cam"),
+                 hw=256, n=1_000_000, per_link=4000, objects=("006_mustard_bottle", "snack_box"), seed=1237),
+}
 H = W = 256
 ENVS_PER_GPU = 64
 N_GAUSS = 1_000_000
 ROBOT = "fr3_umi"
+SCENE_CFG = "fr3_pnp_box"
+FAMILY = "fr3"
+PER_LINK = 4000
 OBJECTS = ("006_mustard_bottle", "snack_box")
 CAMERAS = ("right_cam", "wrist_cam")
 SEED = 1234 + 3
+CONFIG = "cfg3"
+SHARD = "weak"  # cfg3 (the driver's line): 64 envs on EVERY GPU; the other configs shard their stated env count
 METRIC = "rendered frames/sec (envs x cams, 256^2, 1M Gaussians)"
 WORKLOAD = "cfg3: fr3_umi, 64 envs/GPU x 2 cams (wrist + third-person), 256x256, synthetic 1M-Gaussian scene"
+
+
+def select_config(name, world, n=None, res=None, envs=None):
+    """Point the module-level workload description at one of BASELINE.json's configs."""
+    global H, W, ENVS_PER_GPU, N_GAUSS, ROBOT, SCENE_CFG, FAMILY, PER_LINK, OBJECTS, CAMERAS, SEED, CONFIG, SHARD, WORKLOAD
+    global METRIC
+    c = dict(CONFIGS[name])
+    if name == "cfg5":
+        c["n"], c["hw"], c["envs"] = n or c["n"], res or c["hw"], envs or c["envs"]
+    CONFIG = name
+    H = W = c["hw"]
+    N_GAUSS, ROBOT, SCENE_CFG, FAMILY, PER_LINK = c["n"], c["robot"], c["scene_cfg"], c["family"], c["per_link"]
+    OBJECTS, CAMERAS, SEED = c["objects"], c["cams"], c["seed"]
+    if name == "cfg3":
+        SHARD, ENVS_PER_GPU = "weak", c["envs"]
+    else:
+        from gsworld_b200.dist import shard_envs
+        SHARD = "strong"
+        ENVS_PER_GPU = max(hi - lo for lo, hi in (shard_envs(c["envs"], r, world) for r in range(world)))
+        if c["envs"] % world:
+            raise SystemExit(f"{name}: {c['envs']} envs do not split evenly over {world} GPUs")
+    if name != "cfg3":
+        METRIC = f"rendered frames/sec (envs x cams, {H}^2, {N_GAUSS // 1000}k Gaussians)"
+    per = f"{c['envs']} envs/GPU" if SHARD == "weak" else f"{c['envs']} envs in total ({ENVS_PER_GPU}/GPU)"
+    WORKLOAD = (f"{name}: {ROBOT}, {per} x {len(CAMERAS)} cam{'s' if len(CAMERAS) > 1 else ''}, {H}x{W}, "
+                f"synthetic {N_GAUSS // 1000}k-Gaussian scene")
 
 
 def log(*a):
@@ -44,7 +90,7 @@ def log(*a):
 
 def make_scene():
     from gsworld_b200 import fixtures as fx
-    return fx.make_scene(fx.SceneSpec(robot=ROBOT, n_total=N_GAUSS, per_link=4000, objects=OBJECTS, per_object=7000,
+    return fx.make_scene(fx.SceneSpec(robot=ROBOT, n_total=N_GAUSS, per_link=PER_LINK, objects=OBJECTS, per_object=7000,
                                       seed=SEED))
 
 
@@ -184,12 +230,64 @@ def peaks():
 
 
 def traffic_of(stage):
-    """DRAM read+write bytes per step for a stage from the committed ncu --set full capture, or None."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            return json.load(f)["dram_bytes_per_step"].get(stage)
-    except Exception:
+    """DRAM read+write bytes per step for a stage from the committed ncu --set full capture (newest round), or None.
+    Only meaningful for the configuration the capture was taken on (cfg3, strict cameras)."""
+    if CONFIG != "cfg3":
         return None
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                return json.load(f)["dram_bytes_per_step"].get(stage)
+        except Exception:
+            continue
+    return None
+
+
+def pair_roofline(pairs, kernel_ms, sm_mhz, ref_pairs, traffic):
+    """the blend against FP32 FMA + MUFU throughput.  `pairs` = (splat, pixel) pair evaluations the
+    kernel itself counted for one step (gsw_profile_counters), ~22 fp32 flop + 1 ex2 each."""
+    if not pairs or kernel_ms <= 0:
+        return None
+    clk = (sm_mhz or 1965.0) * 1e6
+    peak_fma = 148 * 128 * 2 * clk / 1e12          # TFLOP/s fp32 (non-tensor)
+    peak_mufu = 148 * 16 * clk / 1e12              # T ex2/s
+    per_s = pairs / (kernel_ms * 1e-3)
+    ach_fma, ach_mufu = per_s * 22 / 1e12, per_s / 1e12
+    frac_fma, frac_mufu = ach_fma / peak_fma, ach_mufu / peak_mufu
+    out = {"bound": "sm_fp32_mufu", "kernel": "blend", "achieved": ach_fma, "peak": peak_fma, "unit": "TFLOP/s",
+           "frac": max(frac_fma, frac_mufu), "frac_fma": frac_fma, "frac_mufu": frac_mufu,
+           "pairs_per_step": int(pairs), "achieved_pairs_per_s": per_s, "peak_fma": peak_fma,
+           "peak_mufu": peak_mufu, "achieved_mufu": ach_mufu, "flop_per_pair": 22, "kernel_ms": kernel_ms,
+           "peak_source": "148 SMs x 128 fp32 lanes x 2 x SM clock; MUFU 16 / clk / SM (SURVEY.md section 8d)",
+           "traffic": traffic,
+           "note": "pairs_per_step is the kernel's own count of per-pixel alpha evaluations (after exact tile culling, "
+                   "the per-warp footprint cull and early termination)"}
+    if ref_pairs:
+        out["reference_pairs_per_step"] = int(ref_pairs["pairs_per_step"])
+        out["reference_pairs_source"] = ref_pairs["source"]
+        out["work_avoided_by_culling"] = 1.0 - pairs / ref_pairs["pairs_per_step"]
+        out["reference_pairs_per_s"] = ref_pairs["pairs_per_step"] / (kernel_ms * 1e-3)
+    return out
+
+
+def reference_pairs_sample(scene, frames_per_cam):
+    """Pair evaluations of the REFERENCE algorithm for one step: the oracle's sum over pixels of n_contrib (how far
+    each pixel walks its tile's list before it terminates), measured on env 0's frame of every camera and scaled to
+    the step's frames (the oracle needs seconds per frame at this size)."""
+    from gsworld_b200 import fixtures as fx
+    from gsworld_b200 import rig_tables as rt
+    from oracle import torch_transform as ot
+    env = fx.FakeEnv(ROBOT, num_envs=1, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED)
+    scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
+    ref = ot.RefPath(env, scene, rt.SIM2GS_ROBOT[FAMILY], rt.LINK_LABELS[FAMILY], list(scan), rt.SIM2GS_OBJECT,
+                     rt.OBJECT_LABELS, rt.OBJECT_OFFSET, rt.OBJECT_SCALE,
+                     xarm_offset=rt.OBJECT_OFFSET["xarm_arm"] if "xarm" in ROBOT else None)
+    env.step(None)
+    ref.transform_gs_perlink()
+    _, aux = ref.render_gsworld(strict=True, return_aux=True)
+    per_cam = {c: int(aux[c][0]["pairs"]) for c in CAMERAS}
+    return {"pairs_per_step": sum(per_cam.values()) * frames_per_cam, "per_frame": per_cam,
+            "source": f"oracle (sum over pixels of n_contrib) on env 0's {len(CAMERAS)} frame(s) x {frames_per_cam}"}
 
 
 def issue_roofline(stage_ms, sm_mhz):
@@ -235,8 +333,9 @@ def cpu_reference_sample(scene, n_envs, steps, warmup, strict=True):
     torch.set_num_threads(os.cpu_count() or 1)
     env = fx.FakeEnv(ROBOT, num_envs=n_envs, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED)
     scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
-    ref = ot.RefPath(env, scene, rt.SIM2GS_ROBOT["fr3"], rt.LINK_LABELS["fr3"], list(scan), rt.SIM2GS_OBJECT,
-                     rt.OBJECT_LABELS, rt.OBJECT_OFFSET, rt.OBJECT_SCALE)
+    ref = ot.RefPath(env, scene, rt.SIM2GS_ROBOT[FAMILY], rt.LINK_LABELS[FAMILY], list(scan), rt.SIM2GS_OBJECT,
+                     rt.OBJECT_LABELS, rt.OBJECT_OFFSET, rt.OBJECT_SCALE,
+                     xarm_offset=rt.OBJECT_OFFSET["xarm_arm"] if "xarm" in ROBOT else None)
     times = []
     for i in range(warmup + steps):
         env.step(None)
@@ -261,8 +360,9 @@ def gpu_reference_restated(scene_cpu, dev, n_envs=4, steps=3):
     env = fx.FakeEnv(ROBOT, num_envs=n_envs, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED, device=dev)
     scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
     scene = scene_cpu.to(dev)
-    ref = ot.RefPath(env, scene, rt.SIM2GS_ROBOT["fr3"], rt.LINK_LABELS["fr3"], list(scan), rt.SIM2GS_OBJECT,
+    ref = ot.RefPath(env, scene, rt.SIM2GS_ROBOT[FAMILY], rt.LINK_LABELS[FAMILY], list(scan), rt.SIM2GS_OBJECT,
                      rt.OBJECT_LABELS, rt.OBJECT_OFFSET, rt.OBJECT_SCALE, device=dev,
+                     xarm_offset=rt.OBJECT_OFFSET["xarm_arm"] if "xarm" in ROBOT else None,
                      rasterizer=ref_gpu.render_like_reference)
     frames = n_envs * len(CAMERAS)
 
@@ -312,12 +412,14 @@ def run_reference(args):
     scene = make_scene()
     n_envs = 1
     fps, ms, cores = cpu_reference_sample(scene, n_envs, args.steps, args.warmup)
-    sample = f"{n_envs} env x {len(CAMERAS)} cams per step (of {ENVS_PER_GPU}), same scene and cameras"
+    sample = f"sample: {n_envs} env x {len(CAMERAS)} cams per step (of {ENVS_PER_GPU} envs), same scene and cameras"
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "cameras": "strict (env-0 camera, reference behaviour)"},
+        "config": {"workload": f"{WORKLOAD} -- {sample}", "cameras": "strict (env-0 camera, reference behaviour)",
+                   "what": "CPU port of the reference path (oracle/): torch transform with deepcopy + isin write-back "
+                           "per frame, CPU rasterizer; per-frame cost does not depend on the env count"},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -342,246 +444,310 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B = ENVS_PER_GPU
-    F = B * len(CAMERAS)
     scene_cpu = make_scene()
     scene = scene_cpu.to(dev)
-    base = fx.FakeEnv(ROBOT, num_envs=B, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED + 17 * rank)
-    scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
-    n_states = 8
 
-    def build(resident, strict):
-        # strict mode = the reference's behaviour: EVERY env of the batch is rendered through env 0's camera
-        # (gs_world_wrapper.py:280-281).  With the batch sharded over ranks that is the GLOBAL env 0, so every
-        # rank takes its camera parameters from a replica of rank 0's env roll-out.
-        cam_base = None
-        if strict and world > 1 and rank != 0:
-            cam_base = fx.FakeEnv(ROBOT, num_envs=B, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED)
-            for _ in range(build.calls * n_states):
-                cam_base.step(None)
-        env = ReplayEnv(base, n_states, dev, resident, cam_base=cam_base)
-        build.calls += 1
-        wrap = GSWorldWrapper(env, PipelineParams(), "fr3_pnp_box", device=dev, merged_model=scene,
-                              scan_link_mats=list(scan), strict_reference=strict)
-        for _ in range(n_states):  # size the grow-only workspace over every replay state (not timed)
+    def run_legs(B, lean):
+        """All timed legs for B envs on this GPU.  lean: the resident-input strict leg only (strong-scaling point)."""
+        F = B * len(CAMERAS)
+        base = fx.FakeEnv(ROBOT, num_envs=B, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED + 17 * rank)
+        scan = fx.forward_kinematics(ROBOT, rt.ROBOT_SCAN_QPOS[ROBOT][None])[0]
+        n_states = 8
+
+        def build(resident, strict):
+            # strict mode = the reference's behaviour: EVERY env of the batch is rendered through env 0's camera
+            # (gs_world_wrapper.py:280-281).  With the batch sharded over ranks that is the GLOBAL env 0, so every
+            # rank takes its camera parameters from a replica of rank 0's env roll-out.
+            cam_base = None
+            if strict and world > 1 and rank != 0:
+                cam_base = fx.FakeEnv(ROBOT, num_envs=B, cameras=CAMERAS, hw=(H, W), objects=OBJECTS, seed=SEED)
+                for _ in range(build.calls * n_states):
+                    cam_base.step(None)
+            env = ReplayEnv(base, n_states, dev, resident, cam_base=cam_base)
+            build.calls += 1
+            wrap = GSWorldWrapper(env, PipelineParams(), SCENE_CFG, device=dev, merged_model=scene,
+                                  scan_link_mats=list(scan), strict_reference=strict)
+            for _ in range(n_states):  # size the grow-only workspace over every replay state (not timed)
+                env.advance()
+                wrap.transform_gs_perlink(None)
+                wrap._render_gsworld()
+            return env, wrap
+
+        # Multi-GPU: every step ends with ONE all-gather of the uint8 observations.  It is issued asynchronously
+        # into one of two buffers, so the exchange of step k overlaps the rendering of step k+1; a buffer is
+        # only reused after the collective that read/wrote it has completed.
+        nbuf = 2
+        # "peer" (default where torch symmetric memory works): libgsw's peer stream pushes every finished frame group
+        # into the POLICY rank's buffer (rank 0, SURVEY.md section 8e) with the copy engines, overlapped with the
+        # blend; arrival is a symmetric-memory signal per producer, buffer reuse a credit signal back (dist.py).
+        # "peer_all": the same into every rank's buffer + one device-side barrier per step.  "all": NCCL all-gather;
+        # "root": NCCL gather to rank 0; "none": no exchange
+        GATHER = os.environ.get("GSW_BENCH_GATHER", "peer")
+        build.calls = 0
+        xchg = None
+        if world > 1 and GATHER in ("peer", "peer_all"):
+            from gsworld_b200.dist import PeerObservationExchange
+            ok = 0
+            try:
+                if PeerObservationExchange.available():
+                    xchg = PeerObservationExchange((len(CAMERAS), B, H, W, 3), dev, nbuf=nbuf,
+                                                   roots=[0] if GATHER == "peer" else None)
+                    ok = 1
+            except Exception as e:  # noqa: BLE001
+                log(f"[rank {rank}] symmetric memory unavailable ({e!r}); falling back to the NCCL all-gather")
+            flag = torch.tensor([ok], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 0:
+                xchg, GATHER = None, "all"
+        gathered = [torch.empty((world, len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(nbuf)] \
+            if world > 1 and xchg is None and GATHER in ("all", "root") else None
+        pending = [None] * nbuf
+        counter = [0]
+        consumer = torch.cuda.Stream(device=dev) if xchg is not None and xchg.is_root else None
+        verified = [None]
+
+        def consume(k):
+            """The policy side: wait for step k's batch on its own stream, then hand the buffer back."""
+            if consumer is not None and k >= 0:
+                with torch.cuda.stream(consumer):
+                    xchg.wait_ready(k)
+                    xchg.release(k)
+
+        def step(env, wrap):
             env.advance()
             wrap.transform_gs_perlink(None)
-            wrap._render_gsworld()
-        return env, wrap
-
-    # Multi-GPU: every step ends with ONE all-gather of the uint8 observations.  It is issued asynchronously
-    # into one of two buffers, so the exchange of step k overlaps the rendering of step k+1; a buffer is
-    # only reused after the collective that read/wrote it has completed.
-    nbuf = 2
-    # "peer" (default where torch symmetric memory works): libgsw's copy stream pushes every finished frame group
-    # into every rank's buffer with the copy engines, overlapped with the blend, + one device-side barrier per
-    # step; "all": NCCL all-gather; "root": NCCL gather to rank 0; "none": no exchange
-    GATHER = os.environ.get("GSW_BENCH_GATHER", "peer")
-    build.calls = 0
-    xchg = None
-    if world > 1 and GATHER == "peer":
-        from gsworld_b200.dist import PeerObservationExchange
-        ok = 0
-        try:
-            if PeerObservationExchange.available():
-                xchg = PeerObservationExchange((len(CAMERAS), B, H, W, 3), dev, nbuf=nbuf)
-                ok = 1
-        except Exception as e:  # noqa: BLE001
-            log(f"[rank {rank}] symmetric memory unavailable ({e!r}); falling back to the NCCL all-gather")
-        flag = torch.tensor([ok], device=dev)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        if int(flag.item()) == 0:
-            xchg, GATHER = None, "all"
-    # (the synchronous e2e leg keeps the asynchronous NCCL all-gather also in "peer" mode: with the host waiting
-    # for every step, the cross-rank barrier of the peer exchange would sit on the critical path)
-    gathered = [torch.empty((world, len(CAMERAS), B, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(nbuf)] \
-        if world > 1 and GATHER in ("all", "root", "peer") else None
-    pending = [None] * nbuf
-    counter = [0]
-
-    def step(env, wrap):
-        env.advance()
-        wrap.transform_gs_perlink(None)
-        if xchg is not None and not wrap.sync_each_step:
-            k = counter[0]
-            counter[0] += 1
-            xchg.begin(k)
-            wrap.obs_out = xchg.local_out(k)  # composite straight into this rank's slot of its own buffer
-            wrap.obs_peers = xchg.destinations(k)
-            wrap.defer_delivery_join = True
+            if xchg is not None:
+                k = counter[0]
+                counter[0] += 1
+                xchg.begin(k, wrap._engine)
+                wrap.obs_out = xchg.local_out(k)  # composite straight into this rank's slot of its own buffer
+                wrap.obs_peers = xchg.destinations(k)
+                # asynchronous legs: the render stream does not wait for the pushes; the host-synchronous e2e leg
+                # joins them (the host reads its own frames right after)
+                wrap.defer_delivery_join = not wrap.sync_each_step
+                out = wrap._render_gsworld()
+                consume(k - 1)  # one step behind, while step k is still being composited
+                xchg.publish(k, wrap._engine)  # after xchg.wait_ready(k), xchg.gathered(k) holds every rank's frames
+                return out
+            wrap.obs_out = wrap.obs_peers = None
+            wrap.defer_delivery_join = False
             out = wrap._render_gsworld()
-            xchg.publish(k, wrap._engine)  # after xchg.wait_ready(k), xchg.gathered(k) holds every rank's frames
-            return out
-        wrap.obs_out = wrap.obs_peers = None
-        wrap.defer_delivery_join = False
-        out = wrap._render_gsworld()
-        if world > 1 and GATHER in ("all", "root", "peer"):
-            k = counter[0] % nbuf
-            counter[0] += 1
-            if pending[k] is not None:
-                pending[k].wait()
-            mine = gathered[k][rank]
-            for i, c in enumerate(CAMERAS):
-                mine[i].copy_(out[c])
-            if GATHER == "root":  # only the policy rank (0) needs the whole batch
-                pending[k] = dist.gather(mine, list(gathered[k].unbind(0)) if rank == 0 else None, dst=0, async_op=True)
-            else:
-                pending[k] = dist.all_gather_into_tensor(gathered[k].view(-1), mine.view(-1), async_op=True)
-        return out
-
-    def drain():
-        if xchg is not None:
-            xchg.stream.synchronize()
-        for k in range(nbuf):
-            if pending[k] is not None:
-                pending[k].wait()
-                pending[k] = None
-
-    def barrier():
-        if world > 1:
-            drain()
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    timed_launches = [0]
-
-    def timed(env, wrap, steps, warmup, d2h=None):
-        for _attempt in range(4):
-            ms = timed_once(env, wrap, steps, warmup, d2h)
-            if ms is not None:
-                return ms
-            warmup = max(warmup, n_states)  # the workspace was grown: prime every replay state again, re-measure
-        raise RuntimeError("tile-entry workspace kept overflowing inside the timed region")
-
-    def timed_once(env, wrap, steps, warmup, d2h=None):
-        wrap.sync_each_step = True  # warm-up validates (and if needed grows) the tile-entry workspace
-        for _ in range(warmup):
-            out = step(env, wrap)
-            if d2h is not None and not isinstance(d2h, str):
+            if world > 1 and GATHER in ("all", "root"):
+                k = counter[0] % nbuf
+                counter[0] += 1
+                if pending[k] is not None:
+                    pending[k].wait()
+                mine = gathered[k][rank]
                 for i, c in enumerate(CAMERAS):
-                    d2h[i].copy_(out[c], non_blocking=True)
-        wrap.sync_each_step = d2h is not None  # resident-input runs are fully asynchronous
-        if not wrap.sync_each_step and steps > 0:
-            for _ in range(2):  # untimed: the asynchronous path (peer exchange, deferred delivery) in its own mode
-                step(env, wrap)
-        barrier()
-        prof = steps > 0 and os.environ.get("GSW_PROFILE_RANGE") == "1"  # ncu --profile-from-start off
-        if prof:
-            torch.cuda.profiler.start()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        launches_before = wrap._engine.kernel_launches()
-        e0.record()
-        h0 = time.perf_counter()
-        for _ in range(steps):
-            out = step(env, wrap)
-            if d2h is not None:
-                if not isinstance(d2h, str):
+                    mine[i].copy_(out[c])
+                if GATHER == "root":  # only the policy rank (0) needs the whole batch
+                    pending[k] = dist.gather(mine, list(gathered[k].unbind(0)) if rank == 0 else None, dst=0, async_op=True)
+                else:
+                    pending[k] = dist.all_gather_into_tensor(gathered[k].view(-1), mine.view(-1), async_op=True)
+            return out
+
+        def verify_exchange(env, wrap):
+            """Once, before anything is timed: the batch the peer exchange delivers to the policy rank is byte-identical
+            to an NCCL all-gather of the same frames (the 2-GPU pytest cannot run on a 1-GPU test box)."""
+            if xchg is None:
+                return
+            wrap.sync_each_step = False
+            ok = True
+            for _ in range(3):  # both buffers, one of them twice
+                out = step(env, wrap)
+                k = counter[0] - 1
+                mine = torch.stack([out[c] for c in CAMERAS]).contiguous()
+                want = torch.empty((world,) + tuple(mine.shape), dtype=torch.uint8, device=dev)
+                dist.all_gather_into_tensor(want.view(-1), mine.view(-1))
+                if xchg.is_root:
+                    xchg.wait_ready(k)
+                    torch.cuda.synchronize(dev)
+                    ok = ok and bool(torch.equal(xchg.gathered(k), want))
+                    xchg.release(k)
+                torch.cuda.synchronize(dev)
+            flag = torch.tensor([1 if ok else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            verified[0] = bool(int(flag.item()))
+            if not verified[0]:
+                raise RuntimeError("peer observation exchange differs from the NCCL all-gather")
+
+        def drain():
+            if xchg is not None:
+                consume(counter[0] - 1)
+                xchg.stream.synchronize()
+                if consumer is not None:
+                    consumer.synchronize()
+            for k in range(nbuf):
+                if pending[k] is not None:
+                    pending[k].wait()
+                    pending[k] = None
+
+        def barrier():
+            if world > 1:
+                drain()
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+
+        timed_launches = [0]
+
+        def timed(env, wrap, steps, warmup, d2h=None):
+            for _attempt in range(4):
+                ms = timed_once(env, wrap, steps, warmup, d2h)
+                if ms is not None:
+                    return ms
+                warmup = max(warmup, n_states)  # the workspace was grown: prime every replay state again, re-measure
+            raise RuntimeError("tile-entry workspace kept overflowing inside the timed region")
+
+        def timed_once(env, wrap, steps, warmup, d2h=None):
+            wrap.sync_each_step = True  # warm-up validates (and if needed grows) the tile-entry workspace
+            for _ in range(warmup):
+                out = step(env, wrap)
+                if d2h is not None and not isinstance(d2h, str):
                     for i, c in enumerate(CAMERAS):
                         d2h[i].copy_(out[c], non_blocking=True)
-                torch.cuda.current_stream().synchronize()  # the caller reads the observation every step
-        host_ms = (time.perf_counter() - h0) * 1e3
-        timed_launches[0] = wrap._engine.kernel_launches() - launches_before  # kernels of the timed region only
-        if world > 1:
-            drain()  # the last exchanges belong to the timed steps
-        e1.record()
-        barrier()
-        if prof:
-            torch.cuda.profiler.stop()
-        ok = wrap._engine.finish(raise_on_overflow=False)
-        if world > 1:  # every rank must take the same decision
-            flag = torch.tensor([0 if ok else 1], device=dev)
-            dist.all_reduce(flag, op=dist.ReduceOp.MAX)
-            ok = int(flag.item()) == 0
-        if not ok:
-            return None  # a launch in the timed region overflowed the tile-entry workspace: number invalid
-        ms = e0.elapsed_time(e1)
-        if os.environ.get("GSW_BENCH_DEBUG") and steps > 0:
-            log(f"[rank {rank}] {ms / steps:.3f} ms/step on this rank, host loop {host_ms / steps:.3f} ms/step, "
-                f"D={wrap._engine.last_stats['D']}")
-        if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+            wrap.sync_each_step = d2h is not None  # resident-input runs are fully asynchronous
+            if not wrap.sync_each_step and steps > 0:
+                for _ in range(2):  # untimed: the asynchronous path (peer exchange, deferred delivery) in its own mode
+                    step(env, wrap)
+            barrier()
+            prof = steps > 0 and os.environ.get("GSW_PROFILE_RANGE") == "1"  # ncu --profile-from-start off
+            if prof:
+                torch.cuda.profiler.start()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            launches_before = wrap._engine.kernel_launches()
+            e0.record()
+            h0 = time.perf_counter()
+            for _ in range(steps):
+                out = step(env, wrap)
+                if d2h is not None:
+                    if not isinstance(d2h, str):
+                        for i, c in enumerate(CAMERAS):
+                            d2h[i].copy_(out[c], non_blocking=True)
+                    torch.cuda.current_stream().synchronize()  # the caller reads the observation every step
+            host_ms = (time.perf_counter() - h0) * 1e3
+            timed_launches[0] = wrap._engine.kernel_launches() - launches_before  # kernels of the timed region only
+            if world > 1:
+                drain()  # the last exchanges belong to the timed steps
+            e1.record()
+            barrier()
+            if prof:
+                torch.cuda.profiler.stop()
+            ok = wrap._engine.finish(raise_on_overflow=False)
+            if world > 1:  # every rank must take the same decision
+                flag = torch.tensor([0 if ok else 1], device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+                ok = int(flag.item()) == 0
+            if not ok:
+                return None  # a launch in the timed region overflowed the tile-entry workspace: number invalid
+            ms = e0.elapsed_time(e1)
+            if os.environ.get("GSW_BENCH_DEBUG") and steps > 0:
+                log(f"[rank {rank}] {ms / steps:.3f} ms/step on this rank, host loop {host_ms / steps:.3f} ms/step, "
+                    f"D={wrap._engine.last_stats['D']}")
+            if world > 1:
+                t = torch.tensor([ms], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            return ms
 
-    results = {}
-    sampler = None
-    modes = (("strict", not args.quick_per_env),) if args.quick else (("strict", True), ("per_env", False))
-    for mode, strict in modes:
-        env, wrap = build(True, strict)
-        eng = wrap._engine
-        if os.environ.get("GSW_NB"):
-            eng.set_depth_buckets(int(os.environ["GSW_NB"]))
-        if os.environ.get("GSW_TILE_CULL"):
-            eng.set_tile_culling(os.environ["GSW_TILE_CULL"] == "1")
-        if mode == "strict":
-            sampler = ClockSampler(local) if rank == 0 else None
-            timed(env, wrap, 0, args.warmup)
-            if sampler is not None:
-                sampler.start()
-            ms = timed(env, wrap, args.steps, 0)
-            clocks = sampler.stop() if sampler is not None else None
-            launches = timed_launches[0]
-        else:
-            ms = timed(env, wrap, args.steps, args.warmup)
-        # stage breakdown + traffic counts (outside the timed region)
-        eng.profile(True)
-        acc = {}
-        for _ in range(3):
-            step(env, wrap)
-            for k, v in eng.stage_ms().items():
-                acc[k] = acc.get(k, 0.0) + v / 3
-        eng.profile(False)
-        if os.environ.get("GSW_BENCH_DEBUG") and rank == 0:  # bin-size histogram of the last step (tuning aid)
-            import numpy as np
-            off = eng.debug_bin_offsets().astype(np.int64)
-            n = np.diff(off)
+        results = {}
+        sampler = None
+        modes = (("strict", not args.quick_per_env),) if args.quick else (("strict", True), ("per_env", False))
+        if lean:
+            modes = (("strict", True),)
+        for mode, strict in modes:
+            env, wrap = build(True, strict)
+            eng = wrap._engine
+            if verified[0] is None and xchg is not None:
+                verify_exchange(env, wrap)
+            if os.environ.get("GSW_NB"):
+                eng.set_depth_buckets(int(os.environ["GSW_NB"]))
+            if os.environ.get("GSW_TILE_CULL"):
+                eng.set_tile_culling(os.environ["GSW_TILE_CULL"] == "1")
+            if mode == "strict":
+                sampler = ClockSampler(local) if rank == 0 else None
+                timed(env, wrap, 0, args.warmup)
+                if sampler is not None:
+                    sampler.start()
+                ms = timed(env, wrap, args.steps, 0)
+                clocks = sampler.stop() if sampler is not None else None
+                launches = timed_launches[0]
+            else:
+                ms = timed(env, wrap, args.steps, args.warmup)
+            # stage breakdown + traffic counts (outside the timed region)
+            eng.profile(True)
+            acc = {}
+            for _ in range(3):
+                step(env, wrap)
+                for k, v in eng.stage_ms().items():
+                    acc[k] = acc.get(k, 0.0) + v / 3
+            eng.profile(False)
+            cnts = eng.counters()  # of the last (profiled) step
+            pairs = cnts["blend_pairs"]
+            if os.environ.get("GSW_BENCH_DEBUG") and rank == 0:  # bin-size histogram of the last step (tuning aid)
+                import numpy as np
+                off = eng.debug_bin_offsets().astype(np.int64)
+                n = np.diff(off)
+                Vn = int(wrap._views(list(CAMERAS))[0].shape[0])
+                T = (len(n)) // (Vn + F)
+                for name, part in (("static", n[:Vn * T]), ("dynamic", n[Vn * T:])):
+                    edges = [0, 1, 65, 129, 257, 513, 1025, 2049, 4097, 16385, 1 << 30]
+                    h, _ = np.histogram(part, bins=edges)
+                    w, _ = np.histogram(part, bins=edges, weights=part)
+                    log(f"[bins {mode} {name}] total {int(part.sum())} in {len(part)} bins; per size class "
+                        f"(upper edge: bins/keys): " + ", ".join(f"<{e}: {int(a)}/{int(b)}" for e, a, b in
+                                                                zip(edges[1:], h, w)))
+            st = dict(eng.last_stats)
             Vn = int(wrap._views(list(CAMERAS))[0].shape[0])
-            T = (len(n)) // (Vn + F)
-            for name, part in (("static", n[:Vn * T]), ("dynamic", n[Vn * T:])):
-                edges = [0, 1, 65, 129, 257, 513, 1025, 2049, 4097, 16385, 1 << 30]
-                h, _ = np.histogram(part, bins=edges)
-                w, _ = np.histogram(part, bins=edges, weights=part)
-                log(f"[bins {mode} {name}] total {int(part.sum())} in {len(part)} bins; per size class "
-                    f"(upper edge: bins/keys): " + ", ".join(f"<{e}: {int(a)}/{int(b)}" for e, a, b in
-                                                            zip(edges[1:], h, w)))
-        st = dict(eng.last_stats)
-        Vn = int(wrap._views(list(CAMERAS))[0].shape[0])
-        off = eng.debug_bin_offsets()
-        fv = wrap._views(list(CAMERAS))[4].cpu().numpy()
-        Tn = (len(off) - 1) // (Vn + F)
-        shared = [v for v in range(Vn) if int((fv == v).sum()) >= 2]
-        d_shared = int(sum(int(off[(v + 1) * Tn]) - int(off[v * Tn]) for v in shared))
-        results[mode] = dict(ms=ms, fps=world * F * args.steps / (ms * 1e-3), stages=acc, stats=st, V=Vn,
-                             D_shared_static=d_shared)
-        if mode == "strict" and not args.quick and not os.environ.get("GSW_TILE_CULL"):
-            # the same step with the reference's full tile lists (exact tile culling off); same pixels
-            eng.set_tile_culling(False)
-            ms_full = timed(env, wrap, args.steps, args.warmup)
-            results[mode]["reference_tile_lists"] = {
-                "value": world * F * args.steps / (ms_full * 1e-3), "ms_per_step": ms_full / args.steps,
-                "D": int(eng.last_stats["D"])}
-            eng.set_tile_culling(True)
-        if mode == "strict":
-            results[mode].update(clocks=clocks, launches=launches)
-            if args.quick:
-                results["e2e"] = dict(ms=float("nan"), fps=float("nan"), h2d=0, d2h=0)
-                results["per_env"] = results["strict"]
-                continue
-            # e2e: host (pinned) inputs every step, uint8 observations read back to pinned host memory
-            env_h, wrap_h = build(False, True)
-            pinned = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8).pin_memory()
-            # the uint8 observations land in pinned host memory: the library sends each eighth of the frames on its
-            # copy stream as soon as the blend kernel has signalled that group complete (obs_host)
-            wrap_h.obs_host = pinned
-            ms_e = timed(env_h, wrap_h, args.steps, args.warmup, d2h="library")
-            wrap_h.obs_host = None
-            results["e2e"] = dict(ms=ms_e, fps=world * F * args.steps / (ms_e * 1e-3), h2d=env_h.h2d_bytes,
-                                  d2h=pinned.numel())
-            del env_h, wrap_h
-        del env, wrap
-        torch.cuda.empty_cache()
+            off = eng.debug_bin_offsets()
+            fv = wrap._views(list(CAMERAS))[4].cpu().numpy()
+            Tn = (len(off) - 1) // (Vn + F)
+            shared = [v for v in range(Vn) if int((fv == v).sum()) >= 2]
+            d_shared = int(sum(int(off[(v + 1) * Tn]) - int(off[v * Tn]) for v in shared))
+            results[mode] = dict(ms=ms, fps=world * F * args.steps / (ms * 1e-3), stages=acc, stats=st, V=Vn,
+                                 D_shared_static=d_shared, pairs=pairs, chunks_live=cnts["static_chunks_live"],
+                                 chunks_total=Vn * ((int((scene_cpu._semantics.reshape(-1) < 0).sum()) + 2047) // 2048))
+            if mode == "strict" and not args.quick and not lean and not os.environ.get("GSW_TILE_CULL"):
+                # the same step with the reference's full tile lists (exact tile culling off); same pixels
+                eng.set_tile_culling(False)
+                ms_full = timed(env, wrap, args.steps, args.warmup)
+                results[mode]["reference_tile_lists"] = {
+                    "value": world * F * args.steps / (ms_full * 1e-3), "ms_per_step": ms_full / args.steps,
+                    "D": int(eng.last_stats["D"])}
+                eng.set_tile_culling(True)
+            if mode == "strict":
+                results[mode].update(clocks=clocks, launches=launches)
+                if lean:
+                    continue
+                if args.quick:
+                    results["e2e"] = dict(ms=float("nan"), fps=float("nan"), h2d=0, d2h=0)
+                    results["per_env"] = results["strict"]
+                    continue
+                # e2e: host (pinned) inputs every step, uint8 observations read back to pinned host memory
+                env_h, wrap_h = build(False, True)
+                pinned = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8).pin_memory()
+                # the uint8 observations land in pinned host memory: the library sends each eighth of the frames on its
+                # copy stream as soon as the blend kernel has signalled that group complete (obs_host)
+                wrap_h.obs_host = pinned
+                ms_e = timed(env_h, wrap_h, args.steps, args.warmup, d2h="library")
+                wrap_h.obs_host = None
+                results["e2e"] = dict(ms=ms_e, fps=world * F * args.steps / (ms_e * 1e-3), h2d=env_h.h2d_bytes,
+                                      d2h=pinned.numel())
+                del env_h, wrap_h
+            del env, wrap
+            torch.cuda.empty_cache()
 
+        return results, xchg is not None, verified[0]
+
+    results, used_peer, exchange_verified = run_legs(ENVS_PER_GPU, False)
+    strong = None
+    if world > 1 and CONFIG == "cfg3" and not args.quick and ENVS_PER_GPU % world == 0:
+        # BASELINE.json states cfg3 as 64 envs over 1/2/4/8 GPUs: the same step with the 64 envs SHARDED (strong scaling)
+        rs, _, _ = run_legs(ENVS_PER_GPU // world, True)
+        strong = {"envs_total": ENVS_PER_GPU, "envs_per_gpu": ENVS_PER_GPU // world, "value": rs["strict"]["fps"],
+                  "ms_per_step": rs["strict"]["ms"] / args.steps, "scaling": "strong",
+                  "stages_ms": {k: round(v, 4) for k, v in rs["strict"]["stages"].items()}}
+    B = ENVS_PER_GPU
+    F = B * len(CAMERAS)
     if rank == 0:
         r = results["strict"]
         peak, peak_src = peaks()
@@ -605,10 +771,32 @@ def run_ours(args):
         }
         ach = alg.get(dom, 0) / (stages[dom] * 1e-3) / 1e9 if stages[dom] > 0 else 0.0
         cpu = None
+        ref_pairs = None
         if world == 1 and not args.no_cpu_baseline and not args.quick:
             fps_c, ms_c, cores = cpu_reference_sample(scene_cpu, 1, 3, 1)
             cpu = {"value": fps_c, "unit": "frames/s", "cores": cores, "kind": "port",
-                   "sample": f"1 env x 2 cams per step (of {B}), 3 steps, same 1M-Gaussian scene, oracle/ port"}
+                   "sample": f"sample: 1 env x {len(CAMERAS)} cams per step (of {B} envs), 3 steps, same "
+                             f"{N_GAUSS // 1000}k-Gaussian scene, oracle/ port"}
+            try:
+                ref_pairs = reference_pairs_sample(scene_cpu, B)
+            except Exception as e:  # noqa: BLE001
+                log(f"reference pair count unavailable: {e!r}")
+        sm_mhz = (r["clocks"] or {}).get("sm_mhz")
+        hbm_dom = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                   "traffic": traffic_of(dom), "peak_source": peak_src, "kernel_ms": stages[dom],
+                   "algorithmic_bytes": alg.get(dom, 0)}
+        if hbm_dom["traffic"]:
+            hbm_dom["traffic_ratio"] = hbm_dom["traffic"] / max(1, alg.get(dom, 0))
+        if dom == "blend":
+            # the dominant kernel is bound by fp32 + MUFU issue, not by HBM: report it against that roofline (SURVEY.md
+            # section 8d) and keep the byte view beside it
+            roof = pair_roofline(r["pairs"], stages["blend"], sm_mhz, ref_pairs, traffic_of("blend")) or hbm_dom
+            if roof is not hbm_dom:
+                roof["hbm_view"] = {k: hbm_dom[k] for k in ("achieved", "peak", "unit", "frac", "algorithmic_bytes")}
+                if roof["traffic"]:
+                    roof["traffic_ratio"] = roof["traffic"] / max(1, alg["blend"])
+        else:
+            roof = hbm_dom
         gpu_ref = None
         if world == 1 and not args.quick and not args.no_gpu_reference:
             try:
@@ -619,25 +807,22 @@ def run_ours(args):
             "metric": METRIC, "value": r["fps"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "envs_per_gpu": B, "frames_per_step_per_gpu": F, "views": V,
+            "config": {"workload": WORKLOAD, "name": CONFIG, "envs_per_gpu": B, "frames_per_step_per_gpu": F, "views": V,
                        "cameras": "strict (env-0 camera for every env = reference behaviour, gs_world_wrapper.py:280-281)",
                        "tile_lists": "exact tile culling on (wrapper default): entries that stay below alpha 1/255 on a "
                                      "whole tile are never binned; pixels and radii bit-identical to the "
                                      "reference's full lists (reference_tile_lists = the same step with it off)",
                        "l2": "inputs larger than L2 (236 MB scene + GB-scale workspace per step), no explicit flush",
-                       "parallelism": f"env-sharded x{world}, scene replicated, uint8 observations exchanged by "
+                       "parity_mode": "tile_culling_on (reference_tile_lists = the contract-conformant lists, same pixels)",
+                       "parallelism": f"env-sharded x{world}, scene replicated, uint8 observations delivered to the "
+                                      "policy rank by "
                                       + ("copy-engine pushes into peer memory (NVLink), overlapped with the blend"
-                                         if xchg is not None else f"NCCL ({GATHER})")},
+                                         if used_peer else "an NCCL collective")},
             "e2e": {"value": results["e2e"]["fps"], "unit": "frames/s", "h2d_bytes_per_step": results["e2e"]["h2d"],
                     "d2h_bytes_per_step": results["e2e"]["d2h"], "ms_per_step": results["e2e"]["ms"] / args.steps},
             "gpu_launches": r["launches"],
             "clocks": r["clocks"],
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": traffic_of(dom), "peak_source": peak_src,
-                         "kernel_ms": stages[dom],
-                         "note": ("blend is bound by the SM issue rate (ncu: ~84 % issue-slot utilisation, <1 % DRAM), "
-                                  "not by HBM; its HBM fraction is low by construction (profiles/README.md)")
-                         if dom == "blend" else None},
+            "roofline": roof,
             "roofline_hbm_kernel": hbm_roofline(stages, alg, peak),
             "roofline_issue": issue_roofline(stages.get("blend", 0.0), (r["clocks"] or {}).get("sm_mhz")),
             "stages_ms": {k: round(v, 4) for k, v in stages.items()},
@@ -650,10 +835,18 @@ def run_ours(args):
             "per_env_cameras": {"value": results["per_env"]["fps"], "ms_per_step": results["per_env"]["ms"] / args.steps,
                                 "views": results["per_env"]["V"],
                                 "stages_ms": {k: round(v, 4) for k, v in results["per_env"]["stages"].items()},
-                                "counts": results["per_env"]["stats"]},
+                                "counts": dict(results["per_env"]["stats"], static_chunks_live=results["per_env"].get("chunks_live"),
+                                               static_chunks_total=results["per_env"].get("chunks_total"))},
             "cpu_baseline": cpu,
             "gpu_reference_restated": gpu_ref,
         }
+        line["scaling"] = SHARD
+        if world > 1:
+            line["exchange_verified"] = exchange_verified
+            line["strong"] = strong
+        pe = results["per_env"]
+        if pe is not r and pe.get("pairs"):
+            line["per_env_cameras"]["roofline"] = pair_roofline(pe["pairs"], pe["stages"]["blend"], sm_mhz, None, None)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -671,7 +864,13 @@ def main():
     ap.add_argument("--quick-per-env", action="store_true", help="with --quick: profile the per-env-camera mode")
     ap.add_argument("--quick", action="store_true",
                     help="profiling aid: strict mode only, no e2e / per-env / cpu legs (line is NOT a bench value)")
+    ap.add_argument("--config", default="cfg3", choices=sorted(CONFIGS),
+                    help="BASELINE.json configuration (default cfg3, the one the metric is quoted on)")
+    ap.add_argument("--n", type=int, default=None, help="cfg5: Gaussians")
+    ap.add_argument("--res", type=int, default=None, help="cfg5: image side")
+    ap.add_argument("--envs", type=int, default=None, help="cfg5: total envs")
     args = ap.parse_args()
+    select_config(args.config, int(os.environ.get("WORLD_SIZE", "1")), args.n, args.res, args.envs)
     if args.steps is None:
         args.steps = 10 if args.impl == "reference" else 20
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -55,6 +55,7 @@ SYMBOLS = {
     "gsw_kernel_launches": (C.c_longlong, []),
     "gsw_profile_enable": (C.c_int, [_vp, C.c_int]),
     "gsw_profile_read": (C.c_int, [_vp, C.POINTER(C.c_float), C.c_int]),
+    "gsw_profile_counters": (C.c_int, [_vp, C.POINTER(_i64), C.c_int]),
     "gsw_debug_frame_attrs": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gsw_debug_frame_lists": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i64, C.POINTER(_i64), _vp]),
     "gsw_debug_bin_offsets": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), _vp]),

@@ -253,31 +253,27 @@ struct Segment {  // a slice of the key array that is sorted independently (a wh
   uint32_t start, count, bin, pad;
 };
 
-// One thread per tile entry, over the whole sorted key array: fully parallel random gather (two aligned
-// 32 B sectors per entry), coalesced key reads and splat writes.  The list an entry belongs to is found
-// by binary search over the V+F list boundaries (bin_off at multiples of bins_per_list).
+// One thread per tile entry of a SHARED view's static list (blockIdx.y = view): fully parallel random gather (two
+// aligned 32 B sectors per entry), coalesced key reads and splat writes.
 // Only static lists of views shared by several frames are materialised (their records are re-read by every
 // frame of the view and by the view pass).  Static lists private to one frame and all dynamic lists are not:
 // part of their entries is never reached before the pixels saturate, so the blend fetches those records itself.
+// CTAs of unshared views leave at once (with one view per env that is all but one of them).
 __global__ void __launch_bounds__(256)
-gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t n_lists, int32_t V, int64_t Ns,
-                     int64_t Nm, int32_t bins_per_list, const int32_t* __restrict__ pos_of,
+gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_t V, int64_t Ns,
+                     int32_t bins_per_list, const int32_t* __restrict__ pos_of,
                      const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
                      int64_t cap, const int32_t* __restrict__ labels, int32_t* __restrict__ lab_stream,
                      const uint32_t* __restrict__ view_cnt) {
+  const int v = blockIdx.y;
+  if (view_cnt[v] < 2u) return;  // fetched lazily by the blend
   if ((int64_t)bin_off[nbins] > cap) return;
-  const uint32_t D = bin_off[(int64_t)V * bins_per_list];  // end of the static lists
-  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < D; p += gridDim.x * blockDim.x) {
-    int lo = 0, hi = V - 1;  // last list whose start is <= p
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (bin_off[(int64_t)mid * bins_per_list] <= p) lo = mid; else hi = mid - 1;
-    }
-    if (view_cnt[lo] < 2u) continue;  // fetched lazily by the blend
+  const uint32_t p0 = bin_off[(int64_t)v * bins_per_list], p1 = bin_off[(int64_t)(v + 1) * bins_per_list];
+  for (uint32_t p = p0 + blockIdx.x * blockDim.x + threadIdx.x; p < p1; p += gridDim.x * blockDim.x) {
     const u64 key = keys[p];
     const uint32_t idx = (uint32_t)(key & 0xffffffffull);
     const int64_t pos = pos_of ? (int64_t)pos_of[idx] : (int64_t)idx;  // position inside the static layer
-    const int64_t item = (int64_t)lo * Ns + pos;
+    const int64_t item = (int64_t)v * Ns + pos;
     splats[p] = make_splat(rec, item);
     if (lab_stream != nullptr) lab_stream[p] = labels[idx];  // segmentation observation only
   }
@@ -614,12 +610,13 @@ int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int6
   if (nbins <= 0) return 0;
   auto& w = ctx->ws;
   const int32_t bpl = g.T * g.NB;
-  const int32_t n_lists = (int32_t)(nbins / bpl);
-  gather_splats_kernel<<<148 * 16, 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, n_lists, V, Ns, Nm, bpl,
-                                                ctx->last.pos_of, w.keys.as<unsigned long long>(),
-                                                w.rec.as<float4>(), w.splats.as<Splat>(), cap, ctx->labels,
-                                                with_labels ? w.lab_stream.as<int32_t>() : nullptr,
-                                                w.view_cnt.as<uint32_t>());
+  (void)Nm;
+  // enough CTAs per view to fill the machine when a single view is shared (the usual case: one world-fixed camera)
+  const unsigned per_view = V >= 16 ? 74u : (unsigned)(148 * 8 / V);
+  gather_splats_kernel<<<dim3(per_view, (unsigned)V), 256, 0, s>>>(
+      w.bin_off.as<uint32_t>(), nbins, V, Ns, bpl, ctx->last.pos_of, w.keys.as<unsigned long long>(),
+      w.rec.as<float4>(), w.splats.as<Splat>(), cap, ctx->labels, with_labels ? w.lab_stream.as<int32_t>() : nullptr,
+      w.view_cnt.as<uint32_t>());
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -80,6 +80,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
   __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
   __shared__ int32_t sLab[SEG ? kChunk : 1];
+  __shared__ uint32_t sPairs[8];  // per warp: records it ran the per-pixel blend for (x 32 pixels = pair evaluations)
   // 32-bit unsigned division (the grid is f-major: blockIdx.x = (f - f_begin) * T + tile)
   const uint32_t fl = blockIdx.x / (uint32_t)g.T;
   const int f = f_begin + (int)fl, tile = (int)(blockIdx.x - fl * (uint32_t)g.T);
@@ -141,6 +142,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   float best_w = 0.f;
   int32_t best_lab = GSW_SEG_NONE;
   uint32_t base = 0;
+  if (threadIdx.x < 8) sPairs[threadIdx.x] = 0u;  // (the first barrier of the loop orders this before any update)
   for (; base < total; base += kChunk) {
     if (__syncthreads_and(Tacc == 0.0f)) break;  // also protects the staging buffers of the previous round
     const uint32_t n = min((uint32_t)kChunk, total - base);
@@ -235,6 +237,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
     for (uint32_t k0 = 0; k0 < cnt; k0 += 16) {
       if (k0 && __all_sync(0xffffffffu, Tacc == 0.0f)) break;
       const uint32_t kend = min(cnt, k0 + 16);
+      if (lane == 0) sPairs[w] += kend - k0;  // kept in shared memory: the loop has no register to spare
 #pragma unroll 4
       for (uint32_t k = k0; k < kend; ++k) {
         const uint32_t qi = lds_u8(aQ + k);
@@ -269,7 +272,15 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
       }
     }
   }
-  if (threadIdx.x == 0) atomicAdd((unsigned long long*)&status[3], (unsigned long long)min(base, total));
+  // measurement counters: entries staged, and (record, pixel) pair evaluations = 32 x records blended per warp
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd((unsigned long long*)&status[3], (unsigned long long)min(base, total));
+    uint32_t ev = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) ev += sPairs[k];
+    atomicAdd((unsigned long long*)&status[4], 32ull * ev);
+  }
 
   if (inside) {
     if (bg_dev) {

@@ -144,6 +144,12 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
   uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;
   uint32_t* const ch_d = chd ? w.cta_hist.as<uint32_t>() + chs : nullptr;
+  const size_t cm_s = (size_t)V * (size_t)layer_chunks(Ns), cm_d = dyn ? (size_t)F * (size_t)layer_chunks(Nm) : 0;
+  if ((rc = w.chunk_mask.reserve((cm_s + cm_d) * 4 + 16)) || (rc = w.work.reserve(cm_s * 4 + 16)) ||
+      (rc = w.view_consts.reserve((size_t)V * 48 * 4)))
+    return rc;
+  uint32_t* const mask_s = w.chunk_mask.as<uint32_t>();
+  uint32_t* const mask_d = w.chunk_mask.as<uint32_t>() + cm_s;
   int kept_s = 0, kept_d = 0;
   // medium and mid queue (half each): whole bins (<= nbins each) plus sub-segments of huge bins, of which
   // every one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries
@@ -177,12 +183,12 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   mark(0);
   if ((rc = fork())) return rc;
   if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
-                              pose, num_slots, ch_s, &kept_s, ss)))
+                              pose, num_slots, ch_s, mask_s, &kept_s, ss)))
     return rc;
   mark(1);
   if (dyn && Nm > 0)
     if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, view, proj, campos, tanfov, frame_env,
-                                frame_view, pose, num_slots, ch_d, &kept_d, s)))
+                                frame_view, pose, num_slots, ch_d, mask_d, &kept_d, s)))
       return rc;
   if ((rc = join())) return rc;
   mark(2);
@@ -191,9 +197,9 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     return rc;
   mark(3);
   if ((rc = fork())) return rc;
-  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, ss))) return rc;
+  if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, mask_s, ss))) return rc;
   if (dyn && Nm > 0)
-    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, s)))
+    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, mask_d, s)))
       return rc;
   if ((rc = join())) return rc;
   mark(4);
@@ -223,7 +229,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
 }
 
 int finish_launch(gsw_ctx* ctx, cudaStream_t s) {
-  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 12 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
   GSW_CUDA(cudaEventRecord(ctx->done_evt, s));
   ctx->launches++;
   return 0;
@@ -255,7 +261,7 @@ int gsw_create(int device, gsw_ctx** out) {
   Guard gd(device);
   gsw_ctx* c = new gsw_ctx();
   c->device = device;
-  cudaError_t e = cudaMallocHost((void**)&c->h_status, 8 * sizeof(int64_t));
+  cudaError_t e = cudaMallocHost((void**)&c->h_status, 16 * sizeof(int64_t));
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->done_evt, cudaEventDisableTiming);
   for (int k = 0; k <= kNumStages && e == cudaSuccess; ++k) e = cudaEventCreate(&c->stage_evt[k]);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
@@ -284,7 +290,7 @@ int gsw_create(int device, gsw_ctx** out) {
     delete c;
     return (int)e;
   }
-  memset(c->h_status, 0, 8 * sizeof(int64_t));
+  memset(c->h_status, 0, 16 * sizeof(int64_t));
   *out = c;
   return GSW_OK;
 }
@@ -295,7 +301,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.chunk_mask, &w.work, &w.view_consts, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
@@ -775,6 +781,19 @@ int gsw_profile_enable(gsw_ctx* c, int on) {
   return GSW_OK;
 }
 
+int gsw_profile_counters(gsw_ctx* c, int64_t* out, int n) {
+  if (!c || !out || n < 2) {
+    set_error("gsw_profile_counters: need room for 2 counters");
+    return GSW_E_INVALID;
+  }
+  Guard gd(c->device);
+  GSW_CUDA(cudaEventSynchronize(c->done_evt));
+  out[0] = c->h_status[4];  // (record, pixel) pair evaluations of the blend (incl. the view pass)
+  out[1] = c->h_status[3];  // entries staged by the blend
+  if (n >= 3) out[2] = (int64_t)(uint32_t)c->h_status[10];  // live (view, chunk) pairs of the static layer's work list
+  return GSW_OK;
+}
+
 int gsw_profile_read(gsw_ctx* c, float* stage_ms, int n) {
   if (!c || !stage_ms || n < kNumStages) {
     set_error("gsw_profile_read: need room for %d stages", kNumStages);
@@ -942,6 +961,9 @@ int na_setup(int device, NaDevice& nd) {
     gmax.NB = 1;
     carve(w.cta_hist, cta_hist_words(kNaMaxP, 1, gmax) * 4 + 16);
   }
+  carve(w.chunk_mask, (size_t)layer_chunks(kNaMaxP) * 4 + 16);
+  carve(w.work, (size_t)layer_chunks(kNaMaxP) * 4 + 16);
+  carve(w.view_consts, 48 * 4);
   if (off > kNaBytes) {
     set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);
     return GSW_E_NOMEM;

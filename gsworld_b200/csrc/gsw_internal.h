@@ -126,6 +126,11 @@ struct Workspace {
   DevBuf view_cnt, st_u8, st_color, st_invd, st_seg;  // frames per view; static-only image of each shared view
   DevBuf lab_stream;            // int32 [cap_entries]: label of every stream entry (segmentation observation only)
   DevBuf cta_hist;  // u32: per preprocess CTA {live flag, per-bin entry counts}, consumed by the scatter pass
+  // per (list, 2048-item chunk): mask of the 256-item groups that survived group culling ([V static lists | F
+  // dynamic lists]); items of dead groups are never written, so every reader of `rad` looks here first
+  DevBuf chunk_mask;
+  DevBuf work;         // u32 (view << 16 | chunk): live (view, chunk) pairs of the static layer, cull_chunks_kernel
+  DevBuf view_consts;  // 48 words per view: ViewSmem + ViewCull, written by cull_chunks_kernel
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -203,11 +208,13 @@ namespace gsw {
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
-                      const float* pose, int32_t num_slots, uint32_t* cta_hist, int* kept_hist, cudaStream_t s);
+                      const float* pose, int32_t num_slots, uint32_t* cta_hist, uint32_t* chunk_mask, int* kept_hist,
+                      cudaStream_t s);
 size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g);
+int64_t layer_chunks(int64_t n_items);  // 2048-item chunks of a layer (one preprocess / scatter CTA round each)
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
-                   cudaStream_t s);
+                   const uint32_t* chunk_mask, cudaStream_t s);
 int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,
                        float* xy, float* conic_opacity, float* rgb, cudaStream_t s);
 int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s);

@@ -618,47 +618,22 @@ __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
   } while (!ok);
 }
 
-// grid: (ceil(n_items / IPB), n_lists); list = view (static layer) or frame (dynamic layer).
-// Dynamic shared memory: [staged arrays (if use_tma)] [hist: T*NB u32 (if use_hist)] [pose table (DYN)].
-template <bool DYN, int IPB, bool TMA, bool CULL>
-__global__ void __launch_bounds__(256, TMA ? 2 : 3)
-preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
-                  const float* __restrict__ views, const float* __restrict__ projs,
-                  const float* __restrict__ campos, const float* __restrict__ tanfov,
-                  const int32_t* __restrict__ frame_env, const int32_t* __restrict__ frame_view,
-                  const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
-                  float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
-                  uint32_t* __restrict__ bin_count, int use_hist, uint32_t* __restrict__ cta_hist) {
-  constexpr int use_tma = TMA ? 1 : 0;
-  __shared__ ViewSmem vs;
-  __shared__ __align__(8) unsigned long long mbar_s;
-  extern __shared__ __align__(128) unsigned char dsm_raw[];
-  constexpr int IPT = IPB / 256;
-  const int nbl = g.T * g.NB;
-  // staged layout (bytes per item): static 12 xyz + 12 scale + 16 quat + 4 opacity + 4 slot = 48;
-  //                                 dynamic 12 xyz + 12 scale + 12 log-scale + 16 quat_raw + 4 opacity + 4 slot = 60
-  constexpr size_t kStage = (size_t)IPB * (DYN ? 60 : 48);
-  unsigned char* stage = dsm_raw;
-  uint32_t* hist_base = reinterpret_cast<uint32_t*>(dsm_raw + (use_tma ? kStage : 0));
-  uint32_t* hist = use_hist ? hist_base : nullptr;
-  float* pose_s = reinterpret_cast<float*>(hist_base + (use_hist ? nbl : 0));
-  const int list = blockIdx.y;
-  int view = list, env = 0;
-  if (DYN) {
-    view = frame_view[list];
-    env = frame_env[list];
-  }
-  const int64_t base = (int64_t)blockIdx.x * IPB;
-  const bool full = base + IPB <= n_items;
-  const bool staged = use_tma && full;  // partial tail chunk: plain global loads
-  float* xyz_s = reinterpret_cast<float*>(stage);
-  float* sc_s = xyz_s + 3 * IPB;
-  float* ls_s = sc_s + 3 * IPB;                                // DYN only
-  float* q_s = DYN ? ls_s + 3 * IPB : sc_s + 3 * IPB;         // 16 B aligned: IPB multiple of 4
-  float* op_s = q_s + 4 * IPB;
-  int32_t* slot_s = reinterpret_cast<int32_t*>(op_s + IPB);
-  __shared__ ViewCull vc;
-  __shared__ int grp_culled[IPT];
+// Per-view constants of the preprocess pass: the view itself plus the numbers of the group-level frustum tests.
+// 48 words; computed by a few designated threads of a 256-thread CTA (compute_view_consts) and, for the static
+// layer's work-list form, kept in global memory by the chunk-cull kernel so that a preprocess CTA only copies them.
+struct ViewConsts {
+  ViewSmem vs;
+  ViewCull vc;
+  float pad[2];
+};
+static_assert(sizeof(ViewConsts) == 48 * 4, "ViewConsts: 48 words");
+constexpr int kViewConstWords = 48;
+
+// Must be called by all threads of a CTA of >= 96 threads; the caller synchronises afterwards.
+__device__ __forceinline__ void compute_view_consts(int view, const FrameGeom& g, const float* __restrict__ views,
+                                                    const float* __restrict__ projs,
+                                                    const float* __restrict__ campos,
+                                                    const float* __restrict__ tanfov, ViewSmem& vs, ViewCull& vc) {
   if (threadIdx.x < 16) {
     vs.V[threadIdx.x] = views[view * 16 + threadIdx.x];
     vs.P[threadIdx.x] = projs[view * 16 + threadIdx.x];
@@ -713,113 +688,228 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     vc.nzb = (float)(g.gy * kTile) - 0.5f * (float)g.H + 7.0f;
     vc.proj_std = ok ? 1 : 0;
   }
-  if (use_hist)
-    for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
-  if (DYN) {
-    for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
-      pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
-  }
-  __syncthreads();  // view / pose / histogram ready
-  if (threadIdx.x < IPT) {
-    const int64_t g0 = base + (int64_t)threadIdx.x * 256;
-    int c = 0;
-    if (g0 >= n_items) c = 1;
-    else if (ga.bounds != nullptr) c = group_culled<DYN>(ga.bounds + (g0 >> 8) * 8, vs, vc, g, pose_s) ? 1 : 0;
-    grp_culled[threadIdx.x] = c;
-  }
+}
+
+// ---- chunk-level culling of the static layer, ahead of the preprocess pass ----
+// One thread per (view, 2048-item chunk): tests the chunk's 8 group spheres against the view and leaves the mask
+// of live groups in chunk_mask[view * nchunks + chunk]; chunks with at least one live group are appended to a
+// compact work list (view << 16 | chunk) that the preprocess and scatter passes of the static layer walk with
+// persistent CTAs.  A wrist camera sees a sliver of the room: with one view per env most (view, chunk) pairs are
+// dead, and launching a CTA for each only to find that out (and to write "radius 0" for its 2048 items) cost more
+// than the live ones' arithmetic.  Items of dead groups are never written at all now; every reader of `rad`
+// consults the mask.  grid (ceil(nchunks / 256), V).
+__global__ void __launch_bounds__(256)
+cull_chunks_kernel(const float* __restrict__ bounds, int64_t n_items, int32_t nchunks, FrameGeom g,
+                   const float* __restrict__ views, const float* __restrict__ projs,
+                   const float* __restrict__ campos, const float* __restrict__ tanfov,
+                   uint32_t* __restrict__ chunk_mask, uint32_t* __restrict__ work, uint32_t* __restrict__ work_count,
+                   uint32_t* __restrict__ view_consts) {
+  __shared__ ViewConsts c;
+  const int view = blockIdx.y;
+  compute_view_consts(view, g, views, projs, campos, tanfov, c.vs, c.vc);
   __syncthreads();
-  bool any_live = false;
+  if (blockIdx.x == 0 && threadIdx.x < kViewConstWords)
+    view_consts[(size_t)view * kViewConstWords + threadIdx.x] = reinterpret_cast<const uint32_t*>(&c)[threadIdx.x];
+  const int chunk = blockIdx.x * 256 + threadIdx.x;
+  uint32_t mask = 0;
+  if (chunk < nchunks) {
+    constexpr int kGroups = kItemsPerBlock / 256;
+#pragma unroll 1
+    for (int k = 0; k < kGroups; ++k) {
+      const int64_t g0 = (int64_t)chunk * kItemsPerBlock + k * 256;
+      if (g0 < n_items && !group_culled<false>(bounds + (g0 >> 8) * 8, c.vs, c.vc, g, nullptr)) mask |= 1u << k;
+    }
+    chunk_mask[(size_t)view * nchunks + chunk] = mask;
+  }
+  const unsigned live = __ballot_sync(0xffffffffu, mask != 0);
+  if (live) {
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(work_count, (uint32_t)__popc(live));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (mask) work[base + __popc(live & ((1u << lane) - 1u))] = ((uint32_t)view << 16) | (uint32_t)chunk;
+  }
+}
+
+// grid: (ceil(n_items / IPB), n_lists); list = view (static layer) or frame (dynamic layer).  WL (static layer
+// only): persistent CTAs pull (view, chunk) pairs from the work list of cull_chunks_kernel with a ticket counter.
+// Dynamic shared memory: [staged arrays (if use_tma)] [hist: T*NB u32 (if use_hist)] [pose table (DYN)].
+template <bool DYN, int IPB, bool TMA, bool CULL, bool WL>
+__global__ void __launch_bounds__(256, TMA ? 2 : 3)
+preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
+                  const float* __restrict__ views, const float* __restrict__ projs,
+                  const float* __restrict__ campos, const float* __restrict__ tanfov,
+                  const int32_t* __restrict__ frame_env, const int32_t* __restrict__ frame_view,
+                  const float* __restrict__ pose, int32_t num_slots, float4* __restrict__ recA,
+                  float4* __restrict__ recB, float4* __restrict__ recC, int32_t* __restrict__ rad,
+                  uint32_t* __restrict__ bin_count, int use_hist, uint32_t* __restrict__ cta_hist,
+                  uint32_t* __restrict__ chunk_mask, int32_t nchunks, const uint32_t* __restrict__ work,
+                  const uint32_t* __restrict__ work_count, uint32_t* __restrict__ ticket,
+                  const uint32_t* __restrict__ view_consts) {
+  static_assert(!(WL && DYN), "the work-list form is the static layer's");
+  constexpr int use_tma = TMA ? 1 : 0;
+  __shared__ ViewConsts vcs;
+  ViewSmem& vs = vcs.vs;
+  ViewCull& vc = vcs.vc;
+  __shared__ __align__(8) unsigned long long mbar_s;
+  __shared__ uint32_t s_work;
+  extern __shared__ __align__(128) unsigned char dsm_raw[];
+  constexpr int IPT = IPB / 256;
+  const int nbl = g.T * g.NB;
+  // staged layout (bytes per item): static 12 xyz + 12 scale + 16 quat + 4 opacity + 4 slot = 48;
+  //                                 dynamic 12 xyz + 12 scale + 12 log-scale + 16 quat_raw + 4 opacity + 4 slot = 60
+  constexpr size_t kStage = (size_t)IPB * (DYN ? 60 : 48);
+  unsigned char* stage = dsm_raw;
+  uint32_t* hist_base = reinterpret_cast<uint32_t*>(dsm_raw + (use_tma ? kStage : 0));
+  uint32_t* hist = use_hist ? hist_base : nullptr;
+  float* pose_s = reinterpret_cast<float*>(hist_base + (use_hist ? nbl : 0));
+  float* xyz_s = reinterpret_cast<float*>(stage);
+  float* sc_s = xyz_s + 3 * IPB;
+  float* ls_s = sc_s + 3 * IPB;                                // DYN only
+  float* q_s = DYN ? ls_s + 3 * IPB : sc_s + 3 * IPB;         // 16 B aligned: IPB multiple of 4
+  float* op_s = q_s + 4 * IPB;
+  int32_t* slot_s = reinterpret_cast<int32_t*>(op_s + IPB);
+  __shared__ int grp_culled[IPT];
+  const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar_s);
+  if (use_tma && threadIdx.x == 0) mbar_init(mb, 1);  // made visible by the first barrier below
+  uint32_t tma_phase = 0;
+#pragma unroll 1
+  for (;;) {
+    int list, chunk;
+    if (WL) {
+      // (the barrier after the view set-up separates this write from the previous round's reads of s_work)
+      if (threadIdx.x == 0) {
+        const uint32_t t = atomicAdd(ticket, 1u);
+        s_work = t < *work_count ? work[t] : 0xffffffffu;
+      }
+      __syncthreads();
+      const uint32_t wv = s_work;
+      if (wv == 0xffffffffu) break;  // CTA-uniform
+      list = (int)(wv >> 16);
+      chunk = (int)(wv & 0xffffu);
+    } else {
+      list = blockIdx.y;
+      chunk = blockIdx.x;
+    }
+    int view = list, env = 0;
+    if (DYN) {
+      view = frame_view[list];
+      env = frame_env[list];
+    }
+    const int64_t base = (int64_t)chunk * IPB;
+    const bool full = base + IPB <= n_items;
+    const bool staged = use_tma && full;  // partial tail chunk: plain global loads
+    const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
+    if (WL) {
+      if (threadIdx.x < kViewConstWords)
+        reinterpret_cast<uint32_t*>(&vcs)[threadIdx.x] = view_consts[(size_t)view * kViewConstWords + threadIdx.x];
+    } else {
+      compute_view_consts(view, g, views, projs, campos, tanfov, vs, vc);
+    }
+    if (use_hist)
+      for (int k = threadIdx.x; k < nbl; k += blockDim.x) hist[k] = 0u;
+    if (DYN) {
+      for (int k = threadIdx.x; k < num_slots * GSW_POSE_STRIDE; k += blockDim.x)
+        pose_s[k] = pose[(size_t)env * num_slots * GSW_POSE_STRIDE + k];
+    }
+    __syncthreads();  // view / pose / histogram ready
+    if (threadIdx.x < IPT) {
+      const int64_t g0 = base + (int64_t)threadIdx.x * 256;
+      int c = 0;
+      if (g0 >= n_items) c = 1;
+      else if (WL) c = ((chunk_mask[chunk_id] >> threadIdx.x) & 1u) ? 0 : 1;
+      else if (ga.bounds != nullptr) c = group_culled<DYN>(ga.bounds + (g0 >> 8) * 8, vs, vc, g, pose_s) ? 1 : 0;
+      grp_culled[threadIdx.x] = c;
+    }
+    __syncthreads();
+    uint32_t live_mask = 0;
 #pragma unroll
-  for (int it = 0; it < IPT; ++it) any_live = any_live || grp_culled[it] == 0;
-  if (!any_live) {  // nothing of this chunk can reach the image: mark every item "no tile" and leave
-#pragma unroll 1
-    for (int it = 0; it < IPT; ++it) {
-      const int64_t i = base + it * 256 + threadIdx.x;
-      if (i < n_items) rad[item_base + (int64_t)list * n_items + i] = 0;
+    for (int it = 0; it < IPT; ++it) live_mask |= grp_culled[it] == 0 ? 1u << it : 0u;
+    // items of dead groups are never written: every reader of `rad` consults this mask first
+    if (!WL && chunk_mask != nullptr && threadIdx.x == 0) chunk_mask[chunk_id] = live_mask;
+    if (live_mask == 0) {  // nothing of this chunk can reach the image
+      if (cta_hist != nullptr && threadIdx.x == 0) cta_hist[chunk_id * (size_t)(nbl + 1)] = 0u;  // scatter skips the chunk
+      if (WL) continue;
+      return;
     }
-    if (cta_hist != nullptr && threadIdx.x == 0)
-      cta_hist[((size_t)list * gridDim.x + blockIdx.x) * (size_t)(g.T * g.NB + 1)] = 0u;  // scatter skips the chunk
-    return;
-  }
-  if (staged && threadIdx.x == 0) {
-    const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar_s);
-    mbar_init(mb, 1);
-    const bool want_slot = DYN || ga.slot != nullptr;
-    const uint32_t bytes = (uint32_t)IPB * ((DYN ? 56u : 44u) + (want_slot ? 4u : 0u));
-    mbar_expect_tx(mb, bytes);
-    auto sa = [](const void* p) { return (uint32_t)__cvta_generic_to_shared(p); };
-    bulk_g2s(sa(xyz_s), ga.xyz + 3 * base, IPB * 12, mb);
-    bulk_g2s(sa(sc_s), ga.scale_act + 3 * base, IPB * 12, mb);
-    if (DYN) {
-      bulk_g2s(sa(ls_s), ga.log_scale_raw + 3 * base, IPB * 12, mb);
-      bulk_g2s(sa(q_s), ga.quat_raw + 4 * base, IPB * 16, mb);
-      bulk_g2s(sa(slot_s), ga.mov_slot + base, IPB * 4, mb);
-    } else {
-      bulk_g2s(sa(q_s), ga.quat_act + 4 * base, IPB * 16, mb);
-      if (want_slot) bulk_g2s(sa(slot_s), ga.slot + base, IPB * 4, mb);
+    if (staged && threadIdx.x == 0) {
+      const bool want_slot = DYN || ga.slot != nullptr;
+      const uint32_t bytes = (uint32_t)IPB * ((DYN ? 56u : 44u) + (want_slot ? 4u : 0u));
+      mbar_expect_tx(mb, bytes);
+      auto sa = [](const void* p) { return (uint32_t)__cvta_generic_to_shared(p); };
+      bulk_g2s(sa(xyz_s), ga.xyz + 3 * base, IPB * 12, mb);
+      bulk_g2s(sa(sc_s), ga.scale_act + 3 * base, IPB * 12, mb);
+      if (DYN) {
+        bulk_g2s(sa(ls_s), ga.log_scale_raw + 3 * base, IPB * 12, mb);
+        bulk_g2s(sa(q_s), ga.quat_raw + 4 * base, IPB * 16, mb);
+        bulk_g2s(sa(slot_s), ga.mov_slot + base, IPB * 4, mb);
+      } else {
+        bulk_g2s(sa(q_s), ga.quat_act + 4 * base, IPB * 16, mb);
+        if (want_slot) bulk_g2s(sa(slot_s), ga.slot + base, IPB * 4, mb);
+      }
+      bulk_g2s(sa(op_s), ga.opacity + base, IPB * 4, mb);
     }
-    bulk_g2s(sa(op_s), ga.opacity + base, IPB * 4, mb);
-  }
-  if (staged) __syncthreads();  // mbarrier initialised before anyone waits on it
-  GaussArrays la = ga;
-  if (staged) {
-    mbar_wait((uint32_t)__cvta_generic_to_shared(&mbar_s), 0);
-    la.xyz = xyz_s;
-    la.scale_act = sc_s;
-    la.opacity = op_s;
-    if (DYN) {
-      la.log_scale_raw = ls_s;
-      la.quat_raw = q_s;
-      la.mov_slot = slot_s;
-    } else {
-      la.quat_act = q_s;
-      if (ga.slot != nullptr) la.slot = slot_s;
-    }
-  }
-  const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)nbl;
-#pragma unroll 1
-  for (int it = 0; it < IPT; ++it) {
-    const int il = it * 256 + threadIdx.x;
-    const int64_t i = base + il;
-    Rect rc{0, 0, 0, 0};
-    uint32_t bk = 0;
-    Foot ft{};
-    if (i < n_items) {
-      const int64_t item = item_base + (int64_t)list * n_items + i;
-      if (grp_culled[it]) {
-        rad[item] = 0;
-      } else if (TMA) {
-        preprocess_item<DYN, CULL>(ga, la, i, staged ? (int64_t)il : i, item, list_base + list, g, vs, pose_s, recA,
-                                   recB, recC, rad, bin_count, hist, rc, bk, ft);
-      } else {  // same object for both roles: every load stays a read-only global load
-        preprocess_item<DYN, CULL>(ga, ga, i, i, item, list_base + list, g, vs, pose_s, recA, recB, recC, rad,
-                                   bin_count, hist, rc, bk, ft);
+    GaussArrays la = ga;
+    if (staged) {
+      mbar_wait(mb, tma_phase);
+      tma_phase ^= 1u;
+      la.xyz = xyz_s;
+      la.scale_act = sc_s;
+      la.opacity = op_s;
+      if (DYN) {
+        la.log_scale_raw = ls_s;
+        la.quat_raw = q_s;
+        la.mov_slot = slot_s;
+      } else {
+        la.quat_act = q_s;
+        if (ga.slot != nullptr) la.slot = slot_s;
       }
     }
-    if (CULL) {  // count into the bins of the tiles that pass the exact test (all 32 lanes arrive here)
-      unsigned long long alive;
-      if (use_hist)
-        alive = warp_cull_count(rc, bk, ft, g.gx, g.NB, [&](uint32_t b) { atomicAdd(&hist[b], 1u); });
-      else
-        alive = warp_cull_count(rc, bk, ft, g.gx, g.NB, [&](uint32_t b) { atomicAdd(&bin_count[lbase + b], 1u); });
-      // recD (4th float4 of the 64 B slot): mask of the alive tiles among the first 64 of the rectangle,
-      // row-major; the scatter pass walks the set bits instead of repeating the test
-      if (rc.x1 > rc.x0)
-        recA[4 * (item_base + (int64_t)list * n_items + i) + 3] =
-            make_float4(__uint_as_float((uint32_t)alive), __uint_as_float((uint32_t)(alive >> 32)), 0.f, 0.f);
+    const uint32_t lbase = (uint32_t)(list_base + list) * (uint32_t)nbl;
+#pragma unroll 1
+    for (int it = 0; it < IPT; ++it) {
+      const int il = it * 256 + threadIdx.x;
+      const int64_t i = base + il;
+      Rect rc{0, 0, 0, 0};
+      uint32_t bk = 0;
+      Foot ft{};
+      if (i < n_items && !grp_culled[it]) {
+        const int64_t item = item_base + (int64_t)list * n_items + i;
+        if (TMA) {
+          preprocess_item<DYN, CULL>(ga, la, i, staged ? (int64_t)il : i, item, list_base + list, g, vs, pose_s, recA,
+                                     recB, recC, rad, bin_count, hist, rc, bk, ft);
+        } else {  // same object for both roles: every load stays a read-only global load
+          preprocess_item<DYN, CULL>(ga, ga, i, i, item, list_base + list, g, vs, pose_s, recA, recB, recC, rad,
+                                     bin_count, hist, rc, bk, ft);
+        }
+      }
+      if (CULL) {  // count into the bins of the tiles that pass the exact test (all 32 lanes arrive here)
+        unsigned long long alive;
+        if (use_hist)
+          alive = warp_cull_count(rc, bk, ft, g.gx, g.NB, [&](uint32_t b) { atomicAdd(&hist[b], 1u); });
+        else
+          alive = warp_cull_count(rc, bk, ft, g.gx, g.NB, [&](uint32_t b) { atomicAdd(&bin_count[lbase + b], 1u); });
+        // recD (4th float4 of the 64 B slot): mask of the alive tiles among the first 64 of the rectangle,
+        // row-major; the scatter pass walks the set bits instead of repeating the test
+        if (rc.x1 > rc.x0)
+          recA[4 * (item_base + (int64_t)list * n_items + i) + 3] =
+              make_float4(__uint_as_float((uint32_t)alive), __uint_as_float((uint32_t)(alive >> 32)), 0.f, 0.f);
+      }
     }
-  }
-  if (use_hist) {
-    __syncthreads();
-    const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
-    // the per-CTA counts are kept for the scatter pass, which walks the same chunk: word 0 = chunk is live
-    uint32_t* keep = cta_hist ? cta_hist + ((size_t)list * gridDim.x + blockIdx.x) * (size_t)(nbl + 1) : nullptr;
-    if (keep != nullptr && threadIdx.x == 0) keep[0] = 1u;
-    for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
-      const uint32_t c = hist[k];
-      if (c) atomicAdd(&bin_count[gb + k], c);
-      if (keep != nullptr) keep[1 + k] = c;
+    if (use_hist) {
+      __syncthreads();
+      const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
+      // the per-CTA counts are kept for the scatter pass, which walks the same chunk: word 0 = chunk is live
+      uint32_t* keep = cta_hist ? cta_hist + chunk_id * (size_t)(nbl + 1) : nullptr;
+      if (keep != nullptr && threadIdx.x == 0) keep[0] = 1u;
+      for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
+        const uint32_t c = hist[k];
+        if (c) atomicAdd(&bin_count[gb + k], c);
+        if (keep != nullptr) keep[1 + k] = c;
+      }
     }
+    if (!WL) break;
+    __syncthreads();  // staged arrays, histogram and view constants are rewritten by the next round
   }
 }
 
@@ -834,25 +924,58 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
 // the chunk's 8 groups (instead of 32 neighbours) cuts same-address shared-memory atomic conflicts 8-fold.
 __device__ __forceinline__ int scatter_slot(int it, int t) { return ((t & 7) << 8) | (it << 5) | (t >> 3); }
 
-template <bool DYN>
+// (list, chunk) of a scatter CTA's next round.  Plain form: one round, the block indices.  Work-list form (static
+// layer): persistent CTAs take (view, chunk) pairs of cull_chunks_kernel's list by ticket.  CTA-uniform result.
+template <bool WL>
+__device__ __forceinline__ bool next_chunk(int& list, int& chunk, bool first, const uint32_t* __restrict__ work,
+                                           const uint32_t* __restrict__ work_count, uint32_t* __restrict__ ticket,
+                                           uint32_t* s_work) {
+  if (!WL) {
+    list = blockIdx.y;
+    chunk = blockIdx.x;
+    return first;
+  }
+  __syncthreads();  // the previous round is done with the shared counters and with s_work
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(ticket, 1u);
+    *s_work = t < *work_count ? work[t] : 0xffffffffu;
+  }
+  __syncthreads();
+  const uint32_t wv = *s_work;
+  list = (int)(wv >> 16);
+  chunk = (int)(wv & 0xffffu);
+  return wv != 0xffffffffu;
+}
+
+template <bool DYN, bool WL>
 __global__ void __launch_bounds__(256)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                const float4* __restrict__ recA, const float4* __restrict__ /*recB*/,
                const float4* __restrict__ recC, const int32_t* __restrict__ rad,
                const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
                unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
-               const uint32_t* __restrict__ cta_hist) {
+               const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
+               const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
+               uint32_t* __restrict__ ticket) {
   extern __shared__ uint32_t dsm[];
+  __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
   uint32_t* hist = dsm;         // counts, then running slot counters
   uint32_t* hbase = dsm + nbl;  // absolute start of this CTA's range in each bin
-  const int list = blockIdx.y;
+  int list, chunk;
+  bool first = true;
+#pragma unroll 1
+  for (; next_chunk<WL>(list, chunk, first, work, work_count, ticket, &s_work); first = false) {
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
-  const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
+  const int64_t base = (int64_t)chunk * kItemsPerBlock;
+  const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
+  // groups of the chunk that the preprocess pass found dead were never written: their items count as radius 0.
+  // scatter_slot() gives every thread items of ONE group, (threadIdx.x & 7).
+  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & 7)) & 1u;
+  if (chunk_mask[chunk_id] == 0u) continue;  // whole chunk culled (CTA-uniform)
   if (use_hist && cta_hist != nullptr) {
     // the preprocess CTA that walked this chunk left its per-bin counts: no second counting pass
-    const uint32_t* keep = cta_hist + ((size_t)list * gridDim.x + blockIdx.x) * (size_t)(nbl + 1);
-    if (keep[0] == 0u) return;  // whole chunk culled
+    const uint32_t* keep = cta_hist + chunk_id * (size_t)(nbl + 1);
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
       const uint32_t c = keep[1 + k];
       if (c) hbase[k] = bin_off[gb + k] + atomicAdd(&bin_cursor[gb + k], c);
@@ -865,7 +988,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
 #pragma unroll 1
     for (int it = 0; it < kItemsPerThread; ++it) {
       const int64_t i = base + scatter_slot(it, threadIdx.x);
-      if (i >= n_items) continue;
+      if (i >= n_items || !glive) continue;
       const int64_t item = item_base + (int64_t)list * n_items + i;
       const int radius = rad[item];
       if (radius <= 0) continue;
@@ -891,7 +1014,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
     const int64_t i = base + scatter_slot(it, threadIdx.x);
-    radius[it] = i < n_items ? rad[item_base + (int64_t)list * n_items + i] : 0;
+    radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
@@ -924,6 +1047,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
       if ((int64_t)pos < cap) keys[pos] = ((unsigned long long)hi << 32) | lo;
     });
   }
+  }  // rounds
 }
 
 // Scatter with exact tile culling: the preprocess pass left, per visible Gaussian, the mask of its alive tiles
@@ -931,24 +1055,32 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
 // (kCoopBitsCull) and rectangles of more than 64 tiles (tested again, same make_foot / tile_alive on the same bits) are
 // expanded by the whole warp.  Needs the preprocess CTA's bin counts (cta_hist) for the shared-memory slot
 // counters; without them it falls back to global cursors.
-template <bool DYN>
+template <bool DYN, bool WL>
 __global__ void __launch_bounds__(256)
 scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                     const float4* __restrict__ recA, const float4* __restrict__ recB,
                     const float4* __restrict__ recC, const int32_t* __restrict__ rad,
                     const uint32_t* __restrict__ bin_off, uint32_t* __restrict__ bin_cursor,
                     unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
-                    const uint32_t* __restrict__ cta_hist) {
+                    const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
+                    const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
+                    uint32_t* __restrict__ ticket) {
   extern __shared__ uint32_t dsm[];
+  __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
   uint32_t* hist = dsm;         // running slot counters
   uint32_t* hbase = dsm + nbl;  // absolute start of this CTA's range in each bin
-  const int list = blockIdx.y;
+  int list, chunk;
+  bool first = true;
+#pragma unroll 1
+  for (; next_chunk<WL>(list, chunk, first, work, work_count, ticket, &s_work); first = false) {
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
-  const int64_t base = (int64_t)blockIdx.x * kItemsPerBlock;
+  const int64_t base = (int64_t)chunk * kItemsPerBlock;
+  const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
+  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & 7)) & 1u;  // see scatter_kernel
+  if (chunk_mask[chunk_id] == 0u) continue;  // whole chunk culled (CTA-uniform)
   if (use_hist) {
-    const uint32_t* keep = cta_hist + ((size_t)list * gridDim.x + blockIdx.x) * (size_t)(nbl + 1);
-    if (keep[0] == 0u) return;  // whole chunk culled
+    const uint32_t* keep = cta_hist + chunk_id * (size_t)(nbl + 1);
     for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
       const uint32_t c = keep[1 + k];
       if (c) hbase[k] = bin_off[gb + k] + atomicAdd(&bin_cursor[gb + k], c);
@@ -969,7 +1101,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
     const int64_t i = base + scatter_slot(it, threadIdx.x);
-    radius[it] = i < n_items ? rad[item_base + (int64_t)list * n_items + i] : 0;
+    radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
   // (loading the 8 items' records ahead of the loop, as the plain scatter does, measured slower here: the loop
   // is not unrolled, so the batch would live in local memory)
@@ -1044,28 +1176,35 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
       }
     }
   }
+  }  // rounds
 }
 
-// Where the preprocess record of original Gaussian i lives for frame f (view v):
-// static layer item = v*Ns + pos, dynamic layer item = V*Ns + f*Nm + pos, pos = pos_of[i] (identity if null).
-__device__ __forceinline__ int64_t item_of(int64_t i, int32_t f, int32_t v, int32_t V, int64_t Ns, int64_t Nm,
-                                           const int32_t* slot, const int32_t* pos_of) {
+// Radius of original Gaussian i in frame f (view v), 0 for items of groups the preprocess pass found dead (those
+// are never written; chunk_mask = live groups per (list, chunk): V static lists, then F dynamic lists).
+__device__ __forceinline__ int radius_of(int64_t i, int32_t f, int32_t v, int32_t V, int64_t Ns, int64_t Nm,
+                                         const int32_t* slot, const int32_t* pos_of, const int32_t* rad,
+                                         const uint32_t* chunk_mask, int64_t* item_out) {
   const int64_t pos = pos_of ? (int64_t)pos_of[i] : i;
-  if (slot != nullptr && slot[i] >= 0) return (int64_t)V * Ns + (int64_t)f * Nm + pos;
-  return (int64_t)v * Ns + pos;
+  const bool dyn = slot != nullptr && slot[i] >= 0;
+  const int64_t nch_s = (Ns + kItemsPerBlock - 1) / kItemsPerBlock, nch_d = (Nm + kItemsPerBlock - 1) / kItemsPerBlock;
+  const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)f * Nm + pos : (int64_t)v * Ns + pos;
+  const int64_t cid = (dyn ? (int64_t)V * nch_s + (int64_t)f * nch_d : (int64_t)v * nch_s) + pos / kItemsPerBlock;
+  *item_out = item;
+  if (chunk_mask != nullptr && !((chunk_mask[cid] >> ((pos % kItemsPerBlock) >> 8)) & 1u)) return 0;
+  return rad[item];
 }
 
 // Per-Gaussian taps of one frame, addressed by original index (parity tests / radii output).
 __global__ void frame_attrs_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V, int32_t frame,
                                    const int32_t* frame_view, const int32_t* slot, const int32_t* pos_of, FrameGeom g,
                                    const float4* recA, const float4* recB, const float4* recC, const int32_t* rad,
-                                   int32_t* radii, int32_t* tiles, float* depth, float* xy, float* conic_o,
-                                   float* rgb) {
+                                   const uint32_t* chunk_mask, int32_t* radii, int32_t* tiles, float* depth, float* xy,
+                                   float* conic_o, float* rgb) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int view = frame_view ? frame_view[frame] : 0;
-  const int64_t item = item_of(i, frame, view, V, Ns, Nm, slot, pos_of);
-  const int r = rad[item];
+  int64_t item;
+  const int r = radius_of(i, frame, view, V, Ns, Nm, slot, pos_of, rad, chunk_mask, &item);
   float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
   int tt = 0;
   if (r > 0) {
@@ -1092,12 +1231,14 @@ __global__ void frame_attrs_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V,
 
 // radii of every frame: out[f, i]
 __global__ void radii_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V, const int32_t* frame_view,
-                             const int32_t* slot, const int32_t* pos_of, const int32_t* rad, int32_t* out) {
+                             const int32_t* slot, const int32_t* pos_of, const int32_t* rad,
+                             const uint32_t* chunk_mask, int32_t* out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int f = blockIdx.y;
   const int view = frame_view ? frame_view[f] : 0;
-  out[(int64_t)f * N + i] = rad[item_of(i, f, view, V, Ns, Nm, slot, pos_of)];
+  int64_t item;
+  out[(int64_t)f * N + i] = radius_of(i, f, view, V, Ns, Nm, slot, pos_of, rad, chunk_mask, &item);
 }
 
 __global__ void mark_visible_kernel(int32_t P, const float* xyz, const float* V, float near_plane, uint8_t* out) {
@@ -1259,10 +1400,23 @@ int ensure_smem(size_t bytes, int device) {
 // keeps plain loads and the larger chunk; only the static layer stages through TMA.
 constexpr int kIpbStatic = 2048, kIpbDynamic = 2048;
 
+// Words of Workspace::status (u32 view) used by the static layer's work list: entries, and one ticket per pass.
+constexpr int kWorkCountWord = 20, kPreTicketWord = 21, kScatterTicketWord = 22;
+
+int64_t layer_chunks(int64_t n_items) { return (n_items + kItemsPerBlock - 1) / kItemsPerBlock; }
+
+// The static layer goes through the chunk-cull work list when its groups have bounds (scene layers; the single-frame
+// entry points have none) and (view, chunk) fits the 16 + 16 bit packing.
+bool use_work_list(bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
+  return !dynamic && ga.bounds != nullptr && n_lists <= 65535 && layer_chunks(n_items) <= 65535 &&
+         getenv("GSW_NO_WORK_LIST") == nullptr;
+}
+
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
-                      const float* pose, int32_t num_slots, uint32_t* cta_hist, int* kept_hist, cudaStream_t s) {
+                      const float* pose, int32_t num_slots, uint32_t* cta_hist, uint32_t* chunk_mask, int* kept_hist,
+                      cudaStream_t s) {
   if (kept_hist) *kept_hist = 0;
   if (n_items <= 0 || n_lists <= 0) return 0;
   auto& w = ctx->ws;
@@ -1284,23 +1438,50 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     use_hist = 1;
   }
   const size_t sm = (use_tma ? stage_b : 0) + (use_hist ? hist_b : 0) + pose_b;
+  const int32_t nchunks = (int32_t)layer_chunks(n_items);
+  const bool wl = use_work_list(dynamic, ga, n_items, n_lists);
+  uint32_t* const st32 = w.status.as<uint32_t>();
+  if (wl) {
+    dim3 cg((unsigned)((nchunks + 255) / 256), (unsigned)n_lists);
+    cull_chunks_kernel<<<cg, 256, 0, s>>>(ga.bounds, n_items, nchunks, g, view, proj, campos, tanfov, chunk_mask,
+                                          w.work.as<uint32_t>(), st32 + kWorkCountWord,
+                                          w.view_consts.as<uint32_t>());
+    count_launches(1);
+  }
   int rc;
-#define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_, CULL_)                                                                   \
+#define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_, CULL_, WL_)                                                              \
   do {                                                                                                            \
-    dim3 grid((unsigned)((n_items + IPB_ - 1) / IPB_), (unsigned)n_lists);                                        \
-    if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_, CULL_>>(sm, ctx->device))) return rc;               \
-    preprocess_kernel<DYN_, IPB_, TMA_, CULL_><<<grid, 256, sm, s>>>(                                             \
+    const int64_t pairs = (int64_t)nchunks * n_lists;                                                             \
+    const int64_t persistent = 148 * ((TMA_) ? 2 : 3);                                                            \
+    dim3 grid((unsigned)nchunks, (unsigned)n_lists);                                                              \
+    if (WL_) grid = dim3((unsigned)(pairs < persistent ? pairs : persistent), 1u);                               \
+    if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_, CULL_, WL_>>(sm, ctx->device))) return rc;          \
+    preprocess_kernel<DYN_, IPB_, TMA_, CULL_, WL_><<<grid, 256, sm, s>>>(                                        \
         ga, n_items, list_base, item_base, g, view, proj, campos, tanfov, frame_env, frame_view, pose, num_slots, \
         w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
-        w.bin_count.as<uint32_t>(), use_hist, use_hist ? cta_hist : nullptr);                                     \
+        w.bin_count.as<uint32_t>(), use_hist, use_hist ? cta_hist : nullptr, chunk_mask, nchunks,                 \
+        w.work.as<uint32_t>(), st32 + kWorkCountWord, st32 + kPreTicketWord, w.view_consts.as<uint32_t>());      \
   } while (0)
   const bool cull = g.tile_cull != 0;
   if (dynamic) {
-    if (cull) GSW_LAUNCH_PRE(true, kIpbDynamic, false, true); else GSW_LAUNCH_PRE(true, kIpbDynamic, false, false);
+    if (cull) GSW_LAUNCH_PRE(true, kIpbDynamic, false, true, false);
+    else GSW_LAUNCH_PRE(true, kIpbDynamic, false, false, false);
   } else if (use_tma) {
-    if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, true, true); else GSW_LAUNCH_PRE(false, kIpbStatic, true, false);
+    if (wl) {
+      if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, true, true, true);
+      else GSW_LAUNCH_PRE(false, kIpbStatic, true, false, true);
+    } else {
+      if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, true, true, false);
+      else GSW_LAUNCH_PRE(false, kIpbStatic, true, false, false);
+    }
   } else {
-    if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true); else GSW_LAUNCH_PRE(false, kIpbStatic, false, false);
+    if (wl) {
+      if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true, true);
+      else GSW_LAUNCH_PRE(false, kIpbStatic, false, false, true);
+    } else {
+      if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true, false);
+      else GSW_LAUNCH_PRE(false, kIpbStatic, false, false, false);
+    }
   }
 #undef GSW_LAUNCH_PRE
   if (kept_hist) *kept_hist = use_hist && cta_hist != nullptr;
@@ -1312,16 +1493,21 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 // words of cta_hist one layer needs (0: the bins do not fit a shared-memory histogram, nothing is kept)
 size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g) {
   if (n_items <= 0 || n_lists <= 0 || (size_t)g.T * g.NB * 4 > kMaxHistBytes) return 0;
-  return (size_t)n_lists * (size_t)((n_items + kItemsPerBlock - 1) / kItemsPerBlock) * (size_t)(g.T * g.NB + 1);
+  return (size_t)n_lists * (size_t)layer_chunks(n_items) * (size_t)(g.T * g.NB + 1);
 }
 
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
-                   cudaStream_t s) {
+                   const uint32_t* chunk_mask, cudaStream_t s) {
   if (n_items <= 0 || n_lists <= 0) return 0;
   static_assert(kIpbStatic == kItemsPerBlock && kIpbDynamic == kItemsPerBlock, "cta_hist: same chunks in both passes");
-  dim3 grid((unsigned)((n_items + kItemsPerBlock - 1) / kItemsPerBlock), (unsigned)n_lists);
+  const int32_t nchunks = (int32_t)layer_chunks(n_items);
+  const bool wl = use_work_list(dynamic, ga, n_items, n_lists);
+  const int64_t pairs = (int64_t)nchunks * n_lists, persistent = 148 * 4;
+  dim3 grid((unsigned)nchunks, (unsigned)n_lists);
+  if (wl) grid = dim3((unsigned)(pairs < persistent ? pairs : persistent), 1u);
   auto& w = ctx->ws;
+  uint32_t* const st32 = w.status.as<uint32_t>();
   const size_t hist_b = (size_t)g.T * g.NB * 8;
   const int use_hist = hist_b <= kMaxHistBytes;
   int rc;
@@ -1331,16 +1517,21 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
     KERNEL_<<<grid, 256, (HIST_) ? hist_b : 0, s>>>(                                                              \
         ga, n_items, list_base, item_base, g, w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, \
         w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(), w.bin_cursor.as<uint32_t>(),                               \
-        w.keys.as<unsigned long long>(), cap, (HIST_) ? 1 : 0, CH_);                                              \
+        w.keys.as<unsigned long long>(), cap, (HIST_) ? 1 : 0, CH_, chunk_mask, nchunks, w.work.as<uint32_t>(),   \
+        st32 + kWorkCountWord, st32 + kScatterTicketWord);                                                        \
   } while (0)
+#define GSW_COMMA ,
   if (g.tile_cull != 0) {  // the culling form has no counting pass of its own: shared counters need cta_hist
     const bool h = use_hist && cta_hist != nullptr;
-    if (dynamic) GSW_LAUNCH_SCATTER(scatter_cull_kernel<true>, h, cta_hist);
-    else GSW_LAUNCH_SCATTER(scatter_cull_kernel<false>, h, cta_hist);
+    if (dynamic) GSW_LAUNCH_SCATTER(scatter_cull_kernel<true GSW_COMMA false>, h, cta_hist);
+    else if (wl) GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA true>, h, cta_hist);
+    else GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA false>, h, cta_hist);
   } else {
-    if (dynamic) GSW_LAUNCH_SCATTER(scatter_kernel<true>, use_hist, cta_hist);
-    else GSW_LAUNCH_SCATTER(scatter_kernel<false>, use_hist, cta_hist);
+    if (dynamic) GSW_LAUNCH_SCATTER(scatter_kernel<true GSW_COMMA false>, use_hist, cta_hist);
+    else if (wl) GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA true>, use_hist, cta_hist);
+    else GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA false>, use_hist, cta_hist);
   }
+#undef GSW_COMMA
 #undef GSW_LAUNCH_SCATTER
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
@@ -1354,8 +1545,8 @@ int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_
   if (L.N <= 0) return 0;
   frame_attrs_kernel<<<(unsigned)((L.N + 255) / 256), 256, 0, s>>>(
       L.N, L.Ns, L.Nm, L.V, frame, L.frame_view, L.slot_orig, L.pos_of, L.g, w.rec.as<float4>(),
-      w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(), radii, tiles_touched, depth, xy,
-      conic_opacity, rgb);
+      w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.chunk_mask.as<uint32_t>(), radii,
+      tiles_touched, depth, xy, conic_opacity, rgb);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
@@ -1367,7 +1558,7 @@ int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s) {
   if (L.N <= 0 || L.F <= 0) return 0;
   dim3 grid((unsigned)((L.N + 255) / 256), (unsigned)L.F);
   radii_kernel<<<grid, 256, 0, s>>>(L.N, L.Ns, L.Nm, L.V, L.frame_view, L.slot_orig, L.pos_of, w.rad.as<int32_t>(),
-                                    out_radii);
+                                    w.chunk_mask.as<uint32_t>(), out_radii);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

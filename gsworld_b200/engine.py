@@ -286,6 +286,12 @@ class Engine:
         _lib.check(self.lib.gsw_profile_read(self._h, buf, 8))
         return {k: float(buf[i]) for i, k in enumerate(self.STAGES)}
 
+    def counters(self):
+        """Work counters of the last launch: blend pair evaluations, entries staged."""
+        buf = (C.c_int64 * 3)()
+        _lib.check(self.lib.gsw_profile_counters(self._h, buf, 3))
+        return {"blend_pairs": int(buf[0]), "blend_staged": int(buf[1]), "static_chunks_live": int(buf[2])}
+
     def kernel_launches(self) -> int:
         return int(self.lib.gsw_kernel_launches())
 

@@ -13,7 +13,8 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libgsw_oracle.so")
+# GSW_ORACLE_LIB: an alternative build of gsw_oracle.cpp (tools/fma_audit.py compares a contracted build with this one)
+_LIB_PATH = os.environ.get("GSW_ORACLE_LIB") or os.path.join(_HERE, "libgsw_oracle.so")
 _lib = None
 
 NEAR_GSWORLD = 0.05  # reference README.md:33 (hand patch of auxiliary.h)

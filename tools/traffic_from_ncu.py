@@ -13,7 +13,7 @@ uR, uW = rows[1][iR], rows[1][iW]
 scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 stage_of = (("preprocess_kernel<0", "preprocess_static"), ("preprocess_kernel<(bool)0", "preprocess_static"),
             ("preprocess_kernel<1", "preprocess_dynamic"), ("preprocess_kernel<(bool)1", "preprocess_dynamic"),
-            ("scan_", "scan"), ("scatter_kernel", "scatter"), ("classify_bins", "sort"), ("refine_big_bins", "sort"),
+            ("scan_", "scan"), ("scatter_", "scatter"), ("cull_chunks", "preprocess_static"), ("classify_bins", "sort"), ("refine_big_bins", "sort"),
             ("sort_segments", "sort"), ("count_view_frames", "sort"), ("gather_splats", "gather"),
             ("blend_kernel", "blend"))
 acc = {}
