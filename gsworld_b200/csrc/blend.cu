@@ -17,6 +17,8 @@
 // Here exp(power) is evaluated as 2^(power*log2 e) with the conic pre-scaled at gather time (binsort.cu);
 // colour / inverse depth are tolerance quantities (max-abs 1e-3).
 // uint8 epilogue: gs_world_wrapper.py:268-270 after render()'s clamp(0,1) (gaussian_renderer/__init__.py:119).
+#include <cstdlib>
+
 #include "gsw_internal.h"
 
 namespace gsw {
@@ -54,7 +56,45 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, uint32_t v) {
   asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v));
 }
 
-template <bool SEG>
+// ---- packed fp32x2 arithmetic (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot for two pixels.  An operand built with
+// bc() (both halves the same scalar) costs no extra instruction: ptxas uses the single-register broadcast form.
+typedef unsigned long long f2;
+__device__ __forceinline__ f2 pk(float lo, float hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ f2 bc(float v) { return pk(v, v); }
+__device__ __forceinline__ float lo_of(f2 v) {
+  float a, b;
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+  return a;
+}
+__device__ __forceinline__ float hi_of(f2 v) {
+  float a, b;
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+  return b;
+}
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+  f2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+  f2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+  f2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
+// PPT = pixels per thread.  1: 256 threads, a warp owns an 8x4 pixel block.  2: 128 threads, a warp owns an 8x8
+// block and every lane the pixels (x, y) and (x, y + 4); the per-pixel arithmetic then runs on packed fp32x2
+// instructions and the record loads / queue reads are paid once for two pixels.
+template <bool SEG, int PPT>
 __device__ __forceinline__ void
 blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
              int32_t f_begin,
@@ -78,7 +118,8 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   // bits, computed once instead of once per env.
   __shared__ float4 sRec[kChunk * 3];                  // staged records, 48 B each: {a, b, c}
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
-  __shared__ uint8_t sQ[8][kChunk];                    // per-warp queue of staged records that touch its pixels
+  constexpr int NT = 256 / PPT, NW = 8 / PPT;          // threads, warps per CTA
+  __shared__ uint8_t sQ[NW][kChunk];                   // per-warp queue of staged records that touch its pixels
   __shared__ int32_t sLab[SEG ? kChunk : 1];
   __shared__ uint32_t sPairs[8];  // per warp: records it ran the per-pixel blend for (x 32 pixels = pair evaluations)
   // 32-bit unsigned division (the grid is f-major: blockIdx.x = (f - f_begin) * T + tile)
@@ -86,11 +127,12 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   const int f = f_begin + (int)fl, tile = (int)(blockIdx.x - fl * (uint32_t)g.T);
   const int tx = tile % g.gx, ty = tile / g.gx;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int wx = tx * kTile + (w & 1) * 8, wy = ty * kTile + (w >> 1) * 4;
-  const int px = wx + (lane & 7), py = wy + (lane >> 3);
+  const int wx = tx * kTile + (w & 1) * 8, wy = ty * kTile + (w >> 1) * 4 * PPT;
+  const int px = wx + (lane & 7), py = wy + (lane >> 3);  // PPT == 2: second pixel at (px, py + 4)
   const bool inside = px < g.W && py < g.H;
+  const bool inside1 = PPT == 2 && px < g.W && py + 4 < g.H;
   const float pxf = (float)px, pyf = (float)py;
-  const float bx0 = (float)wx, bx1 = (float)(wx + 7), by0 = (float)wy, by1 = (float)(wy + 3);
+  const float bx0 = (float)wx, bx1 = (float)(wx + 7), by0 = (float)wy, by1 = (float)(wy + 4 * PPT - 1);
 
   const int v = mode == 1 ? f : (frame_view ? frame_view[f] : 0);
   if (mode == 1 && view_cnt[v] < 2u) return;  // view used by a single frame: nothing to share
@@ -109,8 +151,10 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   constexpr bool lazyD = true;  // dynamic lists are never materialised
   const int64_t itemA = (int64_t)v * Ns, itemD = (int64_t)V * Ns + (int64_t)f * Nm;
   if (mode == 0 && use_view_images && nd == 0 && view_cnt[v] >= 2u) {  // static-only tile of a shared view
-    if (inside) {
-      const size_t HW = (size_t)g.H * g.W, pid = (size_t)py * g.W + px;
+#pragma unroll
+    for (int q = 0; q < PPT; ++q)
+    if (q == 0 ? inside : inside1) {
+      const size_t HW = (size_t)g.H * g.W, pid = (size_t)(py + 4 * q) * g.W + px;
       if (out_u8) {
         const uint8_t* src = st_u8 + ((size_t)v * HW + pid) * 3;
         uint8_t* o = out_u8 + ((size_t)f * HW + pid) * 3;
@@ -141,46 +185,56 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   float Tacc = inside ? 1.0f : 0.0f, Tout = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, invd = 0.f;
   float best_w = 0.f;
   int32_t best_lab = GSW_SEG_NONE;
+  // PPT == 2: the same state for both pixels, packed {pixel 0, pixel 1}
+  // Its transmittance is sign-coded: T > 0 while the pixel is live, -T (the value the reference writes out) once it
+  // has saturated, so that T (1 - alpha) < 1e-4 holds for every later record without a second state variable.
+  f2 T2 = pk(inside ? 1.0f : -1.0f, inside1 ? 1.0f : -1.0f), C0_2 = 0ull, C1_2 = 0ull, C2_2 = 0ull, invd2 = 0ull;
+  const f2 npy2 = pk(-pyf, -(pyf + 4.0f));
+  float best_w1 = 0.f;
+  int32_t best_lab1 = GSW_SEG_NONE;
+  auto all_done = [&]() -> bool {
+    return PPT == 1 ? Tacc == 0.0f : (T2 & 0x8000000080000000ull) == 0x8000000080000000ull;  // both saturated
+  };
   uint32_t base = 0;
   if (threadIdx.x < 8) sPairs[threadIdx.x] = 0u;  // (the first barrier of the loop orders this before any update)
   for (; base < total; base += kChunk) {
-    if (__syncthreads_and(Tacc == 0.0f)) break;  // also protects the staging buffers of the previous round
+    if (__syncthreads_and(all_done())) break;  // also protects the staging buffers of the previous round
     const uint32_t n = min((uint32_t)kChunk, total - base);
     const uint32_t rs = ns - i0, rd = nd - j0;
     if (rs == 0 || rd == 0) {  // single-stream chunk
       const uint32_t src = rd == 0 ? s0 + i0 : d0 + j0;
-      if (threadIdx.x < n) {
+      for (uint32_t t = threadIdx.x; t < n; t += NT) {
         if (rd == 0 ? lazyA : lazyD) {
-          const uint32_t idx = (uint32_t)(keys[src + threadIdx.x] & 0xffffffffull);
+          const uint32_t idx = (uint32_t)(keys[src + t] & 0xffffffffull);
           const Splat sp = make_splat(rec, (rd == 0 ? itemA : itemD) + (pos_of ? (int64_t)pos_of[idx] : (int64_t)idx));
-          sRec[3 * threadIdx.x] = sp.a;
-          sRec[3 * threadIdx.x + 1] = sp.b;
-          sRec[3 * threadIdx.x + 2] = sp.c;
-          if (SEG) sLab[threadIdx.x] = labels[idx];
+          sRec[3 * t] = sp.a;
+          sRec[3 * t + 1] = sp.b;
+          sRec[3 * t + 2] = sp.c;
+          if (SEG) sLab[t] = labels[idx];
         } else {
-          const Splat* sp = splats + src + threadIdx.x;
-          sRec[3 * threadIdx.x] = __ldg(&sp->a);
-          sRec[3 * threadIdx.x + 1] = __ldg(&sp->b);
-          sRec[3 * threadIdx.x + 2] = __ldg(&sp->c);
-          if (SEG) sLab[threadIdx.x] = lab_stream[src + threadIdx.x];
+          const Splat* sp = splats + src + t;
+          sRec[3 * t] = __ldg(&sp->a);
+          sRec[3 * t + 1] = __ldg(&sp->b);
+          sRec[3 * t + 2] = __ldg(&sp->c);
+          if (SEG) sLab[t] = lab_stream[src + t];
         }
       }
       if (rd == 0) i0 += n; else j0 += n;
     } else {  // merge-path over two key windows
       const uint32_t ws = min((uint32_t)kChunk, rs), wd = min((uint32_t)kChunk, rd);
-      if (threadIdx.x < ws) kS[threadIdx.x] = keys[s0 + i0 + threadIdx.x];
-      if (threadIdx.x < wd) kD[threadIdx.x] = keys[d0 + j0 + threadIdx.x];
+      for (uint32_t t = threadIdx.x; t < ws; t += NT) kS[t] = keys[s0 + i0 + t];
+      for (uint32_t t = threadIdx.x; t < wd; t += NT) kD[t] = keys[d0 + j0 + t];
       __syncthreads();
-      bool take_s = false;
-      if (threadIdx.x < n) {
-        const uint32_t t = threadIdx.x;
+      uint32_t took_s = 0;
+      for (uint32_t t = threadIdx.x; t < n; t += NT) {
         uint32_t lo = t > wd ? t - wd : 0u, hi = min(t, ws);
         while (lo < hi) {
           const uint32_t mid = (lo + hi) >> 1;
           if (kS[mid] < kD[t - 1 - mid]) lo = mid + 1; else hi = mid;
         }
         const uint32_t a = lo, b = t - lo;
-        take_s = a < ws && (b >= wd || kS[a] < kD[b]);
+        const bool take_s = a < ws && (b >= wd || kS[a] < kD[b]);
+        took_s += take_s ? 1u : 0u;
         const uint32_t pos = take_s ? s0 + i0 + a : d0 + j0 + b;
         if (take_s ? lazyA : lazyD) {
           const uint32_t idx = (uint32_t)((take_s ? kS[a] : kD[b]) & 0xffffffffull);
@@ -197,12 +251,13 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
           if (SEG) sLab[t] = lab_stream[pos];
         }
       }
-      const uint32_t cs = (uint32_t)__syncthreads_count(take_s);
+      uint32_t cs = (uint32_t)__syncthreads_count(took_s >= 1u);
+      if (PPT == 2) cs += (uint32_t)__syncthreads_count(took_s >= 2u);
       i0 += cs;
       j0 += n - cs;
     }
     __syncthreads();
-    if (__all_sync(0xffffffffu, Tacc == 0.0f)) continue;
+    if (__all_sync(0xffffffffu, all_done())) continue;
 
     // ---- cull: one staged record per lane against this warp's 8x4 pixel block; hits go to the warp's queue.
     // Stage 1: bounding box of the alpha >= 1/255 footprint.  Stage 2 (box hits only): the exact maximum of
@@ -235,15 +290,54 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
 
     // ---- blend the queued records in list order ----
     for (uint32_t k0 = 0; k0 < cnt; k0 += 16) {
-      if (k0 && __all_sync(0xffffffffu, Tacc == 0.0f)) break;
+      if (k0 && __all_sync(0xffffffffu, all_done())) break;
       const uint32_t kend = min(cnt, k0 + 16);
-      if (lane == 0) sPairs[w] += kend - k0;  // kept in shared memory: the loop has no register to spare
+      if (lane == 0) sPairs[w] += (kend - k0) * PPT;  // kept in shared memory: the loop has no register to spare
 #pragma unroll 4
       for (uint32_t k = k0; k < kend; ++k) {
         const uint32_t qi = lds_u8(aQ + k);
         const uint32_t ra = aRec + qi * 48;
         const float2 xy = lds64(ra);
         const float4 b = lds128(ra + 16);
+        if (PPT == 2) {
+          // two pixels of one column: dx is shared, everything that depends on dy is packed
+          const float4 c = lds128(ra + 32);
+          const float dx = xy.x - pxf;
+          const f2 dy = add2(bc(xy.y), npy2);
+          const f2 t = fma2(bc(b.y), dy, bc(b.x * dx));
+          const f2 u = mul2(mul2(bc(b.z), dy), dy);
+          const f2 p2 = fma2(bc(dx), t, u);  // power * log2(e)
+          const float p20 = lo_of(p2), p21 = hi_of(p2);
+          f2 al = mul2(bc(b.w), pk(ex2_approx(p20), ex2_approx(p21)));
+          float a0 = fminf(0.99f, lo_of(al)), a1 = fminf(0.99f, hi_of(al));
+          a0 = ((p20 > 0.0f) || (a0 < 1.0f / 255.0f)) ? 0.0f : a0;  // skipped: alpha 0 leaves T unchanged bit for bit
+          a1 = ((p21 > 0.0f) || (a1 < 1.0f / 255.0f)) ? 0.0f : a1;
+          al = pk(a0, a1);
+          const f2 one_m = add2(bc(1.0f), pk(-a0, -a1));
+          const f2 tt = mul2(T2, one_m);  // T (1 - alpha)
+          const float tt0 = lo_of(tt), tt1 = hi_of(tt);
+          const bool sat0 = tt0 < 0.0001f, sat1 = tt1 < 0.0001f;  // saturated now, or already (T < 0)
+          f2 wg = mul2(al, T2);
+          const float w0 = sat0 ? 0.0f : lo_of(wg), w1 = sat1 ? 0.0f : hi_of(wg);
+          wg = pk(w0, w1);
+          C0_2 = fma2(bc(c.x), wg, C0_2);
+          C1_2 = fma2(bc(c.y), wg, C1_2);
+          C2_2 = fma2(bc(c.z), wg, C2_2);
+          invd2 = fma2(bc(c.w), wg, invd2);
+          if (SEG) {
+            if (w0 > best_w) {
+              best_w = w0;
+              best_lab = sLab[qi];
+            }
+            if (w1 > best_w1) {
+              best_w1 = w1;
+              best_lab1 = sLab[qi];
+            }
+          }
+          // (a skipped record has alpha 0, hence tt == T bit for bit)
+          T2 = pk(sat0 ? -fabsf(lo_of(T2)) : tt0, sat1 ? -fabsf(hi_of(T2)) : tt1);
+          continue;
+        }
         const float dx = xy.x - pxf, dy = xy.y - pyf;
         const float p2 = dx * (b.x * dx + b.y * dy) + (b.z * dy) * dy;  // power * log2(e)
         // Branch-free form of the reference's three tests (power > 0 -> skip; alpha < 1/255 -> skip;
@@ -282,23 +376,34 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
     atomicAdd((unsigned long long*)&status[4], 32ull * ev);
   }
 
-  if (inside) {
-    if (bg_dev) {
-      bg0 = bg_dev[0];
-      bg1 = bg_dev[1];
-      bg2 = bg_dev[2];
+  if (bg_dev) {
+    bg0 = bg_dev[0];
+    bg1 = bg_dev[1];
+    bg2 = bg_dev[2];
+  }
+#pragma unroll
+  for (int q = 0; q < PPT; ++q) {
+    if (!(q == 0 ? inside : inside1)) continue;
+    float T = Tout, c0 = C0, c1 = C1, c2 = C2, idp = invd;
+    int32_t lab = best_lab;
+    if (PPT == 2) {
+      T = fabsf(q ? hi_of(T2) : lo_of(T2));
+      c0 = q ? hi_of(C0_2) : lo_of(C0_2);
+      c1 = q ? hi_of(C1_2) : lo_of(C1_2);
+      c2 = q ? hi_of(C2_2) : lo_of(C2_2);
+      idp = q ? hi_of(invd2) : lo_of(invd2);
+      lab = q ? best_lab1 : best_lab;
     }
-    const float T = Tout;
-    const float r = C0 + T * bg0, gr = C1 + T * bg1, b = C2 + T * bg2;
-    const size_t HW = (size_t)g.H * g.W, pid = (size_t)py * g.W + px;
+    const float r = c0 + T * bg0, gr = c1 + T * bg1, b = c2 + T * bg2;
+    const size_t HW = (size_t)g.H * g.W, pid = (size_t)(py + 4 * q) * g.W + px;
     if (out_color) {
       float* o = out_color + (size_t)f * 3 * HW + pid;
       o[0] = r;
       o[HW] = gr;
       o[2 * HW] = b;
     }
-    if (out_invd) out_invd[(size_t)f * HW + pid] = invd;
-    if (SEG && out_seg) out_seg[(size_t)f * HW + pid] = best_lab;
+    if (out_invd) out_invd[(size_t)f * HW + pid] = idp;
+    if (SEG && out_seg) out_seg[(size_t)f * HW + pid] = lab;
     if (out_u8) {
       uint8_t* o = out_u8 + ((size_t)f * HW + pid) * 3;
       o[0] = (uint8_t)(fminf(fmaxf(r, 0.f), 1.f) * 255.f);
@@ -309,8 +414,8 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
 }
 
 // The kernel proper: blend_body, then (delivery to the host only) the group-completion signal.
-template <bool SEG>
-__global__ void __launch_bounds__(256, 5)  // 48 registers: five CTAs per SM
+template <bool SEG, int PPT>
+__global__ void __launch_bounds__(256 / PPT, PPT == 1 ? 5 : 8)  // 48 / 64 registers: 40 / 32 warps per SM
 blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
              int32_t f_begin, const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats,
              int64_t cap, FrameGeom g, float bg0, float bg1, float bg2, const float* __restrict__ bg_dev,
@@ -321,7 +426,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              const int32_t* __restrict__ st_seg, int use_view_images, const float4* __restrict__ rec,
              const int32_t* __restrict__ pos_of, int64_t Ns, const int32_t* __restrict__ labels, int64_t Nm,
              DoneSig sig) {
-  blend_body<SEG>(bin_off, nbins, frame_view, V, f_begin, keys, splats, cap, g, bg0, bg1, bg2, bg_dev, out_u8,
+  blend_body<SEG, PPT>(bin_off, nbins, frame_view, V, f_begin, keys, splats, cap, g, bg0, bg1, bg2, bg_dev, out_u8,
                   out_color, out_invd, status, mode, view_cnt, st_u8, st_color, st_invd, lab_stream, out_seg, st_seg,
                   use_view_images, rec, pos_of, Ns, labels, Nm);
   if (sig.cnt != nullptr) {
@@ -355,6 +460,16 @@ __global__ void count_view_frames_kernel(int32_t F, const int32_t* __restrict__ 
 
 }  // namespace
 
+// Pixels per thread of the blend kernel (see blend_body).  GSW_BLEND_PPT=1 selects the one-pixel form (A/B aid); the
+// view pass and the frame pass of a launch set always use the same form, so shared static tiles stay bit-identical.
+static int blend_ppt() {
+  static const int v = [] {
+    const char* e = getenv("GSW_BLEND_PPT");
+    return (e != nullptr && e[0] == '1') ? 1 : 2;
+  }();
+  return v;
+}
+
 // Static-tile sharing set-up: counts frames per view and renders the static-only image of every view that is
 // shared by >= 2 frames (mode 1).  Buffers live in the workspace; call before launch_blend when F > V.
 // frames per view (view_cnt): decides which static lists are shared (materialised once, tiles re-used) and
@@ -373,18 +488,19 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
                            bool want_invd, bool want_seg, cudaStream_t s) {
   auto& w = ctx->ws;
   (void)F;
-#define GSW_VIEW_PASS(SEG_)                                                                                      \
-  blend_kernel<SEG_><<<(unsigned)((int64_t)V * g.T), 256, 0, s>>>(                                                 \
+#define GSW_VIEW_PASS(SEG_, PPT_)                                                                                \
+  blend_kernel<SEG_, PPT_><<<(unsigned)((int64_t)V * g.T), 256 / PPT_, 0, s>>>(                                    \
       w.bin_off.as<uint32_t>(), nbins, frame_view, V, 0, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), cap, g, \
       bg[0], bg[1], bg[2], nullptr, want_u8 ? w.st_u8.as<uint8_t>() : nullptr,                                      \
       want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
       w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
       want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr, 0, w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns,    \
       ctx->labels, ctx->last.Nm, DoneSig{})
-  if (want_seg)
-    GSW_VIEW_PASS(true);
-  else
-    GSW_VIEW_PASS(false);
+  if (blend_ppt() == 2) {
+    if (want_seg) GSW_VIEW_PASS(true, 2); else GSW_VIEW_PASS(false, 2);
+  } else {
+    if (want_seg) GSW_VIEW_PASS(true, 1); else GSW_VIEW_PASS(false, 1);
+  }
 #undef GSW_VIEW_PASS
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
@@ -401,17 +517,18 @@ int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int6
   if (FT <= 0) return 0;
   auto& w = ctx->ws;
   const DoneSig sg = sig ? *sig : DoneSig{};
-#define GSW_BLEND(SEG_)                                                                                            \
-  blend_kernel<SEG_><<<(unsigned)FT, 256, 0, s>>>(                                                                   \
+#define GSW_BLEND(SEG_, PPT_)                                                                                      \
+  blend_kernel<SEG_, PPT_><<<(unsigned)FT, 256 / PPT_, 0, s>>>(                                                      \
       w.bin_off.as<uint32_t>(), nbins, frame_view, V, f_begin, w.keys.as<unsigned long long>(), w.splats.as<Splat>(), \
       cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
       w.status.as<long long>(), 0, w.view_cnt.as<uint32_t>(), w.st_u8.as<uint8_t>(), w.st_color.as<float>(),          \
       w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>(), share ? 1 : 0,              \
       w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm, sg)
-  if (out_seg)
-    GSW_BLEND(true);
-  else
-    GSW_BLEND(false);
+  if (blend_ppt() == 2) {
+    if (out_seg) GSW_BLEND(true, 2); else GSW_BLEND(false, 2);
+  } else {
+    if (out_seg) GSW_BLEND(true, 1); else GSW_BLEND(false, 1);
+  }
 #undef GSW_BLEND
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
