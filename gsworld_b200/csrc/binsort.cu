@@ -590,16 +590,21 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, i
   }
   refine_big_bins_kernel<<<148 * 2, 512, 0, ss>>>(Q, w.keys.as<unsigned long long>(), w.splats.as<Splat>(),
                                                   w.status.as<long long>());
+  if (ss != s) GSW_CUDA(cudaEventRecord(ctx->join_evt, ss));  // the medium / mid queues are complete
+  // side stream: the medium class right behind the refinement; main stream: the small class, then (once the
+  // refinement is done) the mid class.  The classes touch disjoint key ranges and each of them alone ends in a
+  // tail of half-empty SMs, so they run next to each other.
+  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 4, 256, smem_m, ss>>>(Q.q[1], Q.count + 1, Q.cap[1],
+                                                                         w.keys.as<unsigned long long>(), ticket);
   sort_segments_kernel<kSmallKeys, 64><<<148 * 16, 64, smem_s, s>>>(Q.q[0], Q.count, Q.cap[0],
                                                                       w.keys.as<unsigned long long>(), ticket + 1);
-  if (ss != s) {
-    GSW_CUDA(cudaEventRecord(ctx->join_evt, ss));
-    GSW_CUDA(cudaStreamWaitEvent(s, ctx->join_evt, 0));
-  }
-  sort_segments_kernel<kSortSmemKeys, 256><<<148 * 4, 256, smem_m, s>>>(Q.q[1], Q.count + 1, Q.cap[1],
-                                                                        w.keys.as<unsigned long long>(), ticket);
+  if (ss != s) GSW_CUDA(cudaStreamWaitEvent(s, ctx->join_evt, 0));
   sort_segments_kernel<kMidKeys, 128><<<148 * 8, 128, 2 * smem_s, s>>>(Q.q[3], Q.count + 3, Q.cap[3],
                                                                       w.keys.as<unsigned long long>(), ticket + 2);
+  if (ss != s) {
+    GSW_CUDA(cudaEventRecord(ctx->fork_evt, ss));
+    GSW_CUDA(cudaStreamWaitEvent(s, ctx->fork_evt, 0));
+  }
   count_launches(5);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -66,13 +66,13 @@ __device__ __forceinline__ f2 pk(float lo, float hi) {
 }
 __device__ __forceinline__ f2 bc(float v) { return pk(v, v); }
 __device__ __forceinline__ float lo_of(f2 v) {
-  float a, b;
-  asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+  float a;
+  asm("mov.b64 {%0,_}, %1;" : "=f"(a) : "l"(v));
   return a;
 }
 __device__ __forceinline__ float hi_of(f2 v) {
-  float a, b;
-  asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+  float b;
+  asm("mov.b64 {_,%0}, %1;" : "=f"(b) : "l"(v));
   return b;
 }
 __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {

@@ -79,7 +79,7 @@ __device__ __forceinline__ Rect tile_rect(float px, float py, int radius, int gx
 // it conservative against ex2.approx / FMA differences in the blend; any NaN keeps the entry.
 struct Foot {
   float px, py, hx, hy;  // centre (pixels), half extents of the alpha >= 1/255 box (-1: never visible, 3e38: unknown)
-  float A, B, C;         // conic: power = -0.5 (A dx^2 + C dy^2) - B dx dy
+  float A, B, C;         // pre-scaled conic (-0.5 A, -B, -0.5 C): power = A dx^2 + B dx dy + C dy^2
   float kyx, kxy;        // -B/C, -B/A: the y (x) that maximises the power on a line of fixed x (y)
   float t;               // ln(255 opacity) with margin: entries with max power < -t are dead
 };
@@ -88,7 +88,7 @@ struct Foot {
 __device__ __forceinline__ Foot make_foot(float px, float py, float hx, float hy, float A, float B, float C,
                                           float opac) {
   Foot f;
-  f.px = px; f.py = py; f.hx = hx; f.hy = hy; f.A = A; f.B = B; f.C = C;
+  f.px = px; f.py = py; f.hx = hx; f.hy = hy; f.A = -0.5f * A; f.B = -B; f.C = -0.5f * C;
   f.kyx = -B / C;
   f.kxy = -B / A;
   f.t = logf(255.0f * opac) * 1.002f + 0.02f;
@@ -104,8 +104,10 @@ __device__ __forceinline__ bool tile_alive(const Foot& f, int tx, int ty) {
   const float xe = fminf(fmaxf(0.f, x0), x1), ye = fminf(fmaxf(0.f, y0), y1);
   const float ys = fminf(fmaxf(f.kyx * xe, y0), y1);
   const float xs = fminf(fmaxf(f.kxy * ye, x0), x1);
-  const float p1 = -0.5f * (f.A * xe * xe + f.C * ys * ys) - f.B * xe * ys;
-  const float p2 = -0.5f * (f.A * xs * xs + f.C * ye * ye) - f.B * xs * ye;
+  // (not a parity quantity: explicit FMAs although the file is built with -fmad=false; the preprocess and the
+  // scatter pass run this very code on the same bits, so they always agree)
+  const float p1 = fmaf(xe, fmaf(f.A, xe, f.B * ys), (f.C * ys) * ys);
+  const float p2 = fmaf(xs, fmaf(f.A, xs, f.B * ye), (f.C * ye) * ye);
   return !(fmaxf(p1, p2) < -f.t);
 }
 
@@ -138,6 +140,7 @@ __device__ __forceinline__ uint32_t depth_bucket(float depth, const FrameGeom& g
 struct ViewSmem {
   float V[16], P[16], cam[3], tanx, tany;
   float wnorm;  // upper bound on the squared spectral norm of the view matrix's 3x3 block (1 for a rigid camera)
+  float focal_x, focal_y;  // W / (2 tanx), H / (2 tany): the same expressions the per-item code used to evaluate
 };
 
 // One colour channel of the degree<=3 SH polynomial, same association as the published kernel.
@@ -248,8 +251,7 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   const float px = ndc2pix(ppx, g.W), py = ndc2pix(ppy, g.H);
 
   // ---- Jacobian of the projection (EWA) ----
-  const float focal_y = (float)g.H / (2.0f * vs.tany);
-  const float focal_x = (float)g.W / (2.0f * vs.tanx);
+  const float focal_y = vs.focal_y, focal_x = vs.focal_x;
   float tx = pvx, ty = pvy;
   const float tz = pvz;
   {
@@ -481,7 +483,11 @@ __device__ __forceinline__ unsigned long long warp_cull_count(const Rect rc, uin
   const int w = rc.x1 - rc.x0;
   const Rect q = alive_rect(ft, rc);
   const int qw = q.x1 - q.x0, n = qw * (q.y1 - q.y0);
-  unsigned long long mask = 0ull;
+  uint32_t mlo = 0u, mhi = 0u;  // the 64-bit mask as two words (64-bit shifts are several instructions each)
+  auto set_bit = [](uint32_t& lo, uint32_t& hi, int bit) {
+    if (bit < 32) lo |= 1u << bit;
+    else if (bit < 64) hi |= 1u << (bit - 32);
+  };
   // neighbours in Morton order have similar footprints, so per-thread loops stay balanced up to a full warp's
   // worth of tiles; the broadcast of a whole Foot only pays beyond that
   const bool coop = n > kCoopTilesCull;
@@ -491,7 +497,7 @@ __device__ __forceinline__ unsigned long long warp_cull_count(const Rect rc, uin
         if (tile_alive(ft, x, y)) {
           f((uint32_t)(y * gx + x) * (uint32_t)NB + bk);
           const int bit = (y - rc.y0) * w + (x - rc.x0);
-          if (bit < 64) mask |= 1ull << bit;
+          set_bit(mlo, mhi, bit);
         }
   }
   unsigned m = __ballot_sync(0xffffffffu, coop);
@@ -510,25 +516,27 @@ __device__ __forceinline__ unsigned long long warp_cull_count(const Rect rc, uin
     fs.A = __shfl_sync(0xffffffffu, ft.A, src);   fs.B = __shfl_sync(0xffffffffu, ft.B, src);
     fs.C = __shfl_sync(0xffffffffu, ft.C, src);   fs.t = __shfl_sync(0xffffffffu, ft.t, src);
     fs.kyx = __shfl_sync(0xffffffffu, ft.kyx, src); fs.kxy = __shfl_sync(0xffffffffu, ft.kxy, src);
-    unsigned long long mine = 0ull;  // alive tiles this lane found, as bits of the owner's mask
+    uint32_t lo = 0u, hi = 0u;  // alive tiles this lane found, as bits of the owner's mask
     for (int t = lane; t < nn; t += 32) {
       const int dy = t / ww;
       const int x = x0 + (t - dy * ww), y = y0 + dy;
       if (tile_alive(fs, x, y)) {
         f((uint32_t)(y * gx + x) * (uint32_t)NB + b);
         const int bit = (y - ry0) * rw + (x - rx0);
-        if (bit < 64) mine |= 1ull << bit;
+        set_bit(lo, hi, bit);
       }
     }
-    uint32_t lo = (uint32_t)mine, hi = (uint32_t)(mine >> 32);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       lo |= __shfl_xor_sync(0xffffffffu, lo, o);
       hi |= __shfl_xor_sync(0xffffffffu, hi, o);
     }
-    if (lane == src) mask = ((unsigned long long)hi << 32) | lo;
+    if (lane == src) {
+      mlo = lo;
+      mhi = hi;
+    }
   }
-  return mask;
+  return ((unsigned long long)mhi << 32) | mlo;
 }
 
 // ---- group-level frustum culling ----
@@ -624,7 +632,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
 struct ViewConsts {
   ViewSmem vs;
   ViewCull vc;
-  float pad[2];
 };
 static_assert(sizeof(ViewConsts) == 48 * 4, "ViewConsts: 48 words");
 constexpr int kViewConstWords = 48;
@@ -643,6 +650,10 @@ __device__ __forceinline__ void compute_view_consts(int view, const FrameGeom& g
     vs.tanx = tanfov[view * 2];
   } else if (threadIdx.x == 20) {
     vs.tany = tanfov[view * 2 + 1];
+  } else if (threadIdx.x == 21) {
+    vs.focal_x = (float)g.W / (2.0f * tanfov[view * 2]);
+  } else if (threadIdx.x == 22) {
+    vs.focal_y = (float)g.H / (2.0f * tanfov[view * 2 + 1]);
   } else if (threadIdx.x == 32) {  // Gershgorin bound on the largest eigenvalue of W^T W (W = view 3x3 block)
     const float* Vg = views + view * 16;
     float w[3][3];
