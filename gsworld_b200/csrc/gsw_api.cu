@@ -186,10 +186,28 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
                               pose, num_slots, ch_s, mask_s, &kept_s, ss)))
     return rc;
   mark(1);
-  if (dyn && Nm > 0)
+  // dynamic layer: CTAs are dispatched heaviest chunk first.  The preprocess pass takes the order of the previous
+  // step (same frame / chunk count), the scatter pass the order made from this step's own weights.
+  const int64_t n_dyn_ctas = (dyn && Nm > 0) ? (int64_t)cm_d : 0;
+  const bool use_order = n_dyn_ctas > 1 && n_dyn_ctas <= (1 << 20) && chd > 0 && getenv("GSW_NO_ORDER") == nullptr;
+  if (use_order &&
+      ((rc = w.dyn_cost.reserve((size_t)n_dyn_ctas * 4)) || (rc = w.dyn_order.reserve((size_t)n_dyn_ctas * 4))))
+    return rc;
+  const uint32_t* prev_order = (use_order && ctx->dyn_order_n == n_dyn_ctas) ? w.dyn_order.as<uint32_t>() : nullptr;
+  bool have_order = false;
+  if (dyn && Nm > 0) {
     if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, view, proj, campos, tanfov, frame_env,
-                                frame_view, pose, num_slots, ch_d, mask_d, &kept_d, s)))
+                                frame_view, pose, num_slots, ch_d, mask_d, &kept_d, s, prev_order,
+                                use_order ? w.dyn_cost.as<uint32_t>() : nullptr)))
       return rc;
+    if (use_order && kept_d) {
+      if ((rc = launch_order_chunks(w.dyn_cost.as<uint32_t>(), n_dyn_ctas, w.dyn_order.as<uint32_t>(), s))) return rc;
+      ctx->dyn_order_n = n_dyn_ctas;
+      have_order = true;
+    } else {
+      ctx->dyn_order_n = 0;
+    }
+  }
   if ((rc = join())) return rc;
   mark(2);
   if ((rc = launch_scan_u32(w.bin_count.as<uint32_t>(), w.bin_off.as<uint32_t>(), nbins, w.scan_tmp.as<uint32_t>(),
@@ -199,7 +217,8 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = fork())) return rc;
   if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, mask_s, ss))) return rc;
   if (dyn && Nm > 0)
-    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, mask_d, s)))
+    if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, mask_d, s,
+                             have_order ? w.dyn_order.as<uint32_t>() : nullptr)))
       return rc;
   if ((rc = join())) return rc;
   mark(4);
@@ -301,7 +320,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.chunk_mask, &w.work, &w.view_consts, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.chunk_mask, &w.work, &w.view_consts, &w.dyn_cost, &w.dyn_order, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
@@ -342,6 +361,7 @@ int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_ac
   Guard gd(c->device);
   cudaStream_t s = (cudaStream_t)stream;
   c->have_scene = false;
+  c->dyn_order_n = 0;
   c->last.valid = false;
   c->N = N;
   c->num_slots = num_slots;

@@ -131,6 +131,9 @@ struct Workspace {
   DevBuf chunk_mask;
   DevBuf work;         // u32 (view << 16 | chunk): live (view, chunk) pairs of the static layer, cull_chunks_kernel
   DevBuf view_consts;  // 48 words per view: ViewSmem + ViewCull, written by cull_chunks_kernel
+  // dynamic layer: weight (tile entries) of every (frame, chunk) CTA of the last launch and the dispatch order made
+  // from it (order_chunks_kernel); the order outlives the launch: the next step's preprocess uses it
+  DevBuf dyn_cost, dyn_order;
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -199,6 +202,7 @@ struct gsw_ctx {
   cudaStream_t side_stream = nullptr;
   cudaEvent_t fork_evt = nullptr, join_evt = nullptr;
   int64_t launches = 0;
+  int64_t dyn_order_n = 0;  // number of (frame, chunk) pairs ws.dyn_order is valid for (0: none yet)
 };
 
 namespace gsw {
@@ -209,12 +213,14 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
                       const float* pose, int32_t num_slots, uint32_t* cta_hist, uint32_t* chunk_mask, int* kept_hist,
-                      cudaStream_t s);
+                      cudaStream_t s, const uint32_t* order = nullptr, uint32_t* cost = nullptr);
+// heaviest-first dispatch order of n (list, chunk) CTAs from their weights (tile entries produced)
+int launch_order_chunks(const uint32_t* cost, int64_t n, uint32_t* order, cudaStream_t s);
 size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g);
 int64_t layer_chunks(int64_t n_items);  // 2048-item chunks of a layer (one preprocess / scatter CTA round each)
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
-                   const uint32_t* chunk_mask, cudaStream_t s);
+                   const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order = nullptr);
 int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_t* tiles_touched, float* depth,
                        float* xy, float* conic_opacity, float* rgb, cudaStream_t s);
 int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s);

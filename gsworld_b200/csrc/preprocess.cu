@@ -756,7 +756,8 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
                   uint32_t* __restrict__ bin_count, int use_hist, uint32_t* __restrict__ cta_hist,
                   uint32_t* __restrict__ chunk_mask, int32_t nchunks, const uint32_t* __restrict__ work,
                   const uint32_t* __restrict__ work_count, uint32_t* __restrict__ ticket,
-                  const uint32_t* __restrict__ view_consts) {
+                  const uint32_t* __restrict__ view_consts, const uint32_t* __restrict__ order,
+                  uint32_t* __restrict__ cost) {
   static_assert(!(WL && DYN), "the work-list form is the static layer's");
   constexpr int use_tma = TMA ? 1 : 0;
   __shared__ ViewConsts vcs;
@@ -764,6 +765,8 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
   ViewCull& vc = vcs.vc;
   __shared__ __align__(8) unsigned long long mbar_s;
   __shared__ uint32_t s_work;
+  __shared__ uint32_t s_cost;
+  if (threadIdx.x == 0) s_cost = 0u;  // (cost is only kept by the one-round forms; a barrier follows before its use)
   extern __shared__ __align__(128) unsigned char dsm_raw[];
   constexpr int IPT = IPB / 256;
   const int nbl = g.T * g.NB;
@@ -799,8 +802,11 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
       list = (int)(wv >> 16);
       chunk = (int)(wv & 0xffffu);
     } else {
-      list = blockIdx.y;
-      chunk = blockIdx.x;
+      // DYN: dispatch in the cost order of order_chunks_kernel when there is one (heaviest chunks first)
+      const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;
+      const uint32_t id = (DYN && order != nullptr) ? order[lin] : lin;
+      list = (int)(id / (uint32_t)nchunks);
+      chunk = (int)(id - (uint32_t)list * (uint32_t)nchunks);
     }
     int view = list, env = 0;
     if (DYN) {
@@ -840,6 +846,7 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     if (!WL && chunk_mask != nullptr && threadIdx.x == 0) chunk_mask[chunk_id] = live_mask;
     if (live_mask == 0) {  // nothing of this chunk can reach the image
       if (cta_hist != nullptr && threadIdx.x == 0) cta_hist[chunk_id * (size_t)(nbl + 1)] = 0u;  // scatter skips the chunk
+      if (cost != nullptr && threadIdx.x == 0) cost[chunk_id] = 0u;
       if (WL) continue;
       return;
     }
@@ -913,10 +920,18 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
       // the per-CTA counts are kept for the scatter pass, which walks the same chunk: word 0 = chunk is live
       uint32_t* keep = cta_hist ? cta_hist + chunk_id * (size_t)(nbl + 1) : nullptr;
       if (keep != nullptr && threadIdx.x == 0) keep[0] = 1u;
+      uint32_t mine = 0;
       for (int k = threadIdx.x; k < nbl; k += blockDim.x) {
         const uint32_t c = hist[k];
         if (c) atomicAdd(&bin_count[gb + k], c);
         if (keep != nullptr) keep[1 + k] = c;
+        mine += c;
+      }
+      if (cost != nullptr) {  // tile entries this chunk produced: its weight in the dispatch order (order_chunks_kernel)
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+        if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&s_cost, mine);
+        __syncthreads();
+        if (threadIdx.x == 0) cost[chunk_id] = s_cost;
       }
     }
     if (!WL) break;
@@ -940,10 +955,12 @@ __device__ __forceinline__ int scatter_slot(int it, int t) { return ((t & 7) << 
 template <bool WL>
 __device__ __forceinline__ bool next_chunk(int& list, int& chunk, bool first, const uint32_t* __restrict__ work,
                                            const uint32_t* __restrict__ work_count, uint32_t* __restrict__ ticket,
-                                           uint32_t* s_work) {
+                                           uint32_t* s_work, const uint32_t* __restrict__ order) {
   if (!WL) {
-    list = blockIdx.y;
-    chunk = blockIdx.x;
+    const uint32_t lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const uint32_t id = order != nullptr ? order[lin] : lin;
+    list = (int)(id / gridDim.x);
+    chunk = (int)(id - (uint32_t)list * gridDim.x);
     return first;
   }
   __syncthreads();  // the previous round is done with the shared counters and with s_work
@@ -967,7 +984,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
                unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
                const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
-               uint32_t* __restrict__ ticket) {
+               uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
   extern __shared__ uint32_t dsm[];
   __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
@@ -976,7 +993,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   int list, chunk;
   bool first = true;
 #pragma unroll 1
-  for (; next_chunk<WL>(list, chunk, first, work, work_count, ticket, &s_work); first = false) {
+  for (; next_chunk<WL>(list, chunk, first, work, work_count, ticket, &s_work, order); first = false) {
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
   const int64_t base = (int64_t)chunk * kItemsPerBlock;
   const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
@@ -1075,7 +1092,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
                     unsigned long long* __restrict__ keys, int64_t cap, int use_hist,
                     const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                     const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
-                    uint32_t* __restrict__ ticket) {
+                    uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
   extern __shared__ uint32_t dsm[];
   __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
@@ -1084,7 +1101,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   int list, chunk;
   bool first = true;
 #pragma unroll 1
-  for (; next_chunk<WL>(list, chunk, first, work, work_count, ticket, &s_work); first = false) {
+  for (; next_chunk<WL>(list, chunk, first, work, work_count, ticket, &s_work, order); first = false) {
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
   const int64_t base = (int64_t)chunk * kItemsPerBlock;
   const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
@@ -1114,36 +1131,80 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
     const int64_t i = base + scatter_slot(it, threadIdx.x);
     radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
-  // (loading the 8 items' records ahead of the loop, as the plain scatter does, measured slower here: the loop
-  // is not unrolled, so the batch would live in local memory)
+  // The kernel is bound by the latency of its dependent loads (radius -> record -> key store), not by issue: the
+  // records of item it + 1 are requested before item it is expanded (one item of look-ahead in registers; loading
+  // all 8 ahead, as the plain scatter does, measured slower here: the loop is not unrolled, the batch went to
+  // local memory).
+  struct Pre {
+    float4 a;
+    float2 m;
+    float depth;
+    uint32_t key;
+  };
+  auto fetch = [&](int it) -> Pre {
+    Pre p;
+    p.a = make_float4(0.f, 0.f, 0.f, 0.f);
+    p.m = make_float2(0.f, 0.f);
+    p.depth = 0.f;
+    p.key = 0u;
+    if (it < kItemsPerThread && radius[it] > 0) {
+      const int64_t i = base + scatter_slot(it, threadIdx.x);
+      const int64_t item = item_base + (int64_t)list * n_items + i;
+      p.a = recA[4 * item];
+      p.m = *reinterpret_cast<const float2*>(recA + 4 * item + 3);
+      p.depth = recC[4 * item].w;
+      p.key = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
+    }
+    return p;
+  };
+  Pre nxt = fetch(0);
 #pragma unroll 1
   for (int it = 0; it < kItemsPerThread; ++it) {
     const int64_t i = base + scatter_slot(it, threadIdx.x);
     const int64_t item = item_base + (int64_t)list * n_items + i;
+    const Pre cur = nxt;
+    nxt = fetch(it + 1);
     Rect rc{0, 0, 0, 0};
     uint32_t bk = 0, klo = 0, khi = 0, mlo = 0, mhi = 0;
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 a = cur.a;
     if (radius[it] > 0) {
-      a = recA[4 * item];
-      const float4 d = recA[4 * item + 3];
-      const float depth = recC[4 * item].w;
+      const float depth = cur.depth;
       rc = tile_rect(a.x, a.y, radius[it], g.gx, g.gy);
-      klo = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
+      klo = cur.key;
       khi = __float_as_uint(depth);
       bk = depth_bucket(depth, g);
-      mlo = __float_as_uint(d.x);
-      mhi = __float_as_uint(d.y);
+      mlo = __float_as_uint(cur.m.x);
+      mhi = __float_as_uint(cur.m.y);
     }
     const int w = rc.x1 - rc.x0, n = w * (rc.y1 - rc.y0);
     const bool huge = n > 64;                                          // test again, whole warp
     const bool wide = !huge && __popc(mlo) + __popc(mhi) > kCoopBitsCull;  // walk the mask, whole warp
     if (!huge && !wide) {
-      unsigned long long mask = ((unsigned long long)mhi << 32) | mlo;
-      while (mask) {
-        const int bit = __ffsll((long long)mask) - 1;
-        mask &= mask - 1;
-        const int dy = bit / w;
-        emit((uint32_t)((rc.y0 + dy) * g.gx + rc.x0 + (bit - dy * w)) * (uint32_t)g.NB + bk, klo, khi);
+      if (w < 32) {
+        // row by row: row dy of the rectangle holds bits [dy w, dy w + w) of the mask; the 64-bit mask is kept as a
+        // two-word window that slides down by w per row (no 64-bit shifts, no division per bit)
+        uint32_t lo = mlo, hi = mhi;
+        const uint32_t rowmask = (1u << w) - 1u;
+        uint32_t tile_row = (uint32_t)(rc.y0 * g.gx + rc.x0);
+        while (lo | hi) {
+          uint32_t row = lo & rowmask;
+          while (row) {
+            const uint32_t dx = (uint32_t)__ffs((int)row) - 1u;
+            row &= row - 1u;
+            emit((tile_row + dx) * (uint32_t)g.NB + bk, klo, khi);
+          }
+          lo = __funnelshift_r(lo, hi, (uint32_t)w);
+          hi >>= w;
+          tile_row += (uint32_t)g.gx;
+        }
+      } else {
+        unsigned long long mask = ((unsigned long long)mhi << 32) | mlo;
+        while (mask) {
+          const int bit = __ffsll((long long)mask) - 1;
+          mask &= mask - 1;
+          const int dy = bit / w;
+          emit((uint32_t)((rc.y0 + dy) * g.gx + rc.x0 + (bit - dy * w)) * (uint32_t)g.NB + bk, klo, khi);
+        }
       }
     }
     unsigned m = __ballot_sync(0xffffffffu, huge || wide);
@@ -1395,6 +1456,38 @@ group_bounds_kernel(int64_t n, const float* __restrict__ xyz, const float* __res
 }  // namespace
 
 namespace {
+// Dispatch order of a layer's (list, chunk) CTAs: heaviest first.  A chunk's weight is the number of tile entries it
+// produced (written by its preprocess CTA); a close-up of the gripper in a wrist camera makes single chunks hundreds
+// of times heavier than the rest, and with CTAs dispatched in index order those happened to come last: the SMs sat
+// idle for a quarter (preprocess) to a half (scatter) of the kernels' duration (ncu: sm cycles active / elapsed).
+// Counting sort by weight class (two classes per power of two, descending), one CTA; order inside a class is
+// arbitrary, which is harmless: the order only decides WHEN a chunk is processed.  The scatter pass of the same step
+// uses it, and so does the preprocess pass of the NEXT step (poses change little from step to step).
+constexpr int kCostClasses = 66;
+__global__ void __launch_bounds__(1024)
+order_chunks_kernel(const uint32_t* __restrict__ cost, uint32_t n, uint32_t* __restrict__ order) {
+  __shared__ uint32_t cnt[kCostClasses], start[kCostClasses];
+  auto cls = [](uint32_t c) -> int {
+    if (c == 0u) return 0;
+    const int l = 31 - __clz(c);                          // floor(log2 c)
+    const int half = l > 0 ? (int)((c >> (l - 1)) & 1u) : 0;
+    return 1 + 2 * l + half;                              // 1 .. 64
+  };
+  for (int k = threadIdx.x; k < kCostClasses; k += blockDim.x) cnt[k] = 0u;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(&cnt[cls(cost[i])], 1u);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int k = kCostClasses - 1; k >= 0; --k) {  // heaviest class first
+      start[k] = run;
+      run += cnt[k];
+    }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) order[atomicAdd(&start[cls(cost[i])], 1u)] = i;
+}
+
 template <auto Kernel>
 int ensure_smem(size_t bytes, int device) {
   static size_t granted[64] = {};  // per kernel and device: raise the opt-in shared-memory limit only when it grows
@@ -1414,6 +1507,15 @@ constexpr int kIpbStatic = 2048, kIpbDynamic = 2048;
 // Words of Workspace::status (u32 view) used by the static layer's work list: entries, and one ticket per pass.
 constexpr int kWorkCountWord = 20, kPreTicketWord = 21, kScatterTicketWord = 22;
 
+// tuning aid: persistent CTAs per SM of the static layer's work-list preprocess (GSW_WL_CTAS; 0 = as many as fit)
+static int wl_ctas_per_sm() {
+  static const int v = [] {
+    const char* e = getenv("GSW_WL_CTAS");
+    return e ? atoi(e) : 0;
+  }();
+  return v;
+}
+
 int64_t layer_chunks(int64_t n_items) { return (n_items + kItemsPerBlock - 1) / kItemsPerBlock; }
 
 // The static layer goes through the chunk-cull work list when its groups have bounds (scene layers; the single-frame
@@ -1427,7 +1529,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
                       int32_t list_base, int64_t item_base, const FrameGeom& g, const float* view, const float* proj,
                       const float* campos, const float* tanfov, const int32_t* frame_env, const int32_t* frame_view,
                       const float* pose, int32_t num_slots, uint32_t* cta_hist, uint32_t* chunk_mask, int* kept_hist,
-                      cudaStream_t s) {
+                      cudaStream_t s, const uint32_t* order, uint32_t* cost) {
   if (kept_hist) *kept_hist = 0;
   if (n_items <= 0 || n_lists <= 0) return 0;
   auto& w = ctx->ws;
@@ -1442,7 +1544,12 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     tma_ok = tma_ok && ga.quat_act != nullptr && aligned16(ga.quat_act) && (ga.slot == nullptr || aligned16(ga.slot));
   const size_t stage_b = dynamic ? (size_t)kIpbDynamic * 60 : (size_t)kIpbStatic * 48;
   const size_t budget = 200 * 1024;
-  int use_tma = !dynamic && tma_ok && stage_b + pose_b + 1024 <= budget;
+  // The bulk staging pays where a CTA's arithmetic is short next to its load latency (few visible items per chunk).
+  // The work-list form only visits live chunks; there the 96 KB stage costs a third of the resident warps and
+  // measured slower (per-env cameras: 1.08 -> 0.90 ms), so it keeps plain loads.  GSW_WL_TMA=1 / GSW_NO_TMA=1 override.
+  const bool wl_pre = use_work_list(dynamic, ga, n_items, n_lists);
+  int use_tma = !dynamic && tma_ok && stage_b + pose_b + 1024 <= budget && getenv("GSW_NO_TMA") == nullptr &&
+                (!wl_pre || getenv("GSW_WL_TMA") != nullptr);
   int use_hist = hist_b <= kMaxHistBytes && (use_tma ? stage_b : 0) + hist_b + pose_b <= budget;
   if (!use_hist && use_tma && hist_b <= kMaxHistBytes) {  // prefer the histogram over staging when both do not fit
     use_tma = 0;
@@ -1463,7 +1570,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 #define GSW_LAUNCH_PRE(DYN_, IPB_, TMA_, CULL_, WL_)                                                              \
   do {                                                                                                            \
     const int64_t pairs = (int64_t)nchunks * n_lists;                                                             \
-    const int64_t persistent = 148 * ((TMA_) ? 2 : 3);                                                            \
+    const int64_t persistent = 148 * (wl_ctas_per_sm() > 0 ? wl_ctas_per_sm() : ((TMA_) ? 2 : 3));               \
     dim3 grid((unsigned)nchunks, (unsigned)n_lists);                                                              \
     if (WL_) grid = dim3((unsigned)(pairs < persistent ? pairs : persistent), 1u);                               \
     if ((rc = ensure_smem<preprocess_kernel<DYN_, IPB_, TMA_, CULL_, WL_>>(sm, ctx->device))) return rc;          \
@@ -1471,7 +1578,8 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
         ga, n_items, list_base, item_base, g, view, proj, campos, tanfov, frame_env, frame_view, pose, num_slots, \
         w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
         w.bin_count.as<uint32_t>(), use_hist, use_hist ? cta_hist : nullptr, chunk_mask, nchunks,                 \
-        w.work.as<uint32_t>(), st32 + kWorkCountWord, st32 + kPreTicketWord, w.view_consts.as<uint32_t>());      \
+        w.work.as<uint32_t>(), st32 + kWorkCountWord, st32 + kPreTicketWord, w.view_consts.as<uint32_t>(),       \
+        order, (use_hist && cta_hist != nullptr) ? cost : nullptr);                                                \
   } while (0)
   const bool cull = g.tile_cull != 0;
   if (dynamic) {
@@ -1509,7 +1617,7 @@ size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g) {
 
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
-                   const uint32_t* chunk_mask, cudaStream_t s) {
+                   const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order) {
   if (n_items <= 0 || n_lists <= 0) return 0;
   static_assert(kIpbStatic == kItemsPerBlock && kIpbDynamic == kItemsPerBlock, "cta_hist: same chunks in both passes");
   const int32_t nchunks = (int32_t)layer_chunks(n_items);
@@ -1529,7 +1637,7 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
         ga, n_items, list_base, item_base, g, w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, \
         w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(), w.bin_cursor.as<uint32_t>(),                               \
         w.keys.as<unsigned long long>(), cap, (HIST_) ? 1 : 0, CH_, chunk_mask, nchunks, w.work.as<uint32_t>(),   \
-        st32 + kWorkCountWord, st32 + kScatterTicketWord);                                                        \
+        st32 + kWorkCountWord, st32 + kScatterTicketWord, order);                                                 \
   } while (0)
 #define GSW_COMMA ,
   if (g.tile_cull != 0) {  // the culling form has no counting pass of its own: shared counters need cta_hist
@@ -1544,6 +1652,14 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   }
 #undef GSW_COMMA
 #undef GSW_LAUNCH_SCATTER
+  count_launches(1);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_order_chunks(const uint32_t* cost, int64_t n, uint32_t* order, cudaStream_t s) {
+  if (n <= 0) return 0;
+  order_chunks_kernel<<<1, 1024, 0, s>>>(cost, (uint32_t)n, order);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
