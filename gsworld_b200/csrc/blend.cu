@@ -91,6 +91,19 @@ __device__ __forceinline__ f2 add2(f2 a, f2 b) {
   return r;
 }
 
+// alpha if the reference would composite it (power <= 0 and alpha >= 1/255, NaNs as the reference's comparisons treat
+// them), else 0: two compares chained through the predicate and one select
+__device__ __forceinline__ float keep_alpha(float alpha, float power) {
+  float r;
+  asm("{ .reg .pred q, p;\n\t"
+      "setp.gt.f32 q, %2, 0f00000000;\n\t"
+      "setp.geu.and.f32 p, %1, 0f3B808081, !q;\n\t"
+      "selp.f32 %0, %1, 0f00000000, p; }"
+      : "=f"(r)
+      : "f"(alpha), "f"(power));
+  return r;
+}
+
 // PPT = pixels per thread.  1: 256 threads, a warp owns an 8x4 pixel block.  2: 128 threads, a warp owns an 8x8
 // block and every lane the pixels (x, y) and (x, y + 4); the per-pixel arithmetic then runs on packed fp32x2
 // instructions and the record loads / queue reads are paid once for two pixels.
@@ -289,10 +302,11 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
     __syncwarp();
 
     // ---- blend the queued records in list order ----
+    uint32_t evaluated = 0;  // records of this chunk the warp really blended (it may stop early)
     for (uint32_t k0 = 0; k0 < cnt; k0 += 16) {
       if (k0 && __all_sync(0xffffffffu, all_done())) break;
       const uint32_t kend = min(cnt, k0 + 16);
-      if (lane == 0) sPairs[w] += (kend - k0) * PPT;  // kept in shared memory: the loop has no register to spare
+      evaluated = kend;
 #pragma unroll 4
       for (uint32_t k = k0; k < kend; ++k) {
         const uint32_t qi = lds_u8(aQ + k);
@@ -310,11 +324,10 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
           const float p20 = lo_of(p2), p21 = hi_of(p2);
           f2 al = mul2(bc(b.w), pk(ex2_approx(p20), ex2_approx(p21)));
           float a0 = fminf(0.99f, lo_of(al)), a1 = fminf(0.99f, hi_of(al));
-          a0 = ((p20 > 0.0f) || (a0 < 1.0f / 255.0f)) ? 0.0f : a0;  // skipped: alpha 0 leaves T unchanged bit for bit
-          a1 = ((p21 > 0.0f) || (a1 < 1.0f / 255.0f)) ? 0.0f : a1;
+          a0 = keep_alpha(a0, p20);  // skipped: alpha 0 leaves T unchanged bit for bit
+          a1 = keep_alpha(a1, p21);
           al = pk(a0, a1);
-          const f2 one_m = add2(bc(1.0f), pk(-a0, -a1));
-          const f2 tt = mul2(T2, one_m);  // T (1 - alpha)
+          const f2 tt = fma2(pk(-a0, -a1), T2, T2);  // T (1 - alpha) = T - alpha T
           const float tt0 = lo_of(tt), tt1 = hi_of(tt);
           const bool sat0 = tt0 < 0.0001f, sat1 = tt1 < 0.0001f;  // saturated now, or already (T < 0)
           f2 wg = mul2(al, T2);
@@ -365,6 +378,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
         Tacc = sat ? 0.0f : test_T;
       }
     }
+    if (lane == 0) sPairs[w] += evaluated * PPT;
   }
   // measurement counters: entries staged, and (record, pixel) pair evaluations = 32 x records blended per warp
   __syncthreads();
