@@ -558,32 +558,41 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t*
   return 0;
 }
 
-int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g,
-                     int64_t cap, cudaStream_t s) {
-  if (nbins <= 0) return 0;
+// Sorts the bins [bin0, bin0 + nb) of the last scan.  `set` selects one of two independent sets of queue storage,
+// queue counters and work tickets (status words), so that the static lists and the dynamic lists can be sorted by two
+// calls on two streams at the same time; set 0 with the full bin range is the single-call form.  `side`: a stream
+// this call may fork onto for the refinement and the medium class (s itself: everything in order on s).
+int launch_sort_bins(const gsw_ctx* ctx, int64_t bin0, int64_t nb, int64_t cap, int set, cudaStream_t s,
+                     cudaStream_t side) {
+  if (nb <= 0) return 0;
   auto& w = ctx->ws;
   constexpr size_t smem_m = (size_t)kSortSmemKeys * sizeof(unsigned long long);  // 32 KB
   constexpr size_t smem_s = (size_t)kSmallKeys * sizeof(unsigned long long);     // 8 KB
-  (void)V; (void)Ns; (void)Nm; (void)g;
-  // queue storage: [small: nbins][huge: nbins][medium: half of the rest][mid: the other half]; a queued
-  // mid/medium segment that is not a whole bin pairs with a neighbour to more than kMidKeys entries
+  // queue storage of a set (half of seg_queue): [small: nb][huge: nb][medium: half of the rest][mid: the other
+  // half]; a queued mid/medium segment that is not a whole bin pairs with a neighbour to more than kMidKeys entries
   Queues Q;
-  Segment* base = w.seg_queue.as<Segment>();
-  const uint32_t total = (uint32_t)(w.seg_queue.bytes / sizeof(Segment));
+  const size_t half = (w.seg_queue.bytes / sizeof(Segment)) / 2;
+  Segment* base = w.seg_queue.as<Segment>() + (set ? half : 0);
+  if (half < (size_t)(2 * nb + 16)) {
+    set_error("sort queues too small for %lld bins", (long long)nb);
+    return GSW_E_NOMEM;
+  }
+  const uint32_t total = (uint32_t)half;
   Q.q[0] = base;
-  Q.cap[0] = (uint32_t)nbins;
-  Q.q[2] = base + nbins;
-  Q.cap[2] = (uint32_t)nbins;
-  Q.cap[1] = Q.cap[3] = (total - 2 * (uint32_t)nbins) / 2;
-  Q.q[1] = base + 2 * nbins;
+  Q.cap[0] = (uint32_t)nb;
+  Q.q[2] = base + nb;
+  Q.cap[2] = (uint32_t)nb;
+  Q.cap[1] = Q.cap[3] = (total - 2 * (uint32_t)nb) / 2;
+  Q.q[1] = base + 2 * nb;
   Q.q[3] = Q.q[1] + Q.cap[1];
-  Q.count = w.status.as<uint32_t>() + 12;  // four words of the status block (zeroed every launch)
-  uint32_t* ticket = w.status.as<uint32_t>() + 16;  // three more: work tickets of the medium / small / mid sort
-  classify_bins_kernel<<<(unsigned)((nbins + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>(), nbins, cap, Q,
-                                                                      w.status.as<long long>());
+  // status words (zeroed every launch): set 0 -> counters 12..15, tickets 16..18; set 1 -> 24..27, 28..30
+  Q.count = w.status.as<uint32_t>() + (set ? 24 : 12);
+  uint32_t* ticket = w.status.as<uint32_t>() + (set ? 28 : 16);
+  classify_bins_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>() + bin0, nb, cap, Q,
+                                                                   w.status.as<long long>());
   // the depth partition of the huge bins (one CTA per bin, half the SMs idle) runs on the side stream next to
   // the small-class sort, which does not depend on it; the mid / medium queues it appends to are sorted after
-  cudaStream_t ss = ctx->side_stream ? ctx->side_stream : s;
+  cudaStream_t ss = side ? side : s;
   if (ss != s) {
     GSW_CUDA(cudaEventRecord(ctx->fork_evt, s));
     GSW_CUDA(cudaStreamWaitEvent(ss, ctx->fork_evt, 0));

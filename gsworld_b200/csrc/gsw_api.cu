@@ -153,7 +153,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   int kept_s = 0, kept_d = 0;
   // medium and mid queue (half each): whole bins (<= nbins each) plus sub-segments of huge bins, of which
   // every one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries
-  if ((rc = w.seg_queue.reserve(seg_queue_bytes(cap, nbins)))) return rc;
+  if ((rc = w.seg_queue.reserve(2 * seg_queue_bytes(cap, nbins)))) return rc;  // two independent queue sets
 
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
@@ -180,6 +180,8 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     GSW_CUDA(cudaStreamWaitEvent(s, ctx->join_evt, 0));
     return 0;
   };
+  if ((rc = w.view_cnt.reserve((size_t)V * 4 + 16))) return rc;
+  if ((rc = launch_count_views(ctx, V, F, frame_view, s))) return rc;
   mark(0);
   if ((rc = fork())) return rc;
   if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
@@ -220,16 +222,25 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, mask_d, s,
                              have_order ? w.dyn_order.as<uint32_t>() : nullptr)))
       return rc;
-  if ((rc = join())) return rc;
-  mark(4);
-  if ((rc = w.view_cnt.reserve((size_t)V * 4 + 16))) return rc;
-  if ((rc = launch_count_views(ctx, V, F, frame_view, s))) return rc;
   ctx->last.pos_of = pos_of;  // the gather reads it
-  if ((rc = launch_sort_bins(ctx, nbins, V, Ns, Nm, g, cap, s))) return rc;
-  mark(5);
   if (with_labels && (rc = w.lab_stream.reserve((size_t)cap * 4))) return rc;
-  if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, with_labels, s))) return rc;
-  mark(6);
+  const int64_t nbs = (int64_t)V * g.T * g.NB;  // static bins come first
+  if (two) {
+    // From here on the two layers are independent until the blend.  Side stream: sort of the static lists, gather
+    // of the shared ones and (gsw_render_frames) the view pass over them.  Main stream: sort of the dynamic lists,
+    // which forks onto a third stream inside.  join_side() closes the fork before the blend.
+    if ((rc = launch_sort_bins(ctx, 0, nbs, cap, 1, ss, ss))) return rc;
+    if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, with_labels, ss))) return rc;
+    if ((rc = launch_sort_bins(ctx, nbs, nbins - nbs, cap, 0, s, ctx->side2_stream ? ctx->side2_stream : s))) return rc;
+    ctx->side_pending = true;
+  } else {
+    if ((rc = join())) return rc;
+    mark(4);
+    if ((rc = launch_sort_bins(ctx, 0, nbins, cap, 0, s, ctx->side_stream ? ctx->side_stream : s))) return rc;
+    mark(5);
+    if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, with_labels, s))) return rc;
+    mark(6);
+  }
 
   ctx->last.valid = true;
   ctx->last.V = V;
@@ -244,6 +255,15 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   ctx->last.frame_view = frame_view;
   ctx->last.nbins = nbins;
   ctx->last.cap = cap;
+  return 0;
+}
+
+// Closes the fork run_pipeline left open (static chain on the side stream): `s` waits for it.
+int join_side(gsw_ctx* ctx, cudaStream_t s) {
+  if (!ctx->side_pending) return 0;
+  ctx->side_pending = false;
+  GSW_CUDA(cudaEventRecord(ctx->join_evt, ctx->side_stream));
+  GSW_CUDA(cudaStreamWaitEvent(s, ctx->join_evt, 0));
   return 0;
 }
 
@@ -302,6 +322,7 @@ int gsw_create(int device, gsw_ctx** out) {
     else e = cudaMemset(c->sig.p, 0, 2 * kMaxSigGroups * sizeof(uint32_t));
   }
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side2_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->fork_evt, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->join_evt, cudaEventDisableTiming);
   if (e != cudaSuccess) {
@@ -337,6 +358,7 @@ int gsw_destroy(gsw_ctx* c) {
   if (c->fork_evt) cudaEventDestroy(c->fork_evt);
   if (c->join_evt) cudaEventDestroy(c->join_evt);
   if (c->side_stream) cudaStreamDestroy(c->side_stream);
+  if (c->side2_stream) cudaStreamDestroy(c->side2_stream);
   for (int k = 0; k <= kNumStages; ++k)
     if (c->stage_evt[k]) cudaEventDestroy(c->stage_evt[k]);
   delete c;
@@ -594,9 +616,11 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
       return rc;
     if ((rc = launch_blend_view_pass(c, d->num_views, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g,
                                      d->bg, d->out_rgb_u8 != nullptr, d->out_color != nullptr,
-                                     d->out_invdepth != nullptr, d->out_seg != nullptr, s)))
+                                     d->out_invdepth != nullptr, d->out_seg != nullptr,
+                                     c->side_pending ? c->side_stream : s)))
       return rc;
   }
+  if ((rc = join_side(c, s))) return rc;
   const bool deliver = d->host_rgb_u8 != nullptr || n_peer > 0;
   // one group of finished frames to every destination (pinned host and / or peer GPUs), on the copy stream
   auto send_group = [&](int f0, int f1) -> int {
@@ -972,7 +996,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.keys, (size_t)kNaMaxEntries * 8);
   carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
   carve(w.status, 128);
-  carve(w.seg_queue, seg_queue_bytes(kNaMaxEntries, nbins));
+  carve(w.seg_queue, 2 * seg_queue_bytes(kNaMaxEntries, nbins));
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view
   {  // the largest per-CTA histogram block run_pipeline can ask for within the limits: kNaMaxP items, kNaMaxTiles tiles

@@ -200,8 +200,10 @@ struct gsw_ctx {
   // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are
   // independent until the scan / the sort, and each leaves a good part of the SMs idle on its own
   cudaStream_t side_stream = nullptr;
+  cudaStream_t side2_stream = nullptr;  // the dynamic lists' sort forks onto it while side_stream carries the static chain
   cudaEvent_t fork_evt = nullptr, join_evt = nullptr;
   int64_t launches = 0;
+  bool side_pending = false;  // run_pipeline left the static chain running on side_stream (join_side closes it)
   int64_t dyn_order_n = 0;  // number of (frame, chunk) pairs ws.dyn_order is valid for (0: none yet)
 };
 
@@ -230,8 +232,8 @@ int launch_gather_layers(const gsw_ctx* ctx, cudaStream_t s);  // compact static
 
 // binsort.cu
 int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s);
-int launch_sort_bins(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g,
-                     int64_t cap, cudaStream_t s);
+int launch_sort_bins(const gsw_ctx* ctx, int64_t bin0, int64_t nb, int64_t cap, int set, cudaStream_t s,
+                     cudaStream_t side);
 int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g, int64_t cap,
                   bool with_labels, cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,
