@@ -296,7 +296,11 @@ def issue_roofline(stage_ms, sm_mhz):
     committed ncu capture (same command, same workload), kernel time measured live."""
     try:
         inst = 0.0
-        with open(os.path.join(ROOT, "profiles", "r01_ncu_full_strict.txt")) as f:
+        src = "r02_ncu_full_strict.txt" if os.path.exists(os.path.join(ROOT, "profiles", "r02_ncu_full_strict.txt")) \
+            else "r01_ncu_full_strict.txt"
+        if CONFIG != "cfg3":
+            return None
+        with open(os.path.join(ROOT, "profiles", src)) as f:
             hdr = [h.split("[")[0].strip() for h in f.readline().split("|")]
             for ln in f:
                 c = [x.strip() for x in ln.split("|")]
@@ -308,7 +312,7 @@ def issue_roofline(stage_ms, sm_mhz):
         ach = inst / (stage_ms * 1e-3) / 1e9
         return {"bound": "sm_issue", "kernel": "blend", "achieved": ach, "peak": peak, "unit": "G warp-inst/s",
                 "frac": ach / peak, "warp_inst_per_step": inst,
-                "source": "instruction count: profiles/r01_ncu_full_strict.txt; time: live stage events"}
+                "source": f"instruction count: profiles/{src}; time: live stage events"}
     except Exception:
         return None
 
