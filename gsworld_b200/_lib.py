@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libgsw.so")
+# GSW_LIB_PATH: another build of the same sources (A/B runs of compile-time tuning constants)
+LIB_PATH = os.environ.get("GSW_LIB_PATH") or os.path.join(_HERE, "csrc", "libgsw.so")
 POSE_STRIDE = 20
 
 GSW_E_CAPACITY = -3

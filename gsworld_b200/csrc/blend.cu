@@ -467,11 +467,6 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
 }
 
 
-__global__ void count_view_frames_kernel(int32_t F, const int32_t* __restrict__ frame_view, uint32_t* view_cnt) {
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f < F) atomicAdd(&view_cnt[frame_view[f]], 1u);
-}
-
 }  // namespace
 
 // Pixels per thread of the blend kernel (see blend_body).  GSW_BLEND_PPT=1 selects the one-pixel form (A/B aid); the
@@ -484,19 +479,8 @@ static int blend_ppt() {
   return v;
 }
 
-// Static-tile sharing set-up: counts frames per view and renders the static-only image of every view that is
+// Static-tile sharing: renders the static-only image of every view that is
 // shared by >= 2 frames (mode 1).  Buffers live in the workspace; call before launch_blend when F > V.
-// frames per view (view_cnt): decides which static lists are shared (materialised once, tiles re-used) and
-// which are private to one frame (fetched lazily by the blend)
-int launch_count_views(const gsw_ctx* ctx, int32_t V, int32_t F, const int32_t* frame_view, cudaStream_t s) {
-  auto& w = ctx->ws;
-  GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
-  count_view_frames_kernel<<<(F + 255) / 256, 256, 0, s>>>(F, frame_view, w.view_cnt.as<uint32_t>());
-  count_launches(1);
-  GSW_CUDA(cudaGetLastError());
-  return 0;
-}
-
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
                            bool want_invd, bool want_seg, cudaStream_t s) {

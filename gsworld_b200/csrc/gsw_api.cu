@@ -140,11 +140,11 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(128))) return rc;
-  const size_t chs = cta_hist_words(Ns, V, g), chd = dyn ? cta_hist_words(Nm, F, g) : 0;
+  const size_t chs = cta_hist_words(Ns, V, g, false), chd = dyn ? cta_hist_words(Nm, F, g, true) : 0;
   if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
   uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;
   uint32_t* const ch_d = chd ? w.cta_hist.as<uint32_t>() + chs : nullptr;
-  const size_t cm_s = (size_t)V * (size_t)layer_chunks(Ns), cm_d = dyn ? (size_t)F * (size_t)layer_chunks(Nm) : 0;
+  const size_t cm_s = (size_t)V * (size_t)layer_chunks(Ns, false), cm_d = dyn ? (size_t)F * (size_t)layer_chunks(Nm, true) : 0;
   if ((rc = w.chunk_mask.reserve((cm_s + cm_d) * 4 + 16)) || (rc = w.work.reserve(cm_s * 4 + 16)) ||
       (rc = w.view_consts.reserve((size_t)V * 48 * 4)))
     return rc;
@@ -181,7 +181,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     return 0;
   };
   if ((rc = w.view_cnt.reserve((size_t)V * 4 + 16))) return rc;
-  if ((rc = launch_count_views(ctx, V, F, frame_view, s))) return rc;
+  if ((rc = launch_prepare_views(ctx, V, F, g, view, proj, campos, tanfov, frame_view, s))) return rc;
   mark(0);
   if ((rc = fork())) return rc;
   if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
@@ -1003,10 +1003,10 @@ int na_setup(int device, NaDevice& nd) {
     FrameGeom gmax{};
     gmax.T = kNaMaxTiles;
     gmax.NB = 1;
-    carve(w.cta_hist, cta_hist_words(kNaMaxP, 1, gmax) * 4 + 16);
+    carve(w.cta_hist, cta_hist_words(kNaMaxP, 1, gmax, false) * 4 + 16);
   }
-  carve(w.chunk_mask, (size_t)layer_chunks(kNaMaxP) * 4 + 16);
-  carve(w.work, (size_t)layer_chunks(kNaMaxP) * 4 + 16);
+  carve(w.chunk_mask, (size_t)layer_chunks(kNaMaxP, false) * 4 + 16);
+  carve(w.work, (size_t)layer_chunks(kNaMaxP, false) * 4 + 16);
   carve(w.view_consts, 48 * 4);
   if (off > kNaBytes) {
     set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);

@@ -218,8 +218,8 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
                       cudaStream_t s, const uint32_t* order = nullptr, uint32_t* cost = nullptr);
 // heaviest-first dispatch order of n (list, chunk) CTAs from their weights (tile entries produced)
 int launch_order_chunks(const uint32_t* cost, int64_t n, uint32_t* order, cudaStream_t s);
-size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g);
-int64_t layer_chunks(int64_t n_items);  // 2048-item chunks of a layer (one preprocess / scatter CTA round each)
+size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic);
+int64_t layer_chunks(int64_t n_items, bool dynamic);  // chunks of a layer (one preprocess / scatter CTA round each)
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
                    const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order = nullptr);
@@ -249,7 +249,10 @@ int launch_compose_cameras(int n, const float* ext, const float* K, int H, int W
 int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int64_t nbins, const int32_t* frame_view, int64_t cap,
                  const FrameGeom& g, const float bg[3], const float* bg_dev, uint8_t* out_u8, float* out_color,
                  float* out_invdepth, int32_t* out_seg, bool share, cudaStream_t s, const DoneSig* sig = nullptr);
-int launch_count_views(const gsw_ctx* ctx, int32_t V, int32_t F, const int32_t* frame_view, cudaStream_t s);
+// per-view preprocess constants (ws.view_consts) + frames per view (ws.view_cnt): first kernel of a launch set
+int launch_prepare_views(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, const float* view,
+                         const float* proj, const float* campos, const float* tanfov, const int32_t* frame_view,
+                         cudaStream_t s);
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
                            int64_t cap, const FrameGeom& g, const float bg[3], bool want_u8, bool want_color,
                            bool want_invd, bool want_seg, cudaStream_t s);

@@ -167,8 +167,16 @@ __device__ __forceinline__ float sh_channel(int deg, float x, float y, float z, 
   return fmaxf(res, 0.0f);
 }
 
-constexpr int kItemsPerThread = 8;                   // each CTA walks 256 * 8 consecutive items of one list
-constexpr int kItemsPerBlock = 256 * kItemsPerThread;
+// Items per CTA round ("chunk") of each layer: 256 threads x chunk / 256 consecutive items of one list.  The static
+// layer keeps large chunks (fewer per-CTA histogram flushes over a million Gaussians per view); the dynamic layer
+// uses smaller ones, because a close-up of the gripper makes single chunks of movable Gaussians hundreds of times
+// heavier than the rest, and a chunk is the unit the preprocess and scatter passes are balanced in.
+#ifndef GSW_IPB_DYN
+#define GSW_IPB_DYN 2048
+#endif
+constexpr int kIpbStatic = 2048, kIpbDynamic = GSW_IPB_DYN;
+constexpr int kItemsPerBlock = kIpbStatic;  // the static layer's (chunk-cull work list)
+constexpr int ipb_of(bool dynamic) { return dynamic ? kIpbDynamic : kIpbStatic; }
 constexpr size_t kMaxHistBytes = 160 * 1024;         // per-CTA shared histogram budget; above it: global atomics
 
 // Per-item body.  `hist` (shared, one counter per (tile, bucket) of this list) may be null, in which case
@@ -701,6 +709,24 @@ __device__ __forceinline__ void compute_view_consts(int view, const FrameGeom& g
   }
 }
 
+// First kernel of a launch set: the per-view constants of every view (block v < V; both layers' preprocess CTAs then
+// only copy 48 words instead of each deriving them with two serial threads) and the number of frames that look
+// through each view (view_cnt, zeroed before; decides which static lists are shared).  grid max(V, ceil(F / 256)).
+__global__ void __launch_bounds__(256)
+prepare_views_kernel(int32_t V, int32_t F, FrameGeom g, const float* __restrict__ views,
+                     const float* __restrict__ projs, const float* __restrict__ campos,
+                     const float* __restrict__ tanfov, const int32_t* __restrict__ frame_view,
+                     uint32_t* __restrict__ view_consts, uint32_t* __restrict__ view_cnt) {
+  __shared__ ViewConsts c;
+  const int f = blockIdx.x * 256 + threadIdx.x;
+  if (f < F) atomicAdd(&view_cnt[frame_view ? frame_view[f] : 0], 1u);
+  if ((int)blockIdx.x >= V) return;  // block-uniform
+  compute_view_consts(blockIdx.x, g, views, projs, campos, tanfov, c.vs, c.vc);
+  __syncthreads();
+  if (threadIdx.x < kViewConstWords)
+    view_consts[(size_t)blockIdx.x * kViewConstWords + threadIdx.x] = reinterpret_cast<const uint32_t*>(&c)[threadIdx.x];
+}
+
 // ---- chunk-level culling of the static layer, ahead of the preprocess pass ----
 // One thread per (view, 2048-item chunk): tests the chunk's 8 group spheres against the view and leaves the mask
 // of live groups in chunk_mask[view * nchunks + chunk]; chunks with at least one live group are appended to a
@@ -714,13 +740,12 @@ cull_chunks_kernel(const float* __restrict__ bounds, int64_t n_items, int32_t nc
                    const float* __restrict__ views, const float* __restrict__ projs,
                    const float* __restrict__ campos, const float* __restrict__ tanfov,
                    uint32_t* __restrict__ chunk_mask, uint32_t* __restrict__ work, uint32_t* __restrict__ work_count,
-                   uint32_t* __restrict__ view_consts) {
+                   const uint32_t* __restrict__ view_consts) {
   __shared__ ViewConsts c;
   const int view = blockIdx.y;
-  compute_view_consts(view, g, views, projs, campos, tanfov, c.vs, c.vc);
+  if (threadIdx.x < kViewConstWords)  // written by prepare_views_kernel
+    reinterpret_cast<uint32_t*>(&c)[threadIdx.x] = view_consts[(size_t)view * kViewConstWords + threadIdx.x];
   __syncthreads();
-  if (blockIdx.x == 0 && threadIdx.x < kViewConstWords)
-    view_consts[(size_t)view * kViewConstWords + threadIdx.x] = reinterpret_cast<const uint32_t*>(&c)[threadIdx.x];
   const int chunk = blockIdx.x * 256 + threadIdx.x;
   uint32_t mask = 0;
   if (chunk < nchunks) {
@@ -817,7 +842,7 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     const bool full = base + IPB <= n_items;
     const bool staged = use_tma && full;  // partial tail chunk: plain global loads
     const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
-    if (WL) {
+    if (view_consts != nullptr) {  // prepared once per view by prepare_views_kernel
       if (threadIdx.x < kViewConstWords)
         reinterpret_cast<uint32_t*>(&vcs)[threadIdx.x] = view_consts[(size_t)view * kViewConstWords + threadIdx.x];
     } else {
@@ -948,7 +973,11 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
 // Item handled by thread t in iteration it of a 2048-item chunk.  Items are spatially ordered, so the 256
 // items of a group fall into very few tile bins; letting the 32 lanes of a warp take 4 items from each of
 // the chunk's 8 groups (instead of 32 neighbours) cuts same-address shared-memory atomic conflicts 8-fold.
-__device__ __forceinline__ int scatter_slot(int it, int t) { return ((t & 7) << 8) | (it << 5) | (t >> 3); }
+// (G = groups per chunk = items per thread)
+template <int G>
+__device__ __forceinline__ int scatter_slot(int it, int t) {
+  return ((t & (G - 1)) << 8) + it * (256 / G) + t / G;
+}
 
 // (list, chunk) of a scatter CTA's next round.  Plain form: one round, the block indices.  Work-list form (static
 // layer): persistent CTAs take (view, chunk) pairs of cull_chunks_kernel's list by ticket.  CTA-uniform result.
@@ -985,6 +1014,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
                const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
                uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
+  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic, kItemsPerThread = kItemsPerBlock / 256;  // this layer's chunk
   extern __shared__ uint32_t dsm[];
   __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
@@ -998,8 +1028,8 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   const int64_t base = (int64_t)chunk * kItemsPerBlock;
   const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
   // groups of the chunk that the preprocess pass found dead were never written: their items count as radius 0.
-  // scatter_slot() gives every thread items of ONE group, (threadIdx.x & 7).
-  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & 7)) & 1u;
+  // scatter_slot() gives every thread items of ONE group, threadIdx.x & (groups - 1).
+  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & (kItemsPerThread - 1))) & 1u;
   if (chunk_mask[chunk_id] == 0u) continue;  // whole chunk culled (CTA-uniform)
   if (use_hist && cta_hist != nullptr) {
     // the preprocess CTA that walked this chunk left its per-bin counts: no second counting pass
@@ -1015,7 +1045,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     __syncthreads();
 #pragma unroll 1
     for (int it = 0; it < kItemsPerThread; ++it) {
-      const int64_t i = base + scatter_slot(it, threadIdx.x);
+      const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
       if (i >= n_items || !glive) continue;
       const int64_t item = item_base + (int64_t)list * n_items + i;
       const int radius = rad[item];
@@ -1041,14 +1071,14 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   float ax[kItemsPerThread], ay[kItemsPerThread], dep[kItemsPerThread];
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + scatter_slot(it, threadIdx.x);
+    const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
     radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
     ax[it] = ay[it] = dep[it] = 0.f;
     if (radius[it] > 0) {
-      const int64_t item = item_base + (int64_t)list * n_items + base + scatter_slot(it, threadIdx.x);
+      const int64_t item = item_base + (int64_t)list * n_items + base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
       const float4 a = recA[4 * item];
       ax[it] = a.x;
       ay[it] = a.y;
@@ -1060,7 +1090,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     Rect rc{0, 0, 0, 0};
     uint32_t bk = 0, klo = 0, khi = 0;
     if (radius[it] > 0) {
-      const int64_t i = base + scatter_slot(it, threadIdx.x);
+      const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
       rc = tile_rect(ax[it], ay[it], radius[it], g.gx, g.gy);
       klo = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
       khi = __float_as_uint(dep[it]);
@@ -1093,6 +1123,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
                     const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                     const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
                     uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
+  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic, kItemsPerThread = kItemsPerBlock / 256;  // this layer's chunk
   extern __shared__ uint32_t dsm[];
   __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
@@ -1105,7 +1136,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
   const int64_t base = (int64_t)chunk * kItemsPerBlock;
   const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
-  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & 7)) & 1u;  // see scatter_kernel
+  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & (kItemsPerThread - 1))) & 1u;  // see scatter_kernel
   if (chunk_mask[chunk_id] == 0u) continue;  // whole chunk culled (CTA-uniform)
   if (use_hist) {
     const uint32_t* keep = cta_hist + chunk_id * (size_t)(nbl + 1);
@@ -1128,7 +1159,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   int radius[kItemsPerThread];
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + scatter_slot(it, threadIdx.x);
+    const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
     radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
   // The kernel is bound by the latency of its dependent loads (radius -> record -> key store), not by issue: the
@@ -1148,7 +1179,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
     p.depth = 0.f;
     p.key = 0u;
     if (it < kItemsPerThread && radius[it] > 0) {
-      const int64_t i = base + scatter_slot(it, threadIdx.x);
+      const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
       const int64_t item = item_base + (int64_t)list * n_items + i;
       p.a = recA[4 * item];
       p.m = *reinterpret_cast<const float2*>(recA + 4 * item + 3);
@@ -1160,7 +1191,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   Pre nxt = fetch(0);
 #pragma unroll 1
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + scatter_slot(it, threadIdx.x);
+    const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
     const int64_t item = item_base + (int64_t)list * n_items + i;
     const Pre cur = nxt;
     nxt = fetch(it + 1);
@@ -1258,11 +1289,12 @@ __device__ __forceinline__ int radius_of(int64_t i, int32_t f, int32_t v, int32_
                                          const uint32_t* chunk_mask, int64_t* item_out) {
   const int64_t pos = pos_of ? (int64_t)pos_of[i] : i;
   const bool dyn = slot != nullptr && slot[i] >= 0;
-  const int64_t nch_s = (Ns + kItemsPerBlock - 1) / kItemsPerBlock, nch_d = (Nm + kItemsPerBlock - 1) / kItemsPerBlock;
+  const int64_t nch_s = (Ns + kIpbStatic - 1) / kIpbStatic, nch_d = (Nm + kIpbDynamic - 1) / kIpbDynamic;
   const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)f * Nm + pos : (int64_t)v * Ns + pos;
-  const int64_t cid = (dyn ? (int64_t)V * nch_s + (int64_t)f * nch_d : (int64_t)v * nch_s) + pos / kItemsPerBlock;
+  const int64_t ipb = dyn ? kIpbDynamic : kIpbStatic;
+  const int64_t cid = (dyn ? (int64_t)V * nch_s + (int64_t)f * nch_d : (int64_t)v * nch_s) + pos / ipb;
   *item_out = item;
-  if (chunk_mask != nullptr && !((chunk_mask[cid] >> ((pos % kItemsPerBlock) >> 8)) & 1u)) return 0;
+  if (chunk_mask != nullptr && !((chunk_mask[cid] >> ((pos % ipb) >> 8)) & 1u)) return 0;
   return rad[item];
 }
 
@@ -1502,8 +1534,6 @@ int ensure_smem(size_t bytes, int device) {
 
 // The dynamic layer is arithmetic-bound (transform + SH for nearly every item), not load-latency-bound: it
 // keeps plain loads and the larger chunk; only the static layer stages through TMA.
-constexpr int kIpbStatic = 2048, kIpbDynamic = 2048;
-
 // Words of Workspace::status (u32 view) used by the static layer's work list: entries, and one ticket per pass.
 constexpr int kWorkCountWord = 20, kPreTicketWord = 21, kScatterTicketWord = 22;
 
@@ -1516,12 +1546,12 @@ static int wl_ctas_per_sm() {
   return v;
 }
 
-int64_t layer_chunks(int64_t n_items) { return (n_items + kItemsPerBlock - 1) / kItemsPerBlock; }
+int64_t layer_chunks(int64_t n_items, bool dynamic) { return (n_items + ipb_of(dynamic) - 1) / ipb_of(dynamic); }
 
 // The static layer goes through the chunk-cull work list when its groups have bounds (scene layers; the single-frame
 // entry points have none) and (view, chunk) fits the 16 + 16 bit packing.
 bool use_work_list(bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
-  return !dynamic && ga.bounds != nullptr && n_lists <= 65535 && layer_chunks(n_items) <= 65535 &&
+  return !dynamic && ga.bounds != nullptr && n_lists <= 65535 && layer_chunks(n_items, false) <= 65535 &&
          getenv("GSW_NO_WORK_LIST") == nullptr;
 }
 
@@ -1556,7 +1586,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     use_hist = 1;
   }
   const size_t sm = (use_tma ? stage_b : 0) + (use_hist ? hist_b : 0) + pose_b;
-  const int32_t nchunks = (int32_t)layer_chunks(n_items);
+  const int32_t nchunks = (int32_t)layer_chunks(n_items, dynamic);
   const bool wl = use_work_list(dynamic, ga, n_items, n_lists);
   uint32_t* const st32 = w.status.as<uint32_t>();
   if (wl) {
@@ -1610,17 +1640,16 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 }
 
 // words of cta_hist one layer needs (0: the bins do not fit a shared-memory histogram, nothing is kept)
-size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g) {
+size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic) {
   if (n_items <= 0 || n_lists <= 0 || (size_t)g.T * g.NB * 4 > kMaxHistBytes) return 0;
-  return (size_t)n_lists * (size_t)layer_chunks(n_items) * (size_t)(g.T * g.NB + 1);
+  return (size_t)n_lists * (size_t)layer_chunks(n_items, dynamic) * (size_t)(g.T * g.NB + 1);
 }
 
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
                    const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order) {
   if (n_items <= 0 || n_lists <= 0) return 0;
-  static_assert(kIpbStatic == kItemsPerBlock && kIpbDynamic == kItemsPerBlock, "cta_hist: same chunks in both passes");
-  const int32_t nchunks = (int32_t)layer_chunks(n_items);
+  const int32_t nchunks = (int32_t)layer_chunks(n_items, dynamic);
   const bool wl = use_work_list(dynamic, ga, n_items, n_lists);
   const int64_t pairs = (int64_t)nchunks * n_lists, persistent = 148 * 4;
   dim3 grid((unsigned)nchunks, (unsigned)n_lists);
@@ -1652,6 +1681,19 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   }
 #undef GSW_COMMA
 #undef GSW_LAUNCH_SCATTER
+  count_launches(1);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_prepare_views(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGeom& g, const float* view,
+                         const float* proj, const float* campos, const float* tanfov, const int32_t* frame_view,
+                         cudaStream_t s) {
+  auto& w = ctx->ws;
+  GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
+  const int blocks = V > (F + 255) / 256 ? V : (F + 255) / 256;
+  prepare_views_kernel<<<blocks, 256, 0, s>>>(V, F, g, view, proj, campos, tanfov, frame_view,
+                                              w.view_consts.as<uint32_t>(), w.view_cnt.as<uint32_t>());
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
