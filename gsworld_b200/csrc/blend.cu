@@ -118,7 +118,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
              const float* __restrict__ st_color, const float* __restrict__ st_invd,
              const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg, const int32_t* __restrict__ st_seg,
              int use_view_images, const float4* __restrict__ rec, const int32_t* __restrict__ pos_of, int64_t Ns,
-             const int32_t* __restrict__ labels, int64_t Nm) {
+             const int32_t* __restrict__ labels, int64_t Nm, int tma_stage) {
   // Only static lists of views shared by several frames are materialised as a splat stream
   // (gather_splats_kernel); for every other list this kernel fetches the records of the entries it actually
   // reaches (about 70 % of them at cfg3, a quarter with per-env cameras) from the per-item records through
@@ -129,7 +129,8 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   // view that is shared by >= 2 frames into the st_* images (passed as out_*), once.  In mode 0 a tile whose
   // frame has no dynamic entries there is then a plain copy of the view's tile: same list, same code, same
   // bits, computed once instead of once per env.
-  __shared__ float4 sRec[kChunk * 3];                  // staged records, 48 B each: {a, b, c}
+  __shared__ __align__(128) float4 sRec[kChunk * 3];   // staged records, 48 B each: {a, b, c}
+  __shared__ __align__(8) unsigned long long mbar_s;   // completion of the bulk copies (tma_stage)
   __shared__ unsigned long long kS[kChunk], kD[kChunk];  // key windows of the two streams (merged tiles only)
   constexpr int NT = 256 / PPT, NW = 8 / PPT;          // threads, warps per CTA
   __shared__ uint8_t sQ[NW][kChunk];                   // per-warp queue of staged records that touch its pixels
@@ -210,12 +211,27 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   };
   uint32_t base = 0;
   if (threadIdx.x < 8) sPairs[threadIdx.x] = 0u;  // (the first barrier of the loop orders this before any update)
+  // tma_stage: chunks that come from ONE materialised stream (the shared static list of a view: contiguous 48 B
+  // splats) are pulled in by one elected thread with a single bulk copy (cp.async.bulk + mbarrier) instead of three
+  // 16 B loads and stores per thread.  Chunks that are merged from two streams or fetched through keys -> records are
+  // gathers and stay as they are.
+  const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar_s);
+  uint32_t tma_phase = 0;
+  if (tma_stage && threadIdx.x == 0) mbar_init(mb, 1);  // visible to the CTA after the loop's first barrier
   for (; base < total; base += kChunk) {
     if (__syncthreads_and(all_done())) break;  // also protects the staging buffers of the previous round
     const uint32_t n = min((uint32_t)kChunk, total - base);
     const uint32_t rs = ns - i0, rd = nd - j0;
     if (rs == 0 || rd == 0) {  // single-stream chunk
       const uint32_t src = rd == 0 ? s0 + i0 : d0 + j0;
+      if (!SEG && tma_stage && rd == 0 && !lazyA) {  // CTA-uniform
+        if (threadIdx.x == 0) {
+          mbar_expect_tx(mb, n * 48u);
+          bulk_g2s(aRec, splats + src, n * 48u, mb);
+        }
+        mbar_wait(mb, tma_phase);
+        tma_phase ^= 1u;
+      } else
       for (uint32_t t = threadIdx.x; t < n; t += NT) {
         if (rd == 0 ? lazyA : lazyD) {
           const uint32_t idx = (uint32_t)(keys[src + t] & 0xffffffffull);
@@ -439,10 +455,10 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              const float* __restrict__ st_invd, const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg,
              const int32_t* __restrict__ st_seg, int use_view_images, const float4* __restrict__ rec,
              const int32_t* __restrict__ pos_of, int64_t Ns, const int32_t* __restrict__ labels, int64_t Nm,
-             DoneSig sig) {
+             DoneSig sig, int tma_stage) {
   blend_body<SEG, PPT>(bin_off, nbins, frame_view, V, f_begin, keys, splats, cap, g, bg0, bg1, bg2, bg_dev, out_u8,
                   out_color, out_invd, status, mode, view_cnt, st_u8, st_color, st_invd, lab_stream, out_seg, st_seg,
-                  use_view_images, rec, pos_of, Ns, labels, Nm);
+                  use_view_images, rec, pos_of, Ns, labels, Nm, tma_stage);
   if (sig.cnt != nullptr) {
     // every thread's pixel stores precede the barrier; thread 0's release makes them visible device-wide (and to
     // the copy engine) before the counter moves; the CTA that completes a group publishes the epoch
@@ -479,6 +495,15 @@ static int blend_ppt() {
   return v;
 }
 
+// Bulk-copy staging of single-stream chunks of materialised lists (see blend_body).  GSW_BLEND_TMA=0 turns it off.
+static int blend_tma() {
+  static const int v = [] {
+    const char* e = getenv("GSW_BLEND_TMA");
+    return (e != nullptr && e[0] == '0') ? 0 : 1;
+  }();
+  return v;
+}
+
 // Static-tile sharing: renders the static-only image of every view that is
 // shared by >= 2 frames (mode 1).  Buffers live in the workspace; call before launch_blend when F > V.
 int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbins, const int32_t* frame_view,
@@ -493,7 +518,7 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
       want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
       w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
       want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr, 0, w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns,    \
-      ctx->labels, ctx->last.Nm, DoneSig{})
+      ctx->labels, ctx->last.Nm, DoneSig{}, blend_tma())
   if (blend_ppt() == 2) {
     if (want_seg) GSW_VIEW_PASS(true, 2); else GSW_VIEW_PASS(false, 2);
   } else {
@@ -521,7 +546,7 @@ int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int6
       cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
       w.status.as<long long>(), 0, w.view_cnt.as<uint32_t>(), w.st_u8.as<uint8_t>(), w.st_color.as<float>(),          \
       w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>(), share ? 1 : 0,              \
-      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm, sg)
+      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm, sg, blend_tma())
   if (blend_ppt() == 2) {
     if (out_seg) GSW_BLEND(true, 2); else GSW_BLEND(false, 2);
   } else {

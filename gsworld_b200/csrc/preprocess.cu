@@ -611,28 +611,7 @@ __device__ bool group_culled(const float* __restrict__ b, const ViewSmem& vs, co
 // ---- TMA bulk staging (cp.async.bulk + mbarrier): one elected thread pulls the CTA's contiguous slices of
 // the small per-Gaussian arrays into shared memory in a few large asynchronous copies, so the per-item
 // code never waits on a dependent global load for them (the kernel was latency-bound on exactly those).
-__device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count));
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(mbar)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
-  uint32_t ok;
-  do {
-    asm volatile(
-        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-        : "=r"(ok)
-        : "r"(mbar), "r"(parity)
-        : "memory");
-  } while (!ok);
-}
+// (helpers: gsw_internal.h)
 
 // Per-view constants of the preprocess pass: the view itself plus the numbers of the group-level frustum tests.
 // 48 words; computed by a few designated threads of a 256-thread CTA (compute_view_consts) and, for the static
@@ -973,11 +952,17 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
 // Item handled by thread t in iteration it of a 2048-item chunk.  Items are spatially ordered, so the 256
 // items of a group fall into very few tile bins; letting the 32 lanes of a warp take 4 items from each of
 // the chunk's 8 groups (instead of 32 neighbours) cuts same-address shared-memory atomic conflicts 8-fold.
-// (G = groups per chunk = items per thread)
-template <int G>
+// (G = groups per chunk, NT = threads per CTA: NT / G threads share a group, each takes 256 G / NT of its items)
+template <int G, int NT>
 __device__ __forceinline__ int scatter_slot(int it, int t) {
-  return ((t & (G - 1)) << 8) + it * (256 / G) + t / G;
+  return ((t & (G - 1)) << 8) + it * (NT / G) + t / G;
 }
+// Threads per scatter CTA.  The dynamic layer's heaviest chunks (a gripper close-up: every Gaussian covers dozens of
+// tiles) bound the pass; more warps per chunk shorten exactly those.
+#ifndef GSW_SCATTER_NT_DYN
+#define GSW_SCATTER_NT_DYN 256
+#endif
+constexpr int kScatterThreadsStatic = 256, kScatterThreadsDyn = GSW_SCATTER_NT_DYN;
 
 // (list, chunk) of a scatter CTA's next round.  Plain form: one round, the block indices.  Work-list form (static
 // layer): persistent CTAs take (view, chunk) pairs of cull_chunks_kernel's list by ticket.  CTA-uniform result.
@@ -1005,7 +990,7 @@ __device__ __forceinline__ bool next_chunk(int& list, int& chunk, bool first, co
 }
 
 template <bool DYN, bool WL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(DYN ? kScatterThreadsDyn : kScatterThreadsStatic)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                const float4* __restrict__ recA, const float4* __restrict__ /*recB*/,
                const float4* __restrict__ recC, const int32_t* __restrict__ rad,
@@ -1014,7 +999,9 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
                const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
                uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
-  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic, kItemsPerThread = kItemsPerBlock / 256;  // this layer's chunk
+  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic;  // this layer's chunk
+  constexpr int NT = DYN ? kScatterThreadsDyn : kScatterThreadsStatic, kGroups = kItemsPerBlock / 256;
+  constexpr int kItemsPerThread = kItemsPerBlock / NT;
   extern __shared__ uint32_t dsm[];
   __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
@@ -1029,7 +1016,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
   // groups of the chunk that the preprocess pass found dead were never written: their items count as radius 0.
   // scatter_slot() gives every thread items of ONE group, threadIdx.x & (groups - 1).
-  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & (kItemsPerThread - 1))) & 1u;
+  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & (kGroups - 1))) & 1u;
   if (chunk_mask[chunk_id] == 0u) continue;  // whole chunk culled (CTA-uniform)
   if (use_hist && cta_hist != nullptr) {
     // the preprocess CTA that walked this chunk left its per-bin counts: no second counting pass
@@ -1045,7 +1032,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     __syncthreads();
 #pragma unroll 1
     for (int it = 0; it < kItemsPerThread; ++it) {
-      const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+      const int64_t i = base + scatter_slot<kGroups, NT>(it, threadIdx.x);
       if (i >= n_items || !glive) continue;
       const int64_t item = item_base + (int64_t)list * n_items + i;
       const int radius = rad[item];
@@ -1071,14 +1058,14 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
   float ax[kItemsPerThread], ay[kItemsPerThread], dep[kItemsPerThread];
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+    const int64_t i = base + scatter_slot<kGroups, NT>(it, threadIdx.x);
     radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
     ax[it] = ay[it] = dep[it] = 0.f;
     if (radius[it] > 0) {
-      const int64_t item = item_base + (int64_t)list * n_items + base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+      const int64_t item = item_base + (int64_t)list * n_items + base + scatter_slot<kGroups, NT>(it, threadIdx.x);
       const float4 a = recA[4 * item];
       ax[it] = a.x;
       ay[it] = a.y;
@@ -1090,7 +1077,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
     Rect rc{0, 0, 0, 0};
     uint32_t bk = 0, klo = 0, khi = 0;
     if (radius[it] > 0) {
-      const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+      const int64_t i = base + scatter_slot<kGroups, NT>(it, threadIdx.x);
       rc = tile_rect(ax[it], ay[it], radius[it], g.gx, g.gy);
       klo = ga.key_idx ? (uint32_t)ga.key_idx[i] : (uint32_t)i;
       khi = __float_as_uint(dep[it]);
@@ -1114,7 +1101,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
 // expanded by the whole warp.  Needs the preprocess CTA's bin counts (cta_hist) for the shared-memory slot
 // counters; without them it falls back to global cursors.
 template <bool DYN, bool WL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(DYN ? kScatterThreadsDyn : kScatterThreadsStatic)
 scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                     const float4* __restrict__ recA, const float4* __restrict__ recB,
                     const float4* __restrict__ recC, const int32_t* __restrict__ rad,
@@ -1123,7 +1110,9 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
                     const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                     const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
                     uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
-  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic, kItemsPerThread = kItemsPerBlock / 256;  // this layer's chunk
+  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic;  // this layer's chunk
+  constexpr int NT = DYN ? kScatterThreadsDyn : kScatterThreadsStatic, kGroups = kItemsPerBlock / 256;
+  constexpr int kItemsPerThread = kItemsPerBlock / NT;
   extern __shared__ uint32_t dsm[];
   __shared__ uint32_t s_work;
   const int nbl = g.T * g.NB;
@@ -1136,7 +1125,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   const uint32_t gb = (uint32_t)(list_base + list) * (uint32_t)nbl;
   const int64_t base = (int64_t)chunk * kItemsPerBlock;
   const size_t chunk_id = (size_t)list * (size_t)nchunks + (size_t)chunk;
-  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & (kItemsPerThread - 1))) & 1u;  // see scatter_kernel
+  const bool glive = (chunk_mask[chunk_id] >> (threadIdx.x & (kGroups - 1))) & 1u;  // see scatter_kernel
   if (chunk_mask[chunk_id] == 0u) continue;  // whole chunk culled (CTA-uniform)
   if (use_hist) {
     const uint32_t* keep = cta_hist + chunk_id * (size_t)(nbl + 1);
@@ -1159,7 +1148,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   int radius[kItemsPerThread];
 #pragma unroll
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+    const int64_t i = base + scatter_slot<kGroups, NT>(it, threadIdx.x);
     radius[it] = (i < n_items && glive) ? rad[item_base + (int64_t)list * n_items + i] : 0;
   }
   // The kernel is bound by the latency of its dependent loads (radius -> record -> key store), not by issue: the
@@ -1179,7 +1168,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
     p.depth = 0.f;
     p.key = 0u;
     if (it < kItemsPerThread && radius[it] > 0) {
-      const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+      const int64_t i = base + scatter_slot<kGroups, NT>(it, threadIdx.x);
       const int64_t item = item_base + (int64_t)list * n_items + i;
       p.a = recA[4 * item];
       p.m = *reinterpret_cast<const float2*>(recA + 4 * item + 3);
@@ -1191,7 +1180,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
   Pre nxt = fetch(0);
 #pragma unroll 1
   for (int it = 0; it < kItemsPerThread; ++it) {
-    const int64_t i = base + scatter_slot<kItemsPerThread>(it, threadIdx.x);
+    const int64_t i = base + scatter_slot<kGroups, NT>(it, threadIdx.x);
     const int64_t item = item_base + (int64_t)list * n_items + i;
     const Pre cur = nxt;
     nxt = fetch(it + 1);
@@ -1662,7 +1651,7 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
 #define GSW_LAUNCH_SCATTER(KERNEL_, HIST_, CH_)                                                                     \
   do {                                                                                                            \
     if ((rc = ensure_smem<KERNEL_>((HIST_) ? hist_b : 0, ctx->device))) return rc;                                \
-    KERNEL_<<<grid, 256, (HIST_) ? hist_b : 0, s>>>(                                                              \
+    KERNEL_<<<grid, dynamic ? kScatterThreadsDyn : kScatterThreadsStatic, (HIST_) ? hist_b : 0, s>>>(                                                              \
         ga, n_items, list_base, item_base, g, w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, \
         w.rad.as<int32_t>(), w.bin_off.as<uint32_t>(), w.bin_cursor.as<uint32_t>(),                               \
         w.keys.as<unsigned long long>(), cap, (HIST_) ? 1 : 0, CH_, chunk_mask, nchunks, w.work.as<uint32_t>(),   \
