@@ -404,7 +404,28 @@ def gpu_reference_restated(scene_cpu, dev, n_envs=4, steps=3):
         ras_only()
     torch.cuda.synchronize(dev)
     fps_ras = frames * steps / (time.perf_counter() - t0)
+    # integration level 1: OUR GaussianRasterizer shim called the same way, one frame per
+    # call through gsw_rasterize_forward (no layers, no culling hierarchy, a host wait per call for the overflow check)
+    from gsworld_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    zeros = torch.zeros_like(scene._xyz)
+
+    def ours_single():
+        for c in per:
+            rs = GaussianRasterizationSettings(H, W, c["tanfovx"], c["tanfovy"], bg, 1.0, c["view"], c["proj"], 3,
+                                               c["campos"], False, False, False)
+            ras = GaussianRasterizer(rs)
+            for _ in range(n_envs):
+                ras(scene._xyz, zeros, op, shs=shs, scales=sc, rotations=ro)
+
+    ours_single()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ours_single()
+    torch.cuda.synchronize(dev)
+    fps_ours_single = frames * steps / (time.perf_counter() - t0)
     return {"as_gsworld_calls_it": fps_full, "rasterizer_only": fps_ras, "unit": "frames/s",
+            "ours_single_frame_api": fps_ours_single,
             "sample": f"{n_envs} envs x {len(CAMERAS)} cams x {steps} steps, same scene/cameras, 1 GPU",
             "what": "RESTATED reference-style CUDA pipeline (baseline/ref_rasterizer), not the reference's binary"}
 
@@ -729,7 +750,7 @@ def run_ours(args):
                 # e2e: host (pinned) inputs every step, uint8 observations read back to pinned host memory
                 env_h, wrap_h = build(False, True)
                 pinned = torch.empty((len(CAMERAS), B, H, W, 3), dtype=torch.uint8).pin_memory()
-                # the uint8 observations land in pinned host memory: the library sends each eighth of the frames on its
+                # the uint8 observations land in pinned host memory: the library sends the frames group by group on its
                 # copy stream as soon as the blend kernel has signalled that group complete (obs_host)
                 wrap_h.obs_host = pinned
                 ms_e = timed(env_h, wrap_h, args.steps, args.warmup, d2h="library")

@@ -58,7 +58,11 @@ struct DoneSig {
   uint32_t* flag = nullptr;  // [n] last epoch whose group is complete
   uint32_t epoch = 0;
   int32_t n = 0, F = 0;
-  __host__ __device__ int32_t cut(int k) const { return (int32_t)((int64_t)F * k / n); }
+  int32_t geo = 0;  // 1: group sizes double from group to group (first group small: delivery starts early, few groups)
+  __host__ __device__ int32_t cut(int k) const {
+    if (geo) return (int32_t)((int64_t)F * ((1 << k) - 1) / ((1 << n) - 1));
+    return (int32_t)((int64_t)F * k / n);
+  }
 };
 
 #ifdef __CUDACC__

@@ -104,7 +104,7 @@ typedef struct gsw_frames_desc {
   float* out_invdepth;       /* [F,1,H,W] or NULL */
   int32_t* out_radii;        /* [F,N] or NULL */
   uint8_t* host_rgb_u8;      /* HOST pinned [F,H,W,3] or NULL: needs out_rgb_u8.  The frames are delivered device->host
-                              * in up to 8 groups on the context's copy stream while later frames are still being
+                              * in a few groups of doubling size on the context's copy stream while later frames are still being
                               * composited: the blend stays one launch, the last CTA of a group publishes a flag and
                               * the copy stream waits on it with a stream memory operation (cuStreamWaitValue32).
                               * Where the driver refuses that operation, or with GSW_NO_WAIT_VALUE set in the
