@@ -664,7 +664,8 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
       }
       if (n > kMaxSigGroups) n = kMaxSigGroups;
       if (geo && n > 8) n = 8;
-      while (n > 1 && (geo ? ((int64_t)d->num_frames >> (n - 1)) < 1 : d->num_frames < n)) --n;
+      // every group must hold at least one frame (an empty group's flag would never be published)
+      while (n > 1 && (geo ? (int64_t)d->num_frames < ((int64_t)1 << n) - 1 : d->num_frames < n)) --n;
       sg.n = n;
       sg.geo = geo && n > 1;
     }
@@ -677,6 +678,7 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
                            nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s, &sg)))
       return rc;
     for (int k = 0; k < sg.n; ++k) {
+      if (sg.cut(k + 1) <= sg.cut(k)) continue;  // (cannot happen with the group counts chosen above)
       CUresult wr = CUDA_SUCCESS;
       if (c->wait_value32 != nullptr) {
         wr = wait32((CUstream)c->copy_stream, (CUdeviceptr)(uintptr_t)(sg.flag + k), sg.epoch,
