@@ -746,8 +746,7 @@ int gsw_delivery_gate(gsw_ctx* c, gsw_stream stream) {
   }
   Guard gd(c->device);
   GSW_CUDA(cudaEventRecord(c->gate_evt, (cudaStream_t)stream));
-  GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->gate_evt, 0));
-  GSW_CUDA(cudaStreamWaitEvent(c->peer_stream, c->gate_evt, 0));
+  GSW_CUDA(cudaStreamWaitEvent(c->peer_stream, c->gate_evt, 0));  // (copies to this process' host memory need no gate)
   return GSW_OK;
 }
 

@@ -217,7 +217,7 @@ class Engine:
         _lib.check(self.lib.gsw_delivery_wait(self._h, st))
 
     def delivery_gate(self, stream=None):
-        """The next launch's host copies / peer pushes start only after the work enqueued so far on `stream`
+        """The next launch's peer pushes start only after the work enqueued so far on `stream`
         (a torch stream; default: the current one) has completed."""
         st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
         _lib.check(self.lib.gsw_delivery_gate(self._h, st))

@@ -144,8 +144,8 @@ int gsw_finish(gsw_ctx* ctx, int64_t* needed_entries, int64_t stats[4]);
 /* Make `stream` wait for the delivery (host_rgb_u8 / peer_rgb_u8) of the last gsw_render_frames call; a no-op if
  * that call delivered nothing.  Needed only with GSW_DELIVER_NO_JOIN.  No counterpart in the reference. */
 int gsw_delivery_wait(gsw_ctx* ctx, gsw_stream stream);
-/* The reverse ordering: the host copies / peer pushes of the NEXT gsw_render_frames call on this context start only
- * after everything enqueued on `stream` so far has completed (the compositing itself is not held back).  A multi-GPU
+/* The reverse ordering: the peer pushes (peer_rgb_u8) of the NEXT gsw_render_frames call on this context start only
+ * after everything enqueued on `stream` so far has completed (the compositing and the host copies are not held back).  A multi-GPU
  * exchange calls it with the stream that ran the previous step's cross-rank barrier, so that a peer's buffer is not
  * overwritten while that peer may still be reading it.  No counterpart in the reference (single GPU). */
 int gsw_delivery_gate(gsw_ctx* ctx, gsw_stream stream);
