@@ -5,8 +5,10 @@ Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]` pri
 Workload = BASELINE.json configs[2]: PnpBoxFr3Env-v1-shaped step, fr3_umi, 64 envs x 2 cameras
 (wrist + third-person) x 256x256, synthetic 1M-Gaussian scene (SURVEY.md §8d generator), per GPU.
 A "step" = compose the (env, link/object) pose table + render every (env, camera) frame to uint8.
-Multi-GPU: envs are sharded by rank (64 per rank, weak scaling), scene replicated, and each step ends
-with one NCCL all-gather of the uint8 observations (the only exchange on the path).
+Multi-GPU: envs are sharded by rank (cfg3: 64 per rank, weak scaling, plus a `strong` leg with 64 envs in total;
+other --config values shard their stated env count), scene replicated, and every step delivers the uint8
+observations to the policy rank (the only exchange on the path): copy-engine pushes into peer memory overlapped
+with the blend (gsworld_b200/dist.py), verified once against an NCCL all-gather; NCCL all-gather as the fallback.
 
 --impl reference: the reference's own path restated on the host cores (oracle/: torch transform with
 deepcopy + isin write-back per frame, CPU rasterizer) on a bounded sample of the same workload.
