@@ -456,6 +456,11 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              const int32_t* __restrict__ st_seg, int use_view_images, const float4* __restrict__ rec,
              const int32_t* __restrict__ pos_of, int64_t Ns, const int32_t* __restrict__ labels, int64_t Nm,
              DoneSig sig, int tma_stage) {
+  if (sig.times != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    sig.times[16] = t;
+  }
   blend_body<SEG, PPT>(bin_off, nbins, frame_view, V, f_begin, keys, splats, cap, g, bg0, bg1, bg2, bg_dev, out_u8,
                   out_color, out_invd, status, mode, view_cnt, st_u8, st_color, st_invd, lab_stream, out_seg, st_seg,
                   use_view_images, rec, pos_of, Ns, labels, Nm, tma_stage);
@@ -475,6 +480,11 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
       uint32_t old;
       asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(sig.cnt + k) : "memory");
       if (old == ctas - 1u) {
+        if (sig.times != nullptr) {
+          unsigned long long t;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+          sig.times[k] = t;
+        }
         __threadfence();  // acquire side, once per group: the other CTAs' releases on the counter happen-before the flag
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sig.flag + k), "r"(sig.epoch) : "memory");
       }

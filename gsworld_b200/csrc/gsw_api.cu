@@ -318,8 +318,9 @@ int gsw_create(int device, gsw_ctx** out) {
       c->wait_value32 = fn;
     else
       (void)cudaGetLastError();
-    if (c->sig.reserve(2 * kMaxSigGroups * sizeof(uint32_t)) != 0) c->wait_value32 = nullptr;
-    else e = cudaMemset(c->sig.p, 0, 2 * kMaxSigGroups * sizeof(uint32_t));
+    // counters [16] + flags [16] + (tuning aid) completion times [17] as 64-bit words
+    if (c->sig.reserve(2 * kMaxSigGroups * sizeof(uint32_t) + 32 * 8) != 0) c->wait_value32 = nullptr;
+    else e = cudaMemset(c->sig.p, 0, 2 * kMaxSigGroups * sizeof(uint32_t) + 32 * 8);
   }
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side2_stream, cudaStreamNonBlocking);
@@ -673,6 +674,8 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     sg.flag = c->sig.as<uint32_t>() + kMaxSigGroups;
     sg.epoch = ++c->sig_epoch;
     sg.F = d->num_frames;
+    static const bool sig_times = getenv("GSW_SIG_TIMES") != nullptr;
+    if (sig_times) sg.times = reinterpret_cast<unsigned long long*>(c->sig.as<uint32_t>() + 2 * kMaxSigGroups);
     GSW_CUDA(cudaMemsetAsync(sg.cnt, 0, kMaxSigGroups * sizeof(uint32_t), s));
     if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
                            nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s, &sg)))
@@ -757,6 +760,14 @@ int gsw_finish(gsw_ctx* c, int64_t* needed_entries, int64_t stats[4]) {
   }
   Guard gd(c->device);
   GSW_CUDA(cudaEventSynchronize(c->done_evt));
+  if (getenv("GSW_SIG_TIMES") != nullptr && c->sig.p != nullptr) {  // tuning aid: when each delivery group completed
+    unsigned long long t[17];
+    if (cudaMemcpy(t, c->sig.as<uint32_t>() + 2 * kMaxSigGroups, sizeof t, cudaMemcpyDeviceToHost) == cudaSuccess) {
+      fprintf(stderr, "[gsw] delivery groups completed at (us after the blend's first CTA):");
+      for (int k = 0; k < 16 && t[k] >= t[16] && t[k] != 0; ++k) fprintf(stderr, " %.0f", (double)(t[k] - t[16]) * 1e-3);
+      fprintf(stderr, "\n");
+    }
+  }
   const int64_t D = c->h_status[0], M = 0, ovf = c->h_status[2];
   if (needed_entries) *needed_entries = D + M;
   if (stats) {

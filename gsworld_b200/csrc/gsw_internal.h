@@ -58,6 +58,7 @@ struct DoneSig {
   uint32_t* flag = nullptr;  // [n] last epoch whose group is complete
   uint32_t epoch = 0;
   int32_t n = 0, F = 0;
+  unsigned long long* times = nullptr;  // tuning aid (GSW_SIG_TIMES): [n] globaltimer at a group's completion, [16] first CTA's start
   int32_t geo = 0;  // 1: group sizes double from group to group (first group small: delivery starts early, few groups)
   __host__ __device__ int32_t cut(int k) const {
     if (geo) return (int32_t)((int64_t)F * ((1 << k) - 1) / ((1 << n) - 1));
