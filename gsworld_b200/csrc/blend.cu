@@ -444,8 +444,11 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
 }
 
 // The kernel proper: blend_body, then (delivery to the host only) the group-completion signal.
+#ifndef GSW_BLEND_CTAS
+#define GSW_BLEND_CTAS 8
+#endif
 template <bool SEG, int PPT>
-__global__ void __launch_bounds__(256 / PPT, PPT == 1 ? 5 : 8)  // 48 / 64 registers: 40 / 32 warps per SM
+__global__ void __launch_bounds__(256 / PPT, PPT == 1 ? 5 : GSW_BLEND_CTAS)  // 48 / 64 registers: 40 / 32 warps per SM
 blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* __restrict__ frame_view, int32_t V,
              int32_t f_begin, const unsigned long long* __restrict__ keys, const Splat* __restrict__ splats,
              int64_t cap, FrameGeom g, float bg0, float bg1, float bg2, const float* __restrict__ bg_dev,
