@@ -139,7 +139,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   const int64_t mc = (int64_t)g.T + 1;
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
-  if ((rc = w.status.reserve(128))) return rc;
+  if ((rc = w.status.reserve(256))) return rc;
   const size_t chs = cta_hist_words(Ns, V, g, false), chd = dyn ? cta_hist_words(Nm, F, g, true) : 0;
   if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
   uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;
@@ -157,7 +157,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
 
   GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
   GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
-  GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 128, s));
+  GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 256, s));
   auto mark = [&](int k) {
     if (ctx->profile) cudaEventRecord(ctx->stage_evt[k], s);
   };
@@ -268,7 +268,7 @@ int join_side(gsw_ctx* ctx, cudaStream_t s) {
 }
 
 int finish_launch(gsw_ctx* ctx, cudaStream_t s) {
-  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 12 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  GSW_CUDA(cudaMemcpyAsync(ctx->h_status, ctx->ws.status.p, 18 * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
   GSW_CUDA(cudaEventRecord(ctx->done_evt, s));
   ctx->launches++;
   return 0;
@@ -300,7 +300,7 @@ int gsw_create(int device, gsw_ctx** out) {
   Guard gd(device);
   gsw_ctx* c = new gsw_ctx();
   c->device = device;
-  cudaError_t e = cudaMallocHost((void**)&c->h_status, 16 * sizeof(int64_t));
+  cudaError_t e = cudaMallocHost((void**)&c->h_status, 32 * sizeof(int64_t));
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->done_evt, cudaEventDisableTiming);
   for (int k = 0; k <= kNumStages && e == cudaSuccess; ++k) e = cudaEventCreate(&c->stage_evt[k]);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
@@ -331,7 +331,7 @@ int gsw_create(int device, gsw_ctx** out) {
     delete c;
     return (int)e;
   }
-  memset(c->h_status, 0, 16 * sizeof(int64_t));
+  memset(c->h_status, 0, 32 * sizeof(int64_t));
   *out = c;
   return GSW_OK;
 }
@@ -859,6 +859,10 @@ int gsw_profile_counters(gsw_ctx* c, int64_t* out, int n) {
   out[0] = c->h_status[4];  // (record, pixel) pair evaluations of the blend (incl. the view pass)
   out[1] = c->h_status[3];  // entries staged by the blend
   if (n >= 3) out[2] = (int64_t)(uint32_t)c->h_status[10];  // live (view, chunk) pairs of the static layer's work list
+  if (n >= 5) {
+    out[3] = c->h_status[16];  // visible static Gaussian-views (records written by the static preprocess)
+    out[4] = c->h_status[17];  // visible movable Gaussian-frames
+  }
   return GSW_OK;
 }
 
@@ -1019,7 +1023,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.merge_off, (size_t)(kNaMaxTiles + 1) * 4);
   carve(w.keys, (size_t)kNaMaxEntries * 8);
   carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
-  carve(w.status, 128);
+  carve(w.status, 256);
   carve(w.seg_queue, 2 * seg_queue_bytes(kNaMaxEntries, nbins));
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view

@@ -187,7 +187,7 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
                                                 float4* __restrict__ recA, float4* __restrict__ recB,
                                                 float4* __restrict__ recC, int32_t* __restrict__ rad,
                                                 uint32_t* __restrict__ bin_count, uint32_t* hist, Rect& out_rc,
-                                                uint32_t& out_bk, Foot& out_ft) {
+                                                uint32_t& out_bk, Foot& out_ft, uint32_t* s_vis) {
   // CULL: the caller counts the Gaussian into its bins (warp-cooperatively, with the exact tile test) from
   // out_rc / out_bk / out_ft, which stay empty on every early return
   if (!DYN && la.slot != nullptr && la.slot[il] >= 0) {  // movable: handled by the dynamic layer
@@ -419,6 +419,10 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
     hy = sqrtf(2.f * tau * cz) * 1.001f + 0.01f;
   }
 
+  {  // measurement counter: one shared-memory atomic per warp for the lanes that reach this point together
+    const unsigned m = __activemask();
+    if ((threadIdx.x & 31) == __ffs(m) - 1) atomicAdd(s_vis, (uint32_t)__popc(m));
+  }
   recA[4 * item] = make_float4(px, py, hx, hy);
   recB[4 * item] = make_float4(conx, cony, conz, opac);
   recC[4 * item] = make_float4(rgb[0], rgb[1], rgb[2], pvz);
@@ -761,7 +765,7 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
                   uint32_t* __restrict__ chunk_mask, int32_t nchunks, const uint32_t* __restrict__ work,
                   const uint32_t* __restrict__ work_count, uint32_t* __restrict__ ticket,
                   const uint32_t* __restrict__ view_consts, const uint32_t* __restrict__ order,
-                  uint32_t* __restrict__ cost) {
+                  uint32_t* __restrict__ cost, unsigned long long* __restrict__ vis_count) {
   static_assert(!(WL && DYN), "the work-list form is the static layer's");
   constexpr int use_tma = TMA ? 1 : 0;
   __shared__ ViewConsts vcs;
@@ -769,7 +773,8 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
   ViewCull& vc = vcs.vc;
   __shared__ __align__(8) unsigned long long mbar_s;
   __shared__ uint32_t s_work;
-  __shared__ uint32_t s_cost;
+  __shared__ uint32_t s_cost, s_vis;
+  if (threadIdx.x == 0) s_vis = 0u;  // visible items of this CTA (measurement counter, flushed once at exit)
   if (threadIdx.x == 0) s_cost = 0u;  // (cost is only kept by the one-round forms; a barrier follows before its use)
   extern __shared__ __align__(128) unsigned char dsm_raw[];
   constexpr int IPT = IPB / 256;
@@ -899,10 +904,10 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
         const int64_t item = item_base + (int64_t)list * n_items + i;
         if (TMA) {
           preprocess_item<DYN, CULL>(ga, la, i, staged ? (int64_t)il : i, item, list_base + list, g, vs, pose_s, recA,
-                                     recB, recC, rad, bin_count, hist, rc, bk, ft);
+                                     recB, recC, rad, bin_count, hist, rc, bk, ft, &s_vis);
         } else {  // same object for both roles: every load stays a read-only global load
           preprocess_item<DYN, CULL>(ga, ga, i, i, item, list_base + list, g, vs, pose_s, recA, recB, recC, rad,
-                                     bin_count, hist, rc, bk, ft);
+                                     bin_count, hist, rc, bk, ft, &s_vis);
         }
       }
       if (CULL) {  // count into the bins of the tiles that pass the exact test (all 32 lanes arrive here)
@@ -941,6 +946,8 @@ preprocess_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t it
     if (!WL) break;
     __syncthreads();  // staged arrays, histogram and view constants are rewritten by the next round
   }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_vis) atomicAdd(vis_count, (unsigned long long)s_vis);
 }
 
 // Second pass: write (depth bits << 32 | original index) into the bin's slice.  Order inside a bin is
@@ -1598,7 +1605,8 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
         w.rec.as<float4>(), w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(),                  \
         w.bin_count.as<uint32_t>(), use_hist, use_hist ? cta_hist : nullptr, chunk_mask, nchunks,                 \
         w.work.as<uint32_t>(), st32 + kWorkCountWord, st32 + kPreTicketWord, w.view_consts.as<uint32_t>(),       \
-        order, (use_hist && cta_hist != nullptr) ? cost : nullptr);                                                \
+        order, (use_hist && cta_hist != nullptr) ? cost : nullptr,                                                 \
+        w.status.as<unsigned long long>() + (dynamic ? 17 : 16));                                                  \
   } while (0)
   const bool cull = g.tile_cull != 0;
   if (dynamic) {

@@ -288,9 +288,10 @@ class Engine:
 
     def counters(self):
         """Work counters of the last launch: blend pair evaluations, entries staged."""
-        buf = (C.c_int64 * 3)()
-        _lib.check(self.lib.gsw_profile_counters(self._h, buf, 3))
-        return {"blend_pairs": int(buf[0]), "blend_staged": int(buf[1]), "static_chunks_live": int(buf[2])}
+        buf = (C.c_int64 * 5)()
+        _lib.check(self.lib.gsw_profile_counters(self._h, buf, 5))
+        return {"blend_pairs": int(buf[0]), "blend_staged": int(buf[1]), "static_chunks_live": int(buf[2]),
+                "visible_static": int(buf[3]), "visible_dynamic": int(buf[4])}
 
     def kernel_launches(self) -> int:
         return int(self.lib.gsw_kernel_launches())
