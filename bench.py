@@ -477,6 +477,10 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        from gsworld_b200.dist import bind_to_gpu_numa_node
+        numa = bind_to_gpu_numa_node(local)  # before any pinned allocation: host buffers local to the GPU's socket
+        if os.environ.get("GSW_BENCH_DEBUG"):
+            log(f"[rank {rank}] {numa}")
         dist.init_process_group("nccl", device_id=dev)
     scene_cpu = make_scene()
     scene = scene_cpu.to(dev)
@@ -556,9 +560,9 @@ def run_ours(args):
                 xchg.begin(k, wrap._engine)
                 wrap.obs_out = xchg.local_out(k)  # composite straight into this rank's slot of its own buffer
                 wrap.obs_peers = xchg.destinations(k)
-                # asynchronous legs: the render stream does not wait for the pushes; the host-synchronous e2e leg
-                # joins them (the host reads its own frames right after)
-                wrap.defer_delivery_join = not wrap.sync_each_step
+                # asynchronous legs: the render stream does not wait for the delivery; the host-synchronous e2e leg
+                # waits for its own host copy (it reads the frames right after) but not for the pushes to the policy rank
+                wrap.defer_delivery_join = True if not wrap.sync_each_step else "peers"
                 out = wrap._render_gsworld()
                 consume(k - 1)  # one step behind, while step k is still being composited
                 xchg.publish(k, wrap._engine)  # after xchg.wait_ready(k), xchg.gathered(k) holds every rank's frames

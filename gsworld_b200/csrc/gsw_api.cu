@@ -638,14 +638,14 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   };
   // the copy stream's completion event covers both delivery streams
   auto close_delivery = [&]() -> int {
-    if (n_peer > 0) {
-      GSW_CUDA(cudaEventRecord(c->peer_evt, c->peer_stream));
-      GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->peer_evt, 0));
-    }
+    c->delivered_peer = n_peer > 0;
+    if (n_peer > 0) GSW_CUDA(cudaEventRecord(c->peer_evt, c->peer_stream));
     GSW_CUDA(cudaEventRecord(c->copy_evt, c->copy_stream));
     c->delivered = true;
-    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN))
-      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));  // `stream` order covers the delivery
+    if (!(d->deliver_flags & GSW_DELIVER_NO_JOIN)) {  // `stream` order covers the delivery
+      GSW_CUDA(cudaStreamWaitEvent(s, c->copy_evt, 0));
+      if (n_peer > 0 && !(d->deliver_flags & GSW_DELIVER_NO_PEER_JOIN)) GSW_CUDA(cudaStreamWaitEvent(s, c->peer_evt, 0));
+    }
     return 0;
   };
   if (deliver && c->wait_value32 != nullptr) {
@@ -739,6 +739,7 @@ int gsw_delivery_wait(gsw_ctx* c, gsw_stream stream) {
   if (!c->delivered) return GSW_OK;
   Guard gd(c->device);
   GSW_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->copy_evt, 0));
+  if (c->delivered_peer) GSW_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->peer_evt, 0));
   return GSW_OK;
 }
 

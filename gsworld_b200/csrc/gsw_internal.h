@@ -226,6 +226,7 @@ struct gsw_ctx {
   cudaEvent_t gate_evt = nullptr;  // gsw_delivery_gate
   cudaEvent_t copy_evt = nullptr;
   bool delivered = false;  // copy_evt has been recorded by a delivery
+  bool delivered_peer = false;  // ... and peer_evt (the last delivery pushed to peers)
   // static-layer kernels (preprocess, scatter) run on side_stream next to the dynamic-layer ones: they are
   // independent until the scan / the sort, and each leaves a good part of the SMs idle on its own
   cudaStream_t side_stream = nullptr;

@@ -15,6 +15,41 @@ import torch
 import torch.distributed as dist
 
 
+def bind_to_gpu_numa_node(device_index: int) -> str:
+    """Pin the calling process to the CPUs that are local to GPU `device_index` (its PCIe root's NUMA node).
+
+    With one process per GPU on a two-socket box, pinned host buffers are first-touched, and the per-step H2D / D2H
+    copies are driven, from whatever core the scheduler picked; half the ranks then cross the socket interconnect with
+    every observation batch.  Call before allocating pinned memory.  Returns a short description (also when nothing
+    could be done: no NVML, no sysfs entry, a single node)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[device_index]) if vis and vis.split(",")[device_index].strip().isdigit() else device_index
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(phys)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bdf = bus.lower()[-12:]  # 0000:xx:yy.z
+        with open(f"/sys/bus/pci/devices/{bdf}/local_cpulist") as f:
+            txt = f.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if not use or use == allowed:
+            return f"gpu {device_index} ({bdf}): no narrower local CPU set ({txt})"
+        os.sched_setaffinity(0, use)
+        return f"gpu {device_index} ({bdf}): bound to {len(use)} local CPUs ({txt})"
+    except Exception as e:  # noqa: BLE001
+        return f"gpu {device_index}: not bound ({e!r})"
+
+
 def shard_envs(num_envs: int, rank: int, world: int) -> Tuple[int, int]:
     """[lo, hi) of the envs rank `rank` owns; blocks differ by at most one env."""
     if not (0 <= rank < world):

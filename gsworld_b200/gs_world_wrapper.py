@@ -181,8 +181,9 @@ class GSWorldWrapper(_Base):
         # process, e.g. dist.PeerObservationExchange.destinations()): the observations are also pushed there group
         # by group on the copy stream while later frames are still being blended (gsw_frames_desc.peer_rgb_u8).
         self.obs_peers = None
-        # With obs_host / obs_peers: do not make the render stream wait for the delivery (GSW_DELIVER_NO_JOIN); the
-        # caller orders consumers with engine.delivery_wait() and must give a persistent obs_out.
+        # With obs_host / obs_peers: True = do not make the render stream wait for the delivery (GSW_DELIVER_NO_JOIN);
+        # "peers" = wait for the host copy but not for the peer pushes (GSW_DELIVER_NO_PEER_JOIN).  The caller orders
+        # consumers with engine.delivery_wait() and must give a persistent obs_out.
         self.defer_delivery_join = False
         if merged_model is None and cfg_dir is not None:
             # reference path: GaussianModelMerger().load_models_from_config(CFG_DIR/<name>.json) + merge_models()
@@ -474,7 +475,7 @@ class GSWorldWrapper(_Base):
                 self.obs_host.view(len(names) * self.num_envs, H, W, 3),
                 peer_rgb_u8=None if (not self.obs_peers or len(groups) != 1) else
                 [t.view(len(names) * self.num_envs, H, W, 3) for t in self.obs_peers],
-                defer_delivery_join=bool(self.defer_delivery_join and dst is not None))
+                defer_delivery_join=(self.defer_delivery_join if dst is not None else False))
             rgb = out["rgb_u8"].view(len(names), self.num_envs, H, W, 3)
             for i, c in enumerate(names):
                 gs_renders[c] = rgb[i]

@@ -131,6 +131,10 @@ typedef struct gsw_frames_desc {
 } gsw_frames_desc;
 
 #define GSW_DELIVER_NO_JOIN 1
+/* `stream` waits for the host copies of this call but NOT for its peer pushes: a host that reads its own frames after
+ * every step then does not sit on the NVLink traffic and the cross-rank flow control behind it; whoever consumes the
+ * pushed frames (and whoever overwrites out_rgb_u8) is ordered with gsw_delivery_wait as with GSW_DELIVER_NO_JOIN. */
+#define GSW_DELIVER_NO_PEER_JOIN 2
 
 /* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous. */
 int gsw_render_frames(gsw_ctx* ctx, const gsw_frames_desc* desc, gsw_stream stream);
