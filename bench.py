@@ -753,6 +753,14 @@ def run_ours(args):
                     "value": world * F * args.steps / (ms_full * 1e-3), "ms_per_step": ms_full / args.steps,
                     "D": int(eng.last_stats["D"])}
                 eng.set_tile_culling(True)
+                # ... and with the static-list cache off: the world-fixed camera's static lists rebuilt every step
+                os.environ["GSW_NO_STATIC_CACHE"] = "1"
+                try:
+                    ms_nc = timed(env, wrap, args.steps, args.warmup)
+                finally:
+                    os.environ.pop("GSW_NO_STATIC_CACHE", None)
+                results[mode]["static_cache_off"] = {"value": world * F * args.steps / (ms_nc * 1e-3),
+                                                     "ms_per_step": ms_nc / args.steps}
             if mode == "strict":
                 results[mode].update(clocks=clocks, launches=launches)
                 if lean:
@@ -878,6 +886,11 @@ def run_ours(args):
             "counts": {"N": N_GAUSS, "movable": Nm, "D": D, "D_shared_static": r["D_shared_static"],
                        "blend_staged": R, "visible_static": r.get("vis_s"), "visible_dynamic": r.get("vis_d")},
             "reference_tile_lists": r.get("reference_tile_lists"),
+            "static_list_cache": {"on": os.environ.get("GSW_NO_STATIC_CACHE") is None,
+                                  "what": "static lists / static-only tiles of a view are kept from the previous step "
+                                          "while its camera is bitwise unchanged (the world-fixed third-person camera; "
+                                          "the wrist camera and every movable Gaussian change each step); same bytes out",
+                                  "off": r.get("static_cache_off")},
             "per_env_cameras": {"value": results["per_env"]["fps"], "ms_per_step": results["per_env"]["ms"] / args.steps,
                                 "views": results["per_env"]["V"],
                                 "stages_ms": {k: round(v, 4) for k, v in results["per_env"]["stages"].items()},

@@ -264,9 +264,10 @@ gather_splats_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int32_
                      int32_t bins_per_list, const int32_t* __restrict__ pos_of,
                      const u64* __restrict__ keys, const float4* __restrict__ rec, Splat* __restrict__ splats,
                      int64_t cap, const int32_t* __restrict__ labels, int32_t* __restrict__ lab_stream,
-                     const uint32_t* __restrict__ view_cnt) {
+                     const uint32_t* __restrict__ view_cnt, const uint32_t* __restrict__ cache_m) {
   const int v = blockIdx.y;
   if (view_cnt[v] < 2u) return;  // fetched lazily by the blend
+  if (cache_m != nullptr && (uint32_t)v < *cache_m) return;  // gathered in an earlier step, still in place
   if ((int64_t)bin_off[nbins] > cap) return;
   const uint32_t p0 = bin_off[(int64_t)v * bins_per_list], p1 = bin_off[(int64_t)(v + 1) * bins_per_list];
   for (uint32_t p = p0 + blockIdx.x * blockDim.x + threadIdx.x; p < p1; p += gridDim.x * blockDim.x) {
@@ -295,9 +296,11 @@ struct Queues {
 };
 
 __global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, int64_t cap, Queues Q,
-                                     long long* __restrict__ status) {
+                                     long long* __restrict__ status, const uint32_t* __restrict__ cache_m,
+                                     int32_t bins_per_list) {
   const int64_t bin = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (bin >= nbins) return;
+  if (cache_m != nullptr && bin < (int64_t)*cache_m * bins_per_list) return;  // list kept (and sorted) from the last step
   const uint32_t start = bin_off[bin], end = bin_off[bin + 1];
   if (end <= start || (int64_t)end > cap) return;
   const uint32_t n = end - start;
@@ -312,6 +315,7 @@ __global__ void classify_bins_kernel(const uint32_t* __restrict__ bin_off, int64
     Q.q[k][slot] = sg;
   } else {
     status[2] = 3;
+    status[kStatusPoison] = 1;
   }
 }
 
@@ -450,6 +454,7 @@ refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ spl
             ++n_big;
           } else {
             status[2] = 2;
+            status[kStatusPoison] = 1;
           }
           return;
         }
@@ -464,6 +469,7 @@ refine_big_bins_kernel(Queues Q, u64* __restrict__ keys, Splat* __restrict__ spl
           Q.q[k][q] = sg;
         } else {
           status[2] = 3;
+          status[kStatusPoison] = 1;
         }
       };
       for (int k = 0; k < kRefineBuckets; ++k) {
@@ -569,7 +575,7 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t*
 // calls on two streams at the same time; set 0 with the full bin range is the single-call form.  `side`: a stream
 // this call may fork onto for the refinement and the medium class (s itself: everything in order on s).
 int launch_sort_bins(const gsw_ctx* ctx, int64_t bin0, int64_t nb, int64_t cap, int set, cudaStream_t s,
-                     cudaStream_t side) {
+                     cudaStream_t side, int32_t bins_per_list) {
   if (nb <= 0) return 0;
   auto& w = ctx->ws;
   constexpr size_t smem_m = (size_t)kSortSmemKeys * sizeof(unsigned long long);  // 32 KB
@@ -594,8 +600,10 @@ int launch_sort_bins(const gsw_ctx* ctx, int64_t bin0, int64_t nb, int64_t cap, 
   // status words (zeroed every launch): set 0 -> counters 12..15, tickets 16..18; set 1 -> 24..27, 28..30
   Q.count = w.status.as<uint32_t>() + (set ? 24 : 12);
   uint32_t* ticket = w.status.as<uint32_t>() + (set ? 28 : 16);
-  classify_bins_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, s>>>(w.bin_off.as<uint32_t>() + bin0, nb, cap, Q,
-                                                                   w.status.as<long long>());
+  // (the kept prefix of the static lists starts at bin 0: only a call whose range starts there may skip it)
+  classify_bins_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, s>>>(
+      w.bin_off.as<uint32_t>() + bin0, nb, cap, Q, w.status.as<long long>(),
+      (ctx->cache_on && bin0 == 0) ? w.cache_m.as<uint32_t>() : nullptr, bins_per_list);
   // the depth partition of the huge bins (one CTA per bin, half the SMs idle) runs on the side stream next to
   // the small-class sort, which does not depend on it; the mid / medium queues it appends to are sorted after
   cudaStream_t ss = side ? side : s;
@@ -636,7 +644,7 @@ int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int6
   gather_splats_kernel<<<dim3(per_view, (unsigned)V), 256, 0, s>>>(
       w.bin_off.as<uint32_t>(), nbins, V, Ns, bpl, ctx->last.pos_of, w.keys.as<unsigned long long>(),
       w.rec.as<float4>(), w.splats.as<Splat>(), cap, ctx->labels, with_labels ? w.lab_stream.as<int32_t>() : nullptr,
-      w.view_cnt.as<uint32_t>());
+      w.view_cnt.as<uint32_t>(), ctx->cache_on ? w.cache_m.as<uint32_t>() : nullptr);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;

@@ -118,7 +118,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
              const float* __restrict__ st_color, const float* __restrict__ st_invd,
              const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg, const int32_t* __restrict__ st_seg,
              int use_view_images, const float4* __restrict__ rec, const int32_t* __restrict__ pos_of, int64_t Ns,
-             const int32_t* __restrict__ labels, int64_t Nm, int tma_stage) {
+             const int32_t* __restrict__ labels, int64_t Nm, int tma_stage, const uint32_t* __restrict__ cache_m) {
   // Only static lists of views shared by several frames are materialised as a splat stream
   // (gather_splats_kernel); for every other list this kernel fetches the records of the entries it actually
   // reaches (about 70 % of them at cfg3, a quarter with per-env cameras) from the per-item records through
@@ -150,6 +150,7 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
 
   const int v = mode == 1 ? f : (frame_view ? frame_view[f] : 0);
   if (mode == 1 && view_cnt[v] < 2u) return;  // view used by a single frame: nothing to share
+  if (mode == 1 && cache_m != nullptr && (uint32_t)v < *cache_m) return;  // static-only tiles kept from the last step
   // bin indices fit 32 bits (run_pipeline rejects launches with 2^31 bins or more)
   const uint32_t sb = ((uint32_t)v * (uint32_t)g.T + (uint32_t)tile) * (uint32_t)g.NB;
   const uint32_t db = ((uint32_t)(V + f) * (uint32_t)g.T + (uint32_t)tile) * (uint32_t)g.NB;
@@ -159,7 +160,10 @@ blend_body(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t* _
   if ((int64_t)D > cap) ns = nd = 0;  // workspace overflow: lists are incomplete; the launch is flagged invalid
   if (mode == 0 && f == 0 && tile == 0 && threadIdx.x == 0) {
     status[0] = (long long)D;
-    if ((int64_t)D > cap) status[2] = 1;
+    if ((int64_t)D > cap) {
+      status[2] = 1;
+      status[kStatusPoison] = 1;  // the static-list cache must not keep anything of this launch
+    }
   }
   const bool lazyA = mode == 0 && view_cnt[v] < 2u;
   constexpr bool lazyD = true;  // dynamic lists are never materialised
@@ -458,7 +462,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
              const float* __restrict__ st_invd, const int32_t* __restrict__ lab_stream, int32_t* __restrict__ out_seg,
              const int32_t* __restrict__ st_seg, int use_view_images, const float4* __restrict__ rec,
              const int32_t* __restrict__ pos_of, int64_t Ns, const int32_t* __restrict__ labels, int64_t Nm,
-             DoneSig sig, int tma_stage) {
+             DoneSig sig, int tma_stage, const uint32_t* __restrict__ cache_m) {
   if (sig.times != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -466,7 +470,7 @@ blend_kernel(const uint32_t* __restrict__ bin_off, int64_t nbins, const int32_t*
   }
   blend_body<SEG, PPT>(bin_off, nbins, frame_view, V, f_begin, keys, splats, cap, g, bg0, bg1, bg2, bg_dev, out_u8,
                   out_color, out_invd, status, mode, view_cnt, st_u8, st_color, st_invd, lab_stream, out_seg, st_seg,
-                  use_view_images, rec, pos_of, Ns, labels, Nm, tma_stage);
+                  use_view_images, rec, pos_of, Ns, labels, Nm, tma_stage, cache_m);
   if (sig.cnt != nullptr) {
     // every thread's pixel stores precede the barrier; thread 0's release makes them visible device-wide (and to
     // the copy engine) before the counter moves; the CTA that completes a group publishes the epoch
@@ -531,7 +535,7 @@ int launch_blend_view_pass(const gsw_ctx* ctx, int32_t V, int32_t F, int64_t nbi
       want_color ? w.st_color.as<float>() : nullptr, want_invd ? w.st_invd.as<float>() : nullptr,                   \
       w.status.as<long long>(), 1, w.view_cnt.as<uint32_t>(), nullptr, nullptr, nullptr, w.lab_stream.as<int32_t>(), \
       want_seg ? w.st_seg.as<int32_t>() : nullptr, nullptr, 0, w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns,    \
-      ctx->labels, ctx->last.Nm, DoneSig{}, blend_tma())
+      ctx->labels, ctx->last.Nm, DoneSig{}, blend_tma(), ctx->cache_on ? w.cache_m.as<uint32_t>() : nullptr)
   if (blend_ppt() == 2) {
     if (want_seg) GSW_VIEW_PASS(true, 2); else GSW_VIEW_PASS(false, 2);
   } else {
@@ -559,7 +563,7 @@ int launch_blend(const gsw_ctx* ctx, int32_t V, int32_t f_begin, int32_t F, int6
       cap, g, bg ? bg[0] : 0.f, bg ? bg[1] : 0.f, bg ? bg[2] : 0.f, bg_dev, out_u8, out_color, out_invdepth,          \
       w.status.as<long long>(), 0, w.view_cnt.as<uint32_t>(), w.st_u8.as<uint8_t>(), w.st_color.as<float>(),          \
       w.st_invd.as<float>(), w.lab_stream.as<int32_t>(), out_seg, w.st_seg.as<int32_t>(), share ? 1 : 0,              \
-      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm, sg, blend_tma())
+      w.rec.as<float4>(), ctx->last.pos_of, ctx->last.Ns, ctx->labels, ctx->last.Nm, sg, blend_tma(), nullptr)
   if (blend_ppt() == 2) {
     if (out_seg) GSW_BLEND(true, 2); else GSW_BLEND(false, 2);
   } else {

@@ -48,6 +48,7 @@ int DevBuf::reserve(size_t need) {
     return (int)e;
   }
   bytes = want;
+  ++gen;
   return 0;
 }
 
@@ -139,7 +140,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   const int64_t mc = (int64_t)g.T + 1;
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
-  if ((rc = w.status.reserve(256))) return rc;
+  if ((rc = w.status.reserve(kStatusBytes))) return rc;
   const size_t chs = cta_hist_words(Ns, V, g, false), chd = dyn ? cta_hist_words(Nm, F, g, true) : 0;
   if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
   uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;
@@ -155,8 +156,49 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   // every one but the last of a bin pairs with a neighbour to more than kSortSmemKeys / 2 entries
   if ((rc = w.seg_queue.reserve(2 * seg_queue_bytes(cap, nbins)))) return rc;  // two independent queue sets
 
-  GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
-  GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
+  // ---- static-list cache across steps (cache_prefix_kernel) ----
+  // cache_on: the static layer goes through the chunk work list (scene layers).  cache_ok: everything the kept lists
+  // depend on besides the cameras is what it was at the previous launch: scene, sizes, geometry, the view pass'
+  // outputs and background, and the workspace blocks themselves (a reallocation loses their contents).
+  const int64_t nbs0 = (int64_t)V * g.T * g.NB;
+  ctx->cache_on = stat.bounds != nullptr && V <= 65535 && layer_chunks(Ns, false) <= 65535 && Ns > 0 &&
+                  getenv("GSW_NO_WORK_LIST") == nullptr && getenv("GSW_NO_STATIC_CACHE") == nullptr;
+  ctx->cache_ok = false;
+  if (ctx->cache_on) {
+    if ((rc = w.view_prev.reserve((size_t)V * 40 * 4)) || (rc = w.view_cnt_prev.reserve((size_t)V * 4 + 16)) ||
+        (rc = w.view_same.reserve((size_t)V * 4 + 16)) || (rc = w.cache_m.reserve(16)))
+      return rc;
+    gsw_ctx::CacheSig sig;
+    sig.scene_gen = ctx->scene_gen;
+    sig.stream = (const void*)s;
+    sig.Ns = Ns;
+    sig.cap = cap;
+    sig.V = V; sig.F = F; sig.H = g.H; sig.W = g.W; sig.NB = g.NB; sig.tile_cull = g.tile_cull;
+    sig.antialiasing = g.antialiasing;
+    sig.outputs = ctx->view_pass_outputs | (with_labels ? 16 : 0);
+    sig.scale_modifier = g.scale_modifier;
+    sig.near_plane = g.near_plane;
+    for (int k = 0; k < 3; ++k) sig.bg[k] = ctx->view_pass_bg[k];
+    const DevBuf* bufs[16] = {&w.rec, &w.rad, &w.keys, &w.splats, &w.bin_count, &w.bin_off, &w.cta_hist,
+                              &w.chunk_mask, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream,
+                              &w.view_prev, &w.view_cnt_prev, &w.view_same};
+    for (int k = 0; k < 16; ++k) {
+      sig.ptrs[k] = bufs[k]->p;
+      sig.gens[k] = bufs[k]->gen;
+    }
+    ctx->cache_ok = memcmp(&sig, &ctx->cache_sig, sizeof sig) == 0;
+    ctx->cache_sig = sig;
+  } else {
+    ctx->cache_sig = gsw_ctx::CacheSig{};
+  }
+  if (ctx->cache_on) {
+    // the static bins are cleared on the device, view by view, for the views that are rebuilt (cull_chunks_kernel)
+    GSW_CUDA(cudaMemsetAsync(w.bin_count.as<uint32_t>() + nbs0, 0, (size_t)(nbins - nbs0 + 1) * 4, s));
+    GSW_CUDA(cudaMemsetAsync(w.bin_cursor.as<uint32_t>() + nbs0, 0, (size_t)(nbins - nbs0 + 1) * 4, s));
+  } else {
+    GSW_CUDA(cudaMemsetAsync(w.bin_count.p, 0, (size_t)(nbins + 1) * 4, s));
+    GSW_CUDA(cudaMemsetAsync(w.bin_cursor.p, 0, (size_t)(nbins + 1) * 4, s));
+  }
   GSW_CUDA(cudaMemsetAsync(w.status.p, 0, 256, s));
   auto mark = [&](int k) {
     if (ctx->profile) cudaEventRecord(ctx->stage_evt[k], s);
@@ -184,6 +226,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = launch_prepare_views(ctx, V, F, g, view, proj, campos, tanfov, frame_view, s))) return rc;
   mark(0);
   if ((rc = fork())) return rc;
+  if (ctx->cache_on && (rc = launch_cache_prefix(ctx, V, ss))) return rc;
   if ((rc = launch_preprocess(ctx, false, stat, Ns, V, 0, 0, g, view, proj, campos, tanfov, frame_env, frame_view,
                               pose, num_slots, ch_s, mask_s, &kept_s, ss)))
     return rc;
@@ -229,14 +272,17 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     // From here on the two layers are independent until the blend.  Side stream: sort of the static lists, gather
     // of the shared ones and (gsw_render_frames) the view pass over them.  Main stream: sort of the dynamic lists,
     // which forks onto a third stream inside.  join_side() closes the fork before the blend.
-    if ((rc = launch_sort_bins(ctx, 0, nbs, cap, 1, ss, ss))) return rc;
+    if ((rc = launch_sort_bins(ctx, 0, nbs, cap, 1, ss, ss, g.T * g.NB))) return rc;
     if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, with_labels, ss))) return rc;
-    if ((rc = launch_sort_bins(ctx, nbs, nbins - nbs, cap, 0, s, ctx->side2_stream ? ctx->side2_stream : s))) return rc;
+    if ((rc = launch_sort_bins(ctx, nbs, nbins - nbs, cap, 0, s, ctx->side2_stream ? ctx->side2_stream : s,
+                               g.T * g.NB)))
+      return rc;
     ctx->side_pending = true;
   } else {
     if ((rc = join())) return rc;
     mark(4);
-    if ((rc = launch_sort_bins(ctx, 0, nbins, cap, 0, s, ctx->side_stream ? ctx->side_stream : s))) return rc;
+    if ((rc = launch_sort_bins(ctx, 0, nbins, cap, 0, s, ctx->side_stream ? ctx->side_stream : s, g.T * g.NB)))
+      return rc;
     mark(5);
     if ((rc = launch_gather(ctx, nbins, V, Ns, Nm, g, cap, with_labels, s))) return rc;
     mark(6);
@@ -342,7 +388,7 @@ int gsw_destroy(gsw_ctx* c) {
   cudaDeviceSynchronize();
   auto& w = c->ws;
   DevBuf* bufs[] = {&w.rec, &w.rad, &w.bin_count, &w.bin_off, &w.bin_cursor, &w.scan_tmp,
-                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.chunk_mask, &w.work, &w.view_consts, &w.dyn_cost, &w.dyn_order, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
+                    &w.keys, &w.splats, &w.seg_queue, &w.cta_hist, &w.chunk_mask, &w.work, &w.view_consts, &w.dyn_cost, &w.dyn_order, &w.view_prev, &w.view_cnt_prev, &w.view_same, &w.cache_m, &c->sig, &w.view_cnt, &w.st_u8, &w.st_color, &w.st_invd, &w.st_seg, &w.lab_stream, &w.merge_cnt, &w.merge_off, &w.status, &w.cam,
                     &c->mov_xyz, &c->mov_scale_act, &c->mov_opacity, &c->mov_sh, &c->mov_log_scale,
                     &c->mov_quat_raw, &c->mov_slot, &c->mov_idx, &c->mov_bounds, &c->pos_of, &c->st_xyz, &c->st_scale,
                     &c->st_quat, &c->st_opacity, &c->st_idx, &c->st_bounds, &c->rig.dev};
@@ -385,6 +431,7 @@ int gsw_scene_set(gsw_ctx* c, int64_t N, const float* xyz, const float* scale_ac
   cudaStream_t s = (cudaStream_t)stream;
   c->have_scene = false;
   c->dyn_order_n = 0;
+  c->scene_gen++;
   c->last.valid = false;
   c->N = N;
   c->num_slots = num_slots;
@@ -519,6 +566,7 @@ int gsw_scene_set_labels(gsw_ctx* c, const int32_t* labels) {
     return GSW_E_INVALID;
   }
   c->labels = labels;
+  c->scene_gen++;
   return GSW_OK;
 }
 
@@ -598,15 +646,11 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
   dyn.sh_degree = 3;
   dyn.M = 16;
 
-  int rc = run_pipeline(c, c->stat_layer, c->N, c->Ns, c->slot_orig, c->pos_of.as<int32_t>(), &dyn, c->Nm,
-                        d->num_views, d->num_frames, g, d->viewmatrix,
-                        d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s,
-                        d->out_seg != nullptr);
-  if (rc) return rc;
-  c->last.single = false;
   // static-tile sharing: when some view is looked through by several frames, its static-only tiles are
-  // composited once (view pass) and copied into every frame that has no movable Gaussian in that tile
+  // composited once (view pass) and copied into every frame that has no movable Gaussian in that tile.  Its
+  // images are reserved before the pipeline runs: the static-list cache keys on where they live.
   const bool share = d->num_frames > d->num_views;
+  int rc;
   if (share) {
     auto& w = c->ws;
     const size_t HW = (size_t)d->height * d->width, Vn = (size_t)d->num_views;
@@ -615,6 +659,18 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
         (rc = w.st_invd.reserve(d->out_invdepth ? Vn * HW * 4 : 16)) ||
         (rc = w.st_seg.reserve(d->out_seg ? Vn * HW * 4 : 16)))
       return rc;
+  }
+  c->view_pass_outputs = (share ? 32 : 0) | (d->out_rgb_u8 ? 1 : 0) | (d->out_color ? 2 : 0) |
+                         (d->out_invdepth ? 4 : 0) | (d->out_seg ? 8 : 0);
+  for (int k = 0; k < 3; ++k) c->view_pass_bg[k] = d->bg[k];
+
+  rc = run_pipeline(c, c->stat_layer, c->N, c->Ns, c->slot_orig, c->pos_of.as<int32_t>(), &dyn, c->Nm,
+                        d->num_views, d->num_frames, g, d->viewmatrix,
+                        d->projmatrix, d->campos, d->tanfov, d->frame_env, d->frame_view, d->pose, c->num_slots, s,
+                        d->out_seg != nullptr);
+  if (rc) return rc;
+  c->last.single = false;
+  if (share) {
     if ((rc = launch_blend_view_pass(c, d->num_views, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g,
                                      d->bg, d->out_rgb_u8 != nullptr, d->out_color != nullptr,
                                      d->out_invdepth != nullptr, d->out_seg != nullptr,
@@ -1024,7 +1080,7 @@ int na_setup(int device, NaDevice& nd) {
   carve(w.merge_off, (size_t)(kNaMaxTiles + 1) * 4);
   carve(w.keys, (size_t)kNaMaxEntries * 8);
   carve(w.splats, (size_t)kNaMaxEntries * sizeof(Splat));
-  carve(w.status, 256);
+  carve(w.status, kStatusBytes);
   carve(w.seg_queue, 2 * seg_queue_bytes(kNaMaxEntries, nbins));
   carve(w.cam, 64);
   carve(w.view_cnt, 64);  // one view

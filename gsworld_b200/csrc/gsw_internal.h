@@ -33,6 +33,7 @@ struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
   bool fixed = false;  // a slice of memory owned by someone else: never grown, never freed (GSW_E_NOMEM instead)
+  uint32_t gen = 0;    // bumped by every (re)allocation: a new block at an old address still reads as a new block
   int reserve(size_t need);  // returns 0 / cudaError / GSW_E_NOMEM
   void release();
   template <typename T>
@@ -53,6 +54,11 @@ struct Splat {
 // which the copy stream waits with a stream memory operation.  cnt == nullptr: no signalling.
 // (No array member: a dynamically indexed kernel parameter is copied to local memory by every thread.)
 constexpr int kMaxSigGroups = 16;
+// Status block: the first 256 bytes are cleared at the start of every launch; int64 word kStatusPoison is not: a
+// launch that overflowed sets it, and the next launch's cache_prefix_kernel reads and clears it (the static-list
+// cache keeps nothing of an overflowed launch).
+constexpr int kStatusBytes = 512;
+constexpr int kStatusPoison = 32;
 struct DoneSig {
   uint32_t* cnt = nullptr;   // [n] finished CTAs per group (zeroed before the launch)
   uint32_t* flag = nullptr;  // [n] last epoch whose group is complete
@@ -163,6 +169,9 @@ struct Workspace {
   // dynamic layer: weight (tile entries) of every (frame, chunk) CTA of the last launch and the dispatch order made
   // from it (order_chunks_kernel); the order outlives the launch: the next step's preprocess uses it
   DevBuf dyn_cost, dyn_order;
+  // static-list cache across steps (cache_prefix_kernel): last launch's camera per view [V][40], frames per view,
+  // "camera unchanged" flags of this launch, and m = leading views whose static lists are kept
+  DevBuf view_prev, view_cnt_prev, view_same, cache_m;
   DevBuf status;  // device status words
   DevBuf cam;     // single-frame API staging: view/proj/campos/tanfov/frame maps
 };
@@ -233,6 +242,22 @@ struct gsw_ctx {
   cudaStream_t side2_stream = nullptr;  // the dynamic lists' sort forks onto it while side_stream carries the static chain
   cudaEvent_t fork_evt = nullptr, join_evt = nullptr;
   int64_t launches = 0;
+  // static-list cache: cache_on = this launch runs the cache logic (scene layers with a chunk work list); cache_ok = and
+  // nothing the kept lists depend on has changed on the host side since the previous launch (cache_sig)
+  bool cache_on = false, cache_ok = false;
+  struct CacheSig {
+    uint64_t scene_gen = 0;
+    int64_t Ns = 0, cap = 0;
+    int32_t V = 0, F = 0, H = 0, W = 0, NB = 0, tile_cull = 0, antialiasing = 0, outputs = 0;
+    float scale_modifier = 0.f, near_plane = 0.f, bg[3] = {0.f, 0.f, 0.f};
+    int32_t pad_ = 0;  // no padding bytes: the signature is compared with memcmp
+    const void* ptrs[16] = {};
+    uint32_t gens[16] = {};
+    const void* stream = nullptr;  // kept lists are only ordered before a launch on the same stream
+  } cache_sig;
+  uint64_t scene_gen = 0;      // bumped by gsw_scene_set / gsw_scene_set_labels
+  int32_t view_pass_outputs = 0;  // set by gsw_render_frames before run_pipeline: which static-only images the view pass writes
+  float view_pass_bg[3] = {0.f, 0.f, 0.f};
   bool side_pending = false;  // run_pipeline left the static chain running on side_stream (join_side closes it)
   int64_t dyn_order_n = 0;  // number of (frame, chunk) pairs ws.dyn_order is valid for (0: none yet)
 };
@@ -248,6 +273,7 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
                       cudaStream_t s, const uint32_t* order = nullptr, uint32_t* cost = nullptr);
 // heaviest-first dispatch order of n (list, chunk) CTAs from their weights (tile entries produced)
 int launch_order_chunks(const uint32_t* cost, int64_t n, uint32_t* order, cudaStream_t s);
+int launch_cache_prefix(const gsw_ctx* ctx, int32_t V, cudaStream_t s);
 size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic);
 int64_t layer_chunks(int64_t n_items, bool dynamic);  // chunks of a layer (one preprocess / scatter CTA round each)
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
@@ -263,7 +289,7 @@ int launch_gather_layers(const gsw_ctx* ctx, cudaStream_t s);  // compact static
 // binsort.cu
 int launch_scan_u32(const uint32_t* in, uint32_t* out_excl, int64_t n, uint32_t* tmp, cudaStream_t s);
 int launch_sort_bins(const gsw_ctx* ctx, int64_t bin0, int64_t nb, int64_t cap, int set, cudaStream_t s,
-                     cudaStream_t side);
+                     cudaStream_t side, int32_t bins_per_list);
 int launch_gather(const gsw_ctx* ctx, int64_t nbins, int32_t V, int64_t Ns, int64_t Nm, const FrameGeom& g, int64_t cap,
                   bool with_labels, cudaStream_t s);
 int launch_frame_lists(const gsw_ctx* ctx, int32_t frame, int32_t* ranges, uint64_t* keys, uint32_t* vals,

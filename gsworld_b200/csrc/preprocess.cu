@@ -699,15 +699,56 @@ __global__ void __launch_bounds__(256)
 prepare_views_kernel(int32_t V, int32_t F, FrameGeom g, const float* __restrict__ views,
                      const float* __restrict__ projs, const float* __restrict__ campos,
                      const float* __restrict__ tanfov, const int32_t* __restrict__ frame_view,
-                     uint32_t* __restrict__ view_consts, uint32_t* __restrict__ view_cnt) {
+                     uint32_t* __restrict__ view_consts, uint32_t* __restrict__ view_cnt, int cache_ok,
+                     uint32_t* __restrict__ view_prev, uint32_t* __restrict__ view_same) {
   __shared__ ViewConsts c;
   const int f = blockIdx.x * 256 + threadIdx.x;
   if (f < F) atomicAdd(&view_cnt[frame_view ? frame_view[f] : 0], 1u);
   if ((int)blockIdx.x >= V) return;  // block-uniform
+  if (view_prev != nullptr) {
+    // Static-list cache (see cache_prefix_kernel): is this view's camera bitwise the one of the previous launch?
+    // 37 words: view 16, projection 16, camera centre 3, tan(fov/2) 2; kept in view_prev[v][40].
+    const int v = blockIdx.x;
+    uint32_t now = 0u;
+    const int t = threadIdx.x;
+    if (t < 16) now = __float_as_uint(views[v * 16 + t]);
+    else if (t < 32) now = __float_as_uint(projs[v * 16 + t - 16]);
+    else if (t < 35) now = __float_as_uint(campos[v * 3 + t - 32]);
+    else if (t < 37) now = __float_as_uint(tanfov[v * 2 + t - 35]);
+    const bool diff = t < 37 && view_prev[v * 40 + t] != now;
+    const int any_diff = __syncthreads_or(diff ? 1 : 0);
+    if (t < 37) view_prev[v * 40 + t] = now;
+    if (t == 0) view_same[v] = (cache_ok && !any_diff) ? 1u : 0u;
+  }
   compute_view_consts(blockIdx.x, g, views, projs, campos, tanfov, c.vs, c.vc);
   __syncthreads();
   if (threadIdx.x < kViewConstWords)
     view_consts[(size_t)blockIdx.x * kViewConstWords + threadIdx.x] = reinterpret_cast<const uint32_t*>(&c)[threadIdx.x];
+}
+
+// Static-list cache across steps.  A view whose camera, scene, geometry and workspace are exactly those of the previous
+// launch (a world-fixed camera: SURVEY.md section 8(f) row 4, "or once ever") would get bit for bit the same static
+// records, bins, sorted keys, gathered splats and static-only tiles again, and all of those still sit in the workspace.
+// Because the static lists are laid out in view order, only a PREFIX of unchanged views can be kept: m = number of
+// leading views that are unchanged and whose shared / private status is the same as before.  Every static-chain kernel
+// skips views below m (the work list simply holds no chunk of them); their bin counters are not cleared.  One warp.
+__global__ void cache_prefix_kernel(int32_t V, const uint32_t* __restrict__ view_same,
+                                    const uint32_t* __restrict__ view_cnt, uint32_t* __restrict__ view_cnt_prev,
+                                    uint32_t* __restrict__ cache_m, long long* __restrict__ status) {
+  const int lane = threadIdx.x;
+  int m = V;
+  if (status[kStatusPoison] != 0) m = 0;  // the previous launch overflowed: its lists are incomplete
+  __syncwarp();
+  if (lane == 0) status[kStatusPoison] = 0;
+  for (int v0 = 0; v0 < V && m == V; v0 += 32) {
+    const int v = v0 + lane;
+    bool keep = true;
+    if (v < V) keep = view_same[v] != 0u && (view_cnt[v] >= 2u) == (view_cnt_prev[v] >= 2u);
+    const unsigned bad = __ballot_sync(0xffffffffu, !keep);
+    if (bad) m = v0 + __ffs(bad) - 1;
+  }
+  for (int v = lane; v < V; v += 32) view_cnt_prev[v] = view_cnt[v];
+  if (lane == 0) *cache_m = (uint32_t)m;
 }
 
 // ---- chunk-level culling of the static layer, ahead of the preprocess pass ----
@@ -723,9 +764,19 @@ cull_chunks_kernel(const float* __restrict__ bounds, int64_t n_items, int32_t nc
                    const float* __restrict__ views, const float* __restrict__ projs,
                    const float* __restrict__ campos, const float* __restrict__ tanfov,
                    uint32_t* __restrict__ chunk_mask, uint32_t* __restrict__ work, uint32_t* __restrict__ work_count,
-                   const uint32_t* __restrict__ view_consts) {
+                   const uint32_t* __restrict__ view_consts, const uint32_t* __restrict__ cache_m,
+                   uint32_t* __restrict__ bin_count, uint32_t* __restrict__ bin_cursor, int32_t nbl) {
   __shared__ ViewConsts c;
   const int view = blockIdx.y;
+  if (cache_m != nullptr) {
+    if ((uint32_t)view < *cache_m) return;  // static lists of this view are kept from the previous step
+    // this view's bin counters were left alone by the host (they may belong to a kept view): clear them here, before
+    // the preprocess pass that follows on this stream counts into them
+    for (int k = blockIdx.x * 256 + threadIdx.x; k < nbl; k += gridDim.x * 256) {
+      bin_count[(size_t)view * nbl + k] = 0u;
+      bin_cursor[(size_t)view * nbl + k] = 0u;
+    }
+  }
   if (threadIdx.x < kViewConstWords)  // written by prepare_views_kernel
     reinterpret_cast<uint32_t*>(&c)[threadIdx.x] = view_consts[(size_t)view * kViewConstWords + threadIdx.x];
   __syncthreads();
@@ -1589,7 +1640,9 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     dim3 cg((unsigned)((nchunks + 255) / 256), (unsigned)n_lists);
     cull_chunks_kernel<<<cg, 256, 0, s>>>(ga.bounds, n_items, nchunks, g, view, proj, campos, tanfov, chunk_mask,
                                           w.work.as<uint32_t>(), st32 + kWorkCountWord,
-                                          w.view_consts.as<uint32_t>());
+                                          w.view_consts.as<uint32_t>(),
+                                          ctx->cache_on ? w.cache_m.as<uint32_t>() : nullptr,
+                                          w.bin_count.as<uint32_t>(), w.bin_cursor.as<uint32_t>(), g.T * g.NB);
     count_launches(1);
   }
   int rc;
@@ -1690,7 +1743,21 @@ int launch_prepare_views(const gsw_ctx* ctx, int32_t V, int32_t F, const FrameGe
   GSW_CUDA(cudaMemsetAsync(w.view_cnt.p, 0, (size_t)V * 4, s));
   const int blocks = V > (F + 255) / 256 ? V : (F + 255) / 256;
   prepare_views_kernel<<<blocks, 256, 0, s>>>(V, F, g, view, proj, campos, tanfov, frame_view,
-                                              w.view_consts.as<uint32_t>(), w.view_cnt.as<uint32_t>());
+                                              w.view_consts.as<uint32_t>(), w.view_cnt.as<uint32_t>(),
+                                              ctx->cache_ok ? 1 : 0,
+                                              ctx->cache_on ? w.view_prev.as<uint32_t>() : nullptr,
+                                              w.view_same.as<uint32_t>());
+  count_launches(1);
+  GSW_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// m = number of leading views whose static lists are kept from the previous launch (ws.cache_m); after prepare_views
+int launch_cache_prefix(const gsw_ctx* ctx, int32_t V, cudaStream_t s) {
+  auto& w = ctx->ws;
+  cache_prefix_kernel<<<1, 32, 0, s>>>(V, w.view_same.as<uint32_t>(), w.view_cnt.as<uint32_t>(),
+                                       w.view_cnt_prev.as<uint32_t>(), w.cache_m.as<uint32_t>(),
+                                       w.status.as<long long>());
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
