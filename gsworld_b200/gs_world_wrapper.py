@@ -407,14 +407,18 @@ class GSWorldWrapper(_Base):
         if key not in self._cam_bufs:
             counts = [1 if (self.strict_reference or c in static) else B for c in cam_names]
             V = sum(counts)
-            fv, base = [], 0
-            for n in counts:
-                fv.append(torch.full((B,), base, dtype=torch.int32) if n == 1
-                          else base + torch.arange(B, dtype=torch.int32))
-                base += n
+            # view numbering: world-fixed cameras first.  The engine keeps the static lists of a leading run of
+            # views whose camera has not changed since the previous step (static-list cache), so the views that
+            # never move go in front of the ones that move every step.  Frames keep the order camera * B + env.
+            bases, base = [0] * len(cam_names), 0
+            for ci in sorted(range(len(cam_names)), key=lambda i: cam_names[i] not in static):
+                bases[ci] = base
+                base += counts[ci]
+            fv = [torch.full((B,), b, dtype=torch.int32) if n == 1 else b + torch.arange(B, dtype=torch.int32)
+                  for b, n in zip(bases, counts)]
             z = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
-            self._cam_bufs[key] = dict(counts=counts, view=z(V, 16), proj=z(V, 16), campos=z(V, 3), tanfov=z(V, 2),
-                                       fv=torch.cat(fv).to(dev))
+            self._cam_bufs[key] = dict(counts=counts, bases=bases, view=z(V, 16), proj=z(V, 16), campos=z(V, 3),
+                                       tanfov=z(V, 2), fv=torch.cat(fv).to(dev))
         cb = self._cam_bufs[key]
         staged = None
         first = params[cam_names[0]]["extrinsic_cv"]
@@ -434,8 +438,8 @@ class GSWorldWrapper(_Base):
                 o += n * (ne + 9)
             d = st.push()
             staged = [(d[a:b].view(-1, *first.shape[-2:]), d[b:e].view(-1, 3, 3)) for a, b, e in spans]
-        base = 0
         for ci, (c, n) in enumerate(zip(cam_names, cb["counts"])):
+            base = cb["bases"][ci]
             H, W = self._sensor_hw(c)
             if staged is not None:
                 ext, K = staged[ci]
@@ -445,7 +449,6 @@ class GSWorldWrapper(_Base):
             sl = slice(base, base + n)
             self._engine.compose_cameras(ext, K, H, W, self._rigid_host, self._scale_host, cb["view"][sl],
                                          cb["proj"][sl], cb["campos"][sl], cb["tanfov"][sl])
-            base += n
         return cb["view"], cb["proj"], cb["campos"], cb["tanfov"], cb["fv"]
 
     def _maps(self, n_cams):

@@ -136,7 +136,13 @@ typedef struct gsw_frames_desc {
  * pushed frames (and whoever overwrites out_rgb_u8) is ordered with gsw_delivery_wait as with GSW_DELIVER_NO_JOIN. */
 #define GSW_DELIVER_NO_PEER_JOIN 2
 
-/* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous. */
+/* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous.
+ * Static-list cache: a leading run of views whose 37 camera words (viewmatrix, projmatrix, campos, tanfov) are bitwise
+ * those of the previous gsw_render_frames call on this context keeps its static tile lists and static-only tiles
+ * from that call (compared on the device; scene, sizes, switches, outputs, stream and workspace must be unchanged as
+ * well, else everything is rebuilt).  Same bytes out either way; number world-fixed cameras first to profit from it.
+ * GSW_NO_STATIC_CACHE=1 in the environment turns it off.  No counterpart in the reference, which rebuilds the
+ * lists of every frame every step. */
 int gsw_render_frames(gsw_ctx* ctx, const gsw_frames_desc* desc, gsw_stream stream);
 
 /* Wait for the last launch on this context and report it.  Returns GSW_E_CAPACITY if the tile-entry

@@ -122,3 +122,18 @@ def test_scene_or_setting_change_drops_the_kept_lists(rig):
     a, ca, _, _ = _render(cached, True)
     _same(a, b)
     assert ca["static_chunks_live"] == 0
+
+
+def test_world_fixed_cameras_are_numbered_first(rig):
+    """Sensor order (wrist, third-person): the wrapper still gives the world-fixed camera view 0, so its lists are kept."""
+    fx, env, mk = rig
+    env.cameras = ("wrist_cam", "right_cam")
+    env.sensor_hw = {c: (H, W) for c in env.cameras}
+    for strict in (True, False):
+        cached, fresh = mk(strict), mk(strict)
+        _render(cached, True)
+        env.step()
+        a, ca, Da, _ = _render(cached, True)
+        b, cb, Db, _ = _render(fresh, False)
+        _same(a, b)
+        assert Da == Db and 0 < ca["static_chunks_live"] < cb["static_chunks_live"]
