@@ -141,11 +141,12 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(kStatusBytes))) return rc;
-  const size_t chs = cta_hist_words(Ns, V, g, false), chd = dyn ? cta_hist_words(Nm, F, g, true) : 0;
+  ctx->ipb_static = pick_static_ipb(stat, Ns, V);
+  const size_t chs = cta_hist_words(ctx, Ns, V, g, false), chd = dyn ? cta_hist_words(ctx, Nm, F, g, true) : 0;
   if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
   uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;
   uint32_t* const ch_d = chd ? w.cta_hist.as<uint32_t>() + chs : nullptr;
-  const size_t cm_s = (size_t)V * (size_t)layer_chunks(Ns, false), cm_d = dyn ? (size_t)F * (size_t)layer_chunks(Nm, true) : 0;
+  const size_t cm_s = (size_t)V * (size_t)layer_chunks(ctx, Ns, false), cm_d = dyn ? (size_t)F * (size_t)layer_chunks(ctx, Nm, true) : 0;
   if ((rc = w.chunk_mask.reserve((cm_s + cm_d) * 4 + 16)) || (rc = w.work.reserve(cm_s * 4 + 16)) ||
       (rc = w.view_consts.reserve((size_t)V * 48 * 4)))
     return rc;
@@ -161,7 +162,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   // depend on besides the cameras is what it was at the previous launch: scene, sizes, geometry, the view pass'
   // outputs and background, and the workspace blocks themselves (a reallocation loses their contents).
   const int64_t nbs0 = (int64_t)V * g.T * g.NB;
-  ctx->cache_on = stat.bounds != nullptr && V <= 65535 && layer_chunks(Ns, false) <= 65535 && Ns > 0 &&
+  ctx->cache_on = stat.bounds != nullptr && V <= 65535 && layer_chunks(ctx, Ns, false) <= 65535 && Ns > 0 &&
                   getenv("GSW_NO_WORK_LIST") == nullptr && getenv("GSW_NO_STATIC_CACHE") == nullptr;
   ctx->cache_ok = false;
   if (ctx->cache_on) {
@@ -175,6 +176,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
     sig.cap = cap;
     sig.V = V; sig.F = F; sig.H = g.H; sig.W = g.W; sig.NB = g.NB; sig.tile_cull = g.tile_cull;
     sig.antialiasing = g.antialiasing;
+    sig.ipb_static = ctx->ipb_static;
     sig.outputs = ctx->view_pass_outputs | (with_labels ? 16 : 0);
     sig.scale_modifier = g.scale_modifier;
     sig.near_plane = g.near_plane;
@@ -1088,10 +1090,10 @@ int na_setup(int device, NaDevice& nd) {
     FrameGeom gmax{};
     gmax.T = kNaMaxTiles;
     gmax.NB = 1;
-    carve(w.cta_hist, cta_hist_words(kNaMaxP, 1, gmax, false) * 4 + 16);
+    carve(w.cta_hist, cta_hist_words(&nd.ctx, kNaMaxP, 1, gmax, false) * 4 + 16);  // (2048-item chunks: no work list here)
   }
-  carve(w.chunk_mask, (size_t)layer_chunks(kNaMaxP, false) * 4 + 16);
-  carve(w.work, (size_t)layer_chunks(kNaMaxP, false) * 4 + 16);
+  carve(w.chunk_mask, (size_t)layer_chunks(&nd.ctx, kNaMaxP, false) * 4 + 16);
+  carve(w.work, (size_t)layer_chunks(&nd.ctx, kNaMaxP, false) * 4 + 16);
   carve(w.view_consts, 48 * 4);
   if (off > kNaBytes) {
     set_error("gsw_rasterize_forward_static: internal layout (%zu B) exceeds the fixed array (%zu B)", off, kNaBytes);

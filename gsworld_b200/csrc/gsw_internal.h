@@ -245,12 +245,13 @@ struct gsw_ctx {
   // static-list cache: cache_on = this launch runs the cache logic (scene layers with a chunk work list); cache_ok = and
   // nothing the kept lists depend on has changed on the host side since the previous launch (cache_sig)
   bool cache_on = false, cache_ok = false;
+  int32_t ipb_static = 2048;  // items per chunk of the static layer in the last launch (pick_static_ipb)
   struct CacheSig {
     uint64_t scene_gen = 0;
     int64_t Ns = 0, cap = 0;
     int32_t V = 0, F = 0, H = 0, W = 0, NB = 0, tile_cull = 0, antialiasing = 0, outputs = 0;
     float scale_modifier = 0.f, near_plane = 0.f, bg[3] = {0.f, 0.f, 0.f};
-    int32_t pad_ = 0;  // no padding bytes: the signature is compared with memcmp
+    int32_t ipb_static = 0;  // (also: no padding bytes, the signature is compared with memcmp)
     const void* ptrs[16] = {};
     uint32_t gens[16] = {};
     const void* stream = nullptr;  // kept lists are only ordered before a launch on the same stream
@@ -274,8 +275,10 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 // heaviest-first dispatch order of n (list, chunk) CTAs from their weights (tile entries produced)
 int launch_order_chunks(const uint32_t* cost, int64_t n, uint32_t* order, cudaStream_t s);
 int launch_cache_prefix(const gsw_ctx* ctx, int32_t V, cudaStream_t s);
-size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic);
-int64_t layer_chunks(int64_t n_items, bool dynamic);  // chunks of a layer (one preprocess / scatter CTA round each)
+size_t cta_hist_words(const gsw_ctx* ctx, int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic);
+// chunks of a layer (one preprocess / scatter CTA round each); the static layer's chunk size is ctx->ipb_static
+int64_t layer_chunks(const gsw_ctx* ctx, int64_t n_items, bool dynamic);
+int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists);
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
                    const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order = nullptr);

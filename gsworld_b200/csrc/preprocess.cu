@@ -167,16 +167,17 @@ __device__ __forceinline__ float sh_channel(int deg, float x, float y, float z, 
   return fmaxf(res, 0.0f);
 }
 
-// Items per CTA round ("chunk") of each layer: 256 threads x chunk / 256 consecutive items of one list.  The static
-// layer keeps large chunks (fewer per-CTA histogram flushes over a million Gaussians per view); the dynamic layer
-// uses smaller ones, because a close-up of the gripper makes single chunks of movable Gaussians hundreds of times
-// heavier than the rest, and a chunk is the unit the preprocess and scatter passes are balanced in.
+// Items per CTA round ("chunk") of each layer: 256 threads x chunk / 256 consecutive items of one list.  kIpbStatic is
+// the static layer's LARGEST chunk (and the only one of the forms without a work list); with a work list the launch
+// picks 256 ... kIpbStatic (pick_static_ipb).  The dynamic layer's is fixed (512 measured slower at 64 envs: preprocess
+// 0.29 -> 0.36 ms, and no faster at 8 envs once the static chunk is small).
 #ifndef GSW_IPB_DYN
 #define GSW_IPB_DYN 2048
 #endif
-constexpr int kIpbStatic = 2048, kIpbDynamic = GSW_IPB_DYN;
-constexpr int kItemsPerBlock = kIpbStatic;  // the static layer's (chunk-cull work list)
-constexpr int ipb_of(bool dynamic) { return dynamic ? kIpbDynamic : kIpbStatic; }
+#ifndef GSW_IPB_STAT
+#define GSW_IPB_STAT 2048
+#endif
+constexpr int kIpbStatic = GSW_IPB_STAT, kIpbDynamic = GSW_IPB_DYN;
 constexpr size_t kMaxHistBytes = 160 * 1024;         // per-CTA shared histogram budget; above it: global atomics
 
 // Per-item body.  `hist` (shared, one counter per (tile, bucket) of this list) may be null, in which case
@@ -765,7 +766,7 @@ cull_chunks_kernel(const float* __restrict__ bounds, int64_t n_items, int32_t nc
                    const float* __restrict__ campos, const float* __restrict__ tanfov,
                    uint32_t* __restrict__ chunk_mask, uint32_t* __restrict__ work, uint32_t* __restrict__ work_count,
                    const uint32_t* __restrict__ view_consts, const uint32_t* __restrict__ cache_m,
-                   uint32_t* __restrict__ bin_count, uint32_t* __restrict__ bin_cursor, int32_t nbl) {
+                   uint32_t* __restrict__ bin_count, uint32_t* __restrict__ bin_cursor, int32_t nbl, int32_t ipb) {
   __shared__ ViewConsts c;
   const int view = blockIdx.y;
   if (cache_m != nullptr) {
@@ -783,10 +784,10 @@ cull_chunks_kernel(const float* __restrict__ bounds, int64_t n_items, int32_t nc
   const int chunk = blockIdx.x * 256 + threadIdx.x;
   uint32_t mask = 0;
   if (chunk < nchunks) {
-    constexpr int kGroups = kItemsPerBlock / 256;
+    const int groups = ipb >> 8;  // the static layer's chunk is chosen per launch (pick_static_ipb)
 #pragma unroll 1
-    for (int k = 0; k < kGroups; ++k) {
-      const int64_t g0 = (int64_t)chunk * kItemsPerBlock + k * 256;
+    for (int k = 0; k < groups; ++k) {
+      const int64_t g0 = (int64_t)chunk * ipb + k * 256;
       if (g0 < n_items && !group_culled<false>(bounds + (g0 >> 8) * 8, c.vs, c.vc, g, nullptr)) mask |= 1u << k;
     }
     chunk_mask[(size_t)view * nchunks + chunk] = mask;
@@ -1047,7 +1048,7 @@ __device__ __forceinline__ bool next_chunk(int& list, int& chunk, bool first, co
   return wv != 0xffffffffu;
 }
 
-template <bool DYN, bool WL>
+template <bool DYN, bool WL, int IPBS = kIpbStatic>
 __global__ void __launch_bounds__(DYN ? kScatterThreadsDyn : kScatterThreadsStatic)
 scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                const float4* __restrict__ recA, const float4* __restrict__ /*recB*/,
@@ -1057,7 +1058,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
                const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
                uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
-  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic;  // this layer's chunk
+  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : IPBS;  // this layer's chunk
   constexpr int NT = DYN ? kScatterThreadsDyn : kScatterThreadsStatic, kGroups = kItemsPerBlock / 256;
   constexpr int kItemsPerThread = kItemsPerBlock / NT;
   extern __shared__ uint32_t dsm[];
@@ -1158,7 +1159,7 @@ scatter_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_
 // (kCoopBitsCull) and rectangles of more than 64 tiles (tested again, same make_foot / tile_alive on the same bits) are
 // expanded by the whole warp.  Needs the preprocess CTA's bin counts (cta_hist) for the shared-memory slot
 // counters; without them it falls back to global cursors.
-template <bool DYN, bool WL>
+template <bool DYN, bool WL, int IPBS = kIpbStatic>
 __global__ void __launch_bounds__(DYN ? kScatterThreadsDyn : kScatterThreadsStatic)
 scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t item_base, FrameGeom g,
                     const float4* __restrict__ recA, const float4* __restrict__ recB,
@@ -1168,7 +1169,7 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
                     const uint32_t* __restrict__ cta_hist, const uint32_t* __restrict__ chunk_mask, int32_t nchunks,
                     const uint32_t* __restrict__ work, const uint32_t* __restrict__ work_count,
                     uint32_t* __restrict__ ticket, const uint32_t* __restrict__ order) {
-  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : kIpbStatic;  // this layer's chunk
+  constexpr int kItemsPerBlock = DYN ? kIpbDynamic : IPBS;  // this layer's chunk
   constexpr int NT = DYN ? kScatterThreadsDyn : kScatterThreadsStatic, kGroups = kItemsPerBlock / 256;
   constexpr int kItemsPerThread = kItemsPerBlock / NT;
   extern __shared__ uint32_t dsm[];
@@ -1333,12 +1334,12 @@ scatter_cull_kernel(GaussArrays ga, int64_t n_items, int32_t list_base, int64_t 
 // are never written; chunk_mask = live groups per (list, chunk): V static lists, then F dynamic lists).
 __device__ __forceinline__ int radius_of(int64_t i, int32_t f, int32_t v, int32_t V, int64_t Ns, int64_t Nm,
                                          const int32_t* slot, const int32_t* pos_of, const int32_t* rad,
-                                         const uint32_t* chunk_mask, int64_t* item_out) {
+                                         const uint32_t* chunk_mask, int64_t* item_out, int32_t ipb_s) {
   const int64_t pos = pos_of ? (int64_t)pos_of[i] : i;
   const bool dyn = slot != nullptr && slot[i] >= 0;
-  const int64_t nch_s = (Ns + kIpbStatic - 1) / kIpbStatic, nch_d = (Nm + kIpbDynamic - 1) / kIpbDynamic;
+  const int64_t nch_s = (Ns + ipb_s - 1) / ipb_s, nch_d = (Nm + kIpbDynamic - 1) / kIpbDynamic;
   const int64_t item = dyn ? (int64_t)V * Ns + (int64_t)f * Nm + pos : (int64_t)v * Ns + pos;
-  const int64_t ipb = dyn ? kIpbDynamic : kIpbStatic;
+  const int64_t ipb = dyn ? kIpbDynamic : ipb_s;
   const int64_t cid = (dyn ? (int64_t)V * nch_s + (int64_t)f * nch_d : (int64_t)v * nch_s) + pos / ipb;
   *item_out = item;
   if (chunk_mask != nullptr && !((chunk_mask[cid] >> ((pos % ipb) >> 8)) & 1u)) return 0;
@@ -1350,12 +1351,12 @@ __global__ void frame_attrs_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V,
                                    const int32_t* frame_view, const int32_t* slot, const int32_t* pos_of, FrameGeom g,
                                    const float4* recA, const float4* recB, const float4* recC, const int32_t* rad,
                                    const uint32_t* chunk_mask, int32_t* radii, int32_t* tiles, float* depth, float* xy,
-                                   float* conic_o, float* rgb) {
+                                   float* conic_o, float* rgb, int32_t ipb_s) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int view = frame_view ? frame_view[frame] : 0;
   int64_t item;
-  const int r = radius_of(i, frame, view, V, Ns, Nm, slot, pos_of, rad, chunk_mask, &item);
+  const int r = radius_of(i, frame, view, V, Ns, Nm, slot, pos_of, rad, chunk_mask, &item, ipb_s);
   float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
   int tt = 0;
   if (r > 0) {
@@ -1383,13 +1384,13 @@ __global__ void frame_attrs_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V,
 // radii of every frame: out[f, i]
 __global__ void radii_kernel(int64_t N, int64_t Ns, int64_t Nm, int32_t V, const int32_t* frame_view,
                              const int32_t* slot, const int32_t* pos_of, const int32_t* rad,
-                             const uint32_t* chunk_mask, int32_t* out) {
+                             const uint32_t* chunk_mask, int32_t* out, int32_t ipb_s) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int f = blockIdx.y;
   const int view = frame_view ? frame_view[f] : 0;
   int64_t item;
-  out[(int64_t)f * N + i] = radius_of(i, f, view, V, Ns, Nm, slot, pos_of, rad, chunk_mask, &item);
+  out[(int64_t)f * N + i] = radius_of(i, f, view, V, Ns, Nm, slot, pos_of, rad, chunk_mask, &item, ipb_s);
 }
 
 __global__ void mark_visible_kernel(int32_t P, const float* xyz, const float* V, float near_plane, uint8_t* out) {
@@ -1593,13 +1594,38 @@ static int wl_ctas_per_sm() {
   return v;
 }
 
-int64_t layer_chunks(int64_t n_items, bool dynamic) { return (n_items + ipb_of(dynamic) - 1) / ipb_of(dynamic); }
+int64_t layer_chunks(const gsw_ctx* ctx, int64_t n_items, bool dynamic) {
+  const int64_t ipb = dynamic ? kIpbDynamic : ctx->ipb_static;
+  return (n_items + ipb - 1) / ipb;
+}
 
 // The static layer goes through the chunk-cull work list when its groups have bounds (scene layers; the single-frame
 // entry points have none) and (view, chunk) fits the 16 + 16 bit packing.
-bool use_work_list(bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
-  return !dynamic && ga.bounds != nullptr && n_lists <= 65535 && layer_chunks(n_items, false) <= 65535 &&
+bool use_work_list(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
+  return !dynamic && ga.bounds != nullptr && n_lists <= 65535 && layer_chunks(ctx, n_items, false) <= 65535 &&
          getenv("GSW_NO_WORK_LIST") == nullptr;
+}
+
+// Items per chunk of the static layer for this launch.  A chunk is the unit the persistent preprocess / scatter CTAs
+// take from the work list, and one CTA walks it 256 items at a time: with two views a 2048-item chunk leaves a few
+// hundred CTAs each walking eight dependent rounds (measured, 1M Gaussians: static preprocess 0.10 ms at 2048 items
+// per chunk, 0.056 ms at 256; step 1.070 -> 1.017 ms at 64 envs and 0.394 -> 0.362 ms at 8 envs), while with 65 views
+// small chunks only add histogram flushes and per-chunk count rows (per-env cameras 2.95 ms at 2048, 3.40 ms at 256).
+// So: the largest chunk that still yields ~7000 (view, chunk) pairs, 256 at least; always 2048 without a work list
+// (the staged and the plain forms are only instantiated for it).
+int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
+  if (ga.bounds == nullptr || n_lists > 65535 || getenv("GSW_NO_WORK_LIST") != nullptr ||
+      getenv("GSW_WL_TMA") != nullptr)
+    return kIpbStatic;
+  if (const char* e = getenv("GSW_IPB_STATIC")) {  // tuning aid
+    const int v = atoi(e);
+    if ((v == 256 || v == 512 || v == 1024 || v == 2048) && (n_items + v - 1) / v <= 65535) return v;
+  }
+  for (int ipb = kIpbStatic; ipb > 256; ipb >>= 1)
+    if ((int64_t)n_lists * ((n_items + ipb - 1) / ipb) >= 7000) return ipb;
+  int ipb = 256;
+  while (ipb < kIpbStatic && (n_items + ipb - 1) / ipb > 65535) ipb <<= 1;  // 16-bit chunk field of the work list
+  return ipb;
 }
 
 int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
@@ -1619,12 +1645,12 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     tma_ok = tma_ok && aligned16(ga.log_scale_raw) && aligned16(ga.quat_raw) && aligned16(ga.mov_slot);
   else
     tma_ok = tma_ok && ga.quat_act != nullptr && aligned16(ga.quat_act) && (ga.slot == nullptr || aligned16(ga.slot));
-  const size_t stage_b = dynamic ? (size_t)kIpbDynamic * 60 : (size_t)kIpbStatic * 48;
+  const size_t stage_b = dynamic ? (size_t)kIpbDynamic * 60 : (size_t)ctx->ipb_static * 48;
   const size_t budget = 200 * 1024;
   // The bulk staging pays where a CTA's arithmetic is short next to its load latency (few visible items per chunk).
   // The work-list form only visits live chunks; there the 96 KB stage costs a third of the resident warps and
   // measured slower (per-env cameras: 1.08 -> 0.90 ms), so it keeps plain loads.  GSW_WL_TMA=1 / GSW_NO_TMA=1 override.
-  const bool wl_pre = use_work_list(dynamic, ga, n_items, n_lists);
+  const bool wl_pre = use_work_list(ctx, dynamic, ga, n_items, n_lists);
   int use_tma = !dynamic && tma_ok && stage_b + pose_b + 1024 <= budget && getenv("GSW_NO_TMA") == nullptr &&
                 (!wl_pre || getenv("GSW_WL_TMA") != nullptr);
   int use_hist = hist_b <= kMaxHistBytes && (use_tma ? stage_b : 0) + hist_b + pose_b <= budget;
@@ -1633,8 +1659,8 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
     use_hist = 1;
   }
   const size_t sm = (use_tma ? stage_b : 0) + (use_hist ? hist_b : 0) + pose_b;
-  const int32_t nchunks = (int32_t)layer_chunks(n_items, dynamic);
-  const bool wl = use_work_list(dynamic, ga, n_items, n_lists);
+  const int32_t nchunks = (int32_t)layer_chunks(ctx, n_items, dynamic);
+  const bool wl = use_work_list(ctx, dynamic, ga, n_items, n_lists);
   uint32_t* const st32 = w.status.as<uint32_t>();
   if (wl) {
     dim3 cg((unsigned)((nchunks + 255) / 256), (unsigned)n_lists);
@@ -1642,7 +1668,8 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
                                           w.work.as<uint32_t>(), st32 + kWorkCountWord,
                                           w.view_consts.as<uint32_t>(),
                                           ctx->cache_on ? w.cache_m.as<uint32_t>() : nullptr,
-                                          w.bin_count.as<uint32_t>(), w.bin_cursor.as<uint32_t>(), g.T * g.NB);
+                                          w.bin_count.as<uint32_t>(), w.bin_cursor.as<uint32_t>(), g.T * g.NB,
+                                          ctx->ipb_static);
     count_launches(1);
   }
   int rc;
@@ -1674,9 +1701,24 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
       else GSW_LAUNCH_PRE(false, kIpbStatic, true, false, false);
     }
   } else {
-    if (wl) {
-      if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true, true);
-      else GSW_LAUNCH_PRE(false, kIpbStatic, false, false, true);
+    if (wl) {  // the form whose chunk size follows the launch (pick_static_ipb)
+      switch (ctx->ipb_static) {
+        case 256:
+          if (cull) GSW_LAUNCH_PRE(false, 256, false, true, true);
+          else GSW_LAUNCH_PRE(false, 256, false, false, true);
+          break;
+        case 512:
+          if (cull) GSW_LAUNCH_PRE(false, 512, false, true, true);
+          else GSW_LAUNCH_PRE(false, 512, false, false, true);
+          break;
+        case 1024:
+          if (cull) GSW_LAUNCH_PRE(false, 1024, false, true, true);
+          else GSW_LAUNCH_PRE(false, 1024, false, false, true);
+          break;
+        default:
+          if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true, true);
+          else GSW_LAUNCH_PRE(false, kIpbStatic, false, false, true);
+      }
     } else {
       if (cull) GSW_LAUNCH_PRE(false, kIpbStatic, false, true, false);
       else GSW_LAUNCH_PRE(false, kIpbStatic, false, false, false);
@@ -1690,17 +1732,17 @@ int launch_preprocess(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, i
 }
 
 // words of cta_hist one layer needs (0: the bins do not fit a shared-memory histogram, nothing is kept)
-size_t cta_hist_words(int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic) {
+size_t cta_hist_words(const gsw_ctx* ctx, int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic) {
   if (n_items <= 0 || n_lists <= 0 || (size_t)g.T * g.NB * 4 > kMaxHistBytes) return 0;
-  return (size_t)n_lists * (size_t)layer_chunks(n_items, dynamic) * (size_t)(g.T * g.NB + 1);
+  return (size_t)n_lists * (size_t)layer_chunks(ctx, n_items, dynamic) * (size_t)(g.T * g.NB + 1);
 }
 
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
                    const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order) {
   if (n_items <= 0 || n_lists <= 0) return 0;
-  const int32_t nchunks = (int32_t)layer_chunks(n_items, dynamic);
-  const bool wl = use_work_list(dynamic, ga, n_items, n_lists);
+  const int32_t nchunks = (int32_t)layer_chunks(ctx, n_items, dynamic);
+  const bool wl = use_work_list(ctx, dynamic, ga, n_items, n_lists);
   const int64_t pairs = (int64_t)nchunks * n_lists, persistent = 148 * 4;
   dim3 grid((unsigned)nchunks, (unsigned)n_lists);
   if (wl) grid = dim3((unsigned)(pairs < persistent ? pairs : persistent), 1u);
@@ -1708,6 +1750,7 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   uint32_t* const st32 = w.status.as<uint32_t>();
   const size_t hist_b = (size_t)g.T * g.NB * 8;
   const int use_hist = hist_b <= kMaxHistBytes;
+  const int ipbs = ctx->ipb_static;
   int rc;
 #define GSW_LAUNCH_SCATTER(KERNEL_, HIST_, CH_)                                                                     \
   do {                                                                                                            \
@@ -1722,10 +1765,16 @@ int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
   if (g.tile_cull != 0) {  // the culling form has no counting pass of its own: shared counters need cta_hist
     const bool h = use_hist && cta_hist != nullptr;
     if (dynamic) GSW_LAUNCH_SCATTER(scatter_cull_kernel<true GSW_COMMA false>, h, cta_hist);
+    else if (wl && ipbs == 256) GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA true GSW_COMMA 256>, h, cta_hist);
+    else if (wl && ipbs == 512) GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA true GSW_COMMA 512>, h, cta_hist);
+    else if (wl && ipbs == 1024) GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA true GSW_COMMA 1024>, h, cta_hist);
     else if (wl) GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA true>, h, cta_hist);
     else GSW_LAUNCH_SCATTER(scatter_cull_kernel<false GSW_COMMA false>, h, cta_hist);
   } else {
     if (dynamic) GSW_LAUNCH_SCATTER(scatter_kernel<true GSW_COMMA false>, use_hist, cta_hist);
+    else if (wl && ipbs == 256) GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA true GSW_COMMA 256>, use_hist, cta_hist);
+    else if (wl && ipbs == 512) GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA true GSW_COMMA 512>, use_hist, cta_hist);
+    else if (wl && ipbs == 1024) GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA true GSW_COMMA 1024>, use_hist, cta_hist);
     else if (wl) GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA true>, use_hist, cta_hist);
     else GSW_LAUNCH_SCATTER(scatter_kernel<false GSW_COMMA false>, use_hist, cta_hist);
   }
@@ -1779,7 +1828,7 @@ int launch_frame_attrs(const gsw_ctx* ctx, int32_t frame, int32_t* radii, int32_
   frame_attrs_kernel<<<(unsigned)((L.N + 255) / 256), 256, 0, s>>>(
       L.N, L.Ns, L.Nm, L.V, frame, L.frame_view, L.slot_orig, L.pos_of, L.g, w.rec.as<float4>(),
       w.rec.as<float4>() + 1, w.rec.as<float4>() + 2, w.rad.as<int32_t>(), w.chunk_mask.as<uint32_t>(), radii,
-      tiles_touched, depth, xy, conic_opacity, rgb);
+      tiles_touched, depth, xy, conic_opacity, rgb, ctx->ipb_static);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
@@ -1791,7 +1840,7 @@ int launch_radii(const gsw_ctx* ctx, int32_t* out_radii, cudaStream_t s) {
   if (L.N <= 0 || L.F <= 0) return 0;
   dim3 grid((unsigned)((L.N + 255) / 256), (unsigned)L.F);
   radii_kernel<<<grid, 256, 0, s>>>(L.N, L.Ns, L.Nm, L.V, L.frame_view, L.slot_orig, L.pos_of, w.rad.as<int32_t>(),
-                                    w.chunk_mask.as<uint32_t>(), out_radii);
+                                    w.chunk_mask.as<uint32_t>(), out_radii, ctx->ipb_static);
   count_launches(1);
   GSW_CUDA(cudaGetLastError());
   return 0;
