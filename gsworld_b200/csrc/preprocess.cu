@@ -205,41 +205,18 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   if (DYN) {
     // ---- rigid transform of a movable Gaussian (gs_utils.py:283-385 order: scale, rotate, translate) ----
     const float* ps = pose_s + la.mov_slot[il] * GSW_POSE_STRIDE;
-    const float kappa = ps[16];
-    const bool has_scale = ps[17] != 0.f;
-    if (has_scale) {
+    if (ps[17] != 0.f) {  // object: positions scaled by kappa
+      const float kappa = ps[16];
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        p[k] = p[k] * kappa;
-        const float u = expf(la.log_scale_raw[3 * il + k]) * kappa;
-        const float ls = logf(u / (1.0f - u));  // inverse_sigmoid, the reference behaviour (gs_utils.py:310)
-        sc[k] = expf(ls);
-      }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 3; ++k) sc[k] = la.scale_act[3 * il + k];
+      for (int k = 0; k < 3; ++k) p[k] = p[k] * kappa;
     }
     float rp[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r) rp[r] = ps[3 * r] * p[0] + ps[3 * r + 1] * p[1] + ps[3 * r + 2] * p[2];
-    const float4 qr = reinterpret_cast<const float4*>(la.quat_raw)[il];
-    const float nrm = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
-    const float bw = qr.x / nrm, bx = qr.y / nrm, by = qr.z / nrm, bz = qr.w / nrm;
-    const float aw = ps[12], ax = ps[13], ay = ps[14], az = ps[15];
-    float ow = aw * bw - ax * bx - ay * by - az * bz;
-    float ox = aw * bx + ax * bw + ay * bz - az * by;
-    float oy = aw * by - ax * bz + ay * bw + az * bx;
-    float oz = aw * bz + ax * by - ay * bx + az * bw;
-    if (ow < 0.f) {
-      ow = -ow; ox = -ox; oy = -oy; oz = -oz;
-    }
-    const float q2[4] = {ow * nrm, ox * nrm, oy * nrm, oz * nrm};
-    const float n2 = sqrtf(q2[0] * q2[0] + q2[1] * q2[1] + q2[2] * q2[2] + q2[3] * q2[3]);
-    const float den = fmaxf(n2, 1e-12f);  // F.normalize eps (gaussian_model.py:47)
-#pragma unroll
-    for (int k = 0; k < 4; ++k) q[k] = q2[k] / den;
 #pragma unroll
     for (int k = 0; k < 3; ++k) p[k] = rp[k] + ps[9 + k];
+    // (scales and the rotation part of the transform follow the early culls below: most movable Gaussians of a frame
+    // end there)
   }
 
   // ---- near-plane cull on view-space depth ----
@@ -274,22 +251,80 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
   J.m[1][0] = 0.f;           J.m[1][1] = focal_y / tz;   J.m[1][2] = -(focal_y * ty) / (tz * tz);
   J.m[2][0] = 0.f;           J.m[2][1] = 0.f;            J.m[2][2] = 0.f;
 
-  // ---- 3D covariance: M = S*R first, so that an upper bound on the screen radius is available early ----
+  // ---- conservative frustum cull (not in the reference; it only skips work whose result is "no tile") ----
+  // trace(cov2D) <= lambda_max(Sigma) * |J|_F^2 * |W|_2^2 and lambda_1 <= trace(cov2D) + 0.92, so the true
+  // radius ceil(3 sqrt(lambda_1)) is <= r_b; if even a splat of radius r_b around (px,py) cannot reach the
+  // tile grid, the exact path below would end in the same empty tile rectangle.  NaNs fail every test.
+  // lambda_max(Sigma) <= trace(Sigma) = sum_k s_k^2 |row_k(R)|^2, and the rows of R (built from a quaternion
+  // normalised to a few ulp) have length 1 to ~1e-6: the scales alone give the bound, before any of the
+  // rotation algebra (quaternion product, R, S R) is spent on a Gaussian that ends here.
   float c3[6];
-  M3 M;
-  float tr_sigma;  // trace of the 3D covariance >= its largest eigenvalue
+  float tr_sigma;  // >= trace of the 3D covariance >= its largest eigenvalue
   if (have_cov) {
 #pragma unroll
     for (int k = 0; k < 6; ++k) c3[k] = ga.cov3d_precomp[6 * big + k];
     tr_sigma = c3[0] + c3[3] + c3[5];
   } else {
-    if (!DYN) {
+    bool raw_scale = false;
+    if (DYN) {
+      const float* ps = pose_s + la.mov_slot[il] * GSW_POSE_STRIDE;
+      if (ps[17] != 0.f) {  // object: scales go through exp -> * kappa -> inverse_sigmoid -> exp (gs_utils.py:310)
+        raw_scale = true;
+        const float kappa = ps[16];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float u = expf(la.log_scale_raw[3 * il + k]) * kappa;
+          const float ls = logf(u / (1.0f - u));  // inverse_sigmoid, the reference behaviour
+          sc[k] = expf(ls);
+        }
+      }
+    }
+    if (!raw_scale) {
       sc[0] = la.scale_act[3 * il];
       sc[1] = la.scale_act[3 * il + 1];
       sc[2] = la.scale_act[3 * il + 2];
+    }
+    const float s0 = g.scale_modifier * sc[0], s1 = g.scale_modifier * sc[1], s2 = g.scale_modifier * sc[2];
+    tr_sigma = (s0 * s0 + s1 * s1 + s2 * s2) * 1.001f;
+  }
+  {
+    const float jf2 = J.m[0][0] * J.m[0][0] + J.m[0][2] * J.m[0][2] + J.m[1][1] * J.m[1][1] + J.m[1][2] * J.m[1][2];
+    const float lam_b = tr_sigma * jf2 * vs.wnorm * 1.02f + 1.0f;
+    const float r_b = 3.0f * sqrtf(lam_b) + 2.0f;
+    if (tr_sigma >= 0.f &&
+        (px + r_b < 0.5f || px - r_b > (float)(g.gx * kTile) + 0.5f || py + r_b < 0.5f ||
+         py - r_b > (float)(g.gy * kTile) + 0.5f)) {
+      rad[item] = 0;
+      return;
+    }
+  }
+
+  // ---- 3D covariance ----
+  if (!have_cov) {
+    if (DYN) {
+      // rotation part of the rigid transform (gs_utils.py:283-385): q = normalize(pose_q * normalize(q_raw) * |q_raw|)
+      const float* ps = pose_s + la.mov_slot[il] * GSW_POSE_STRIDE;
+      const float4 qr = reinterpret_cast<const float4*>(la.quat_raw)[il];
+      const float nrm = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
+      const float bw = qr.x / nrm, bx = qr.y / nrm, by = qr.z / nrm, bz = qr.w / nrm;
+      const float aw = ps[12], ax = ps[13], ay = ps[14], az = ps[15];
+      float ow = aw * bw - ax * bx - ay * by - az * bz;
+      float ox = aw * bx + ax * bw + ay * bz - az * by;
+      float oy = aw * by - ax * bz + ay * bw + az * bx;
+      float oz = aw * bz + ax * by - ay * bx + az * bw;
+      if (ow < 0.f) {
+        ow = -ow; ox = -ox; oy = -oy; oz = -oz;
+      }
+      const float q2[4] = {ow * nrm, ox * nrm, oy * nrm, oz * nrm};
+      const float n2 = sqrtf(q2[0] * q2[0] + q2[1] * q2[1] + q2[2] * q2[2] + q2[3] * q2[3]);
+      const float den = fmaxf(n2, 1e-12f);  // F.normalize eps (gaussian_model.py:47)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) q[k] = q2[k] / den;
+    } else {
       const float4 qq = reinterpret_cast<const float4*>(la.quat_act)[il];
       q[0] = qq.x; q[1] = qq.y; q[2] = qq.z; q[3] = qq.w;
     }
+    M3 M;
     M3 S;
 #pragma unroll
     for (int c = 0; c < 3; ++c)
@@ -310,29 +345,6 @@ __device__ __forceinline__ void preprocess_item(const GaussArrays& ga, const Gau
     R.m[2][1] = 2.f * (y * z + r * x);
     R.m[2][2] = 1.f - 2.f * (x * x + y * y);
     M = mul3(S, R);
-    tr_sigma = 0.f;
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-#pragma unroll
-      for (int rr = 0; rr < 3; ++rr) tr_sigma += M.m[c][rr] * M.m[c][rr];
-  }
-
-  // ---- conservative frustum cull (not in the reference; it only skips work whose result is "no tile") ----
-  // trace(cov2D) <= lambda_max(Sigma) * |J|_F^2 * |W|_2^2 and lambda_1 <= trace(cov2D) + 0.92, so the true
-  // radius ceil(3 sqrt(lambda_1)) is <= r_b; if even a splat of radius r_b around (px,py) cannot reach the
-  // tile grid, the exact path below would end in the same empty tile rectangle.  NaNs fail every test.
-  {
-    const float jf2 = J.m[0][0] * J.m[0][0] + J.m[0][2] * J.m[0][2] + J.m[1][1] * J.m[1][1] + J.m[1][2] * J.m[1][2];
-    const float lam_b = tr_sigma * jf2 * vs.wnorm * 1.02f + 1.0f;
-    const float r_b = 3.0f * sqrtf(lam_b) + 2.0f;
-    if (tr_sigma >= 0.f &&
-        (px + r_b < 0.5f || px - r_b > (float)(g.gx * kTile) + 0.5f || py + r_b < 0.5f ||
-         py - r_b > (float)(g.gy * kTile) + 0.5f)) {
-      rad[item] = 0;
-      return;
-    }
-  }
-  if (!have_cov) {
     const M3 Sig = mul3(tr3(M), M);
     c3[0] = Sig.m[0][0]; c3[1] = Sig.m[0][1]; c3[2] = Sig.m[0][2];
     c3[3] = Sig.m[1][1]; c3[4] = Sig.m[1][2]; c3[5] = Sig.m[2][2];
