@@ -137,3 +137,24 @@ def test_world_fixed_cameras_are_numbered_first(rig):
         b, cb, Db, _ = _render(fresh, False)
         _same(a, b)
         assert Da == Db and 0 < ca["static_chunks_live"] < cb["static_chunks_live"]
+
+
+def test_static_chunk_size_changes_no_byte(rig):
+    """The static layer's chunk (items per work-list entry) is picked per launch from the number of views; every
+    choice must give the same bytes (GSW_IPB_STATIC forces one; read at every launch)."""
+    fx, env, mk = rig
+    for strict in (True, False):
+        ref, _, Dref, _ = _render(mk(strict), False)
+        for ipb in ("256", "512", "1024", "2048"):
+            os.environ["GSW_IPB_STATIC"] = ipb
+            try:
+                w = mk(strict)
+                a, _, Da, _ = _render(w, True)
+                env_state = env._q.copy()
+                b, cb, Db, _ = _render(w, True)  # second launch: kept lists, same chunk size
+            finally:
+                os.environ.pop("GSW_IPB_STATIC", None)
+            assert (env._q == env_state).all()
+            _same(a, ref)
+            _same(b, ref)
+            assert Da == Dref == Db and cb["static_chunks_live"] == 0
