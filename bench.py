@@ -521,6 +521,7 @@ def run_ours(args):
         # "peer_all": the same into every rank's buffer + one device-side barrier per step.  "all": NCCL all-gather;
         # "root": NCCL gather to rank 0; "none": no exchange
         GATHER = os.environ.get("GSW_BENCH_GATHER", "peer")
+        NO_DATA = os.environ.get("GSW_BENCH_XCHG_NO_DATA") == "1"
         build.calls = 0
         xchg = None
         if world > 1 and GATHER in ("peer", "peer_all"):
@@ -559,10 +560,14 @@ def run_ours(args):
                 counter[0] += 1
                 xchg.begin(k, wrap._engine)
                 wrap.obs_out = xchg.local_out(k)  # composite straight into this rank's slot of its own buffer
-                wrap.obs_peers = xchg.destinations(k)
+                # (diagnostic: GSW_BENCH_XCHG_NO_DATA=1 keeps the signals and credits but pushes no frames)
+                wrap.obs_peers = [] if NO_DATA else xchg.destinations(k)
                 # asynchronous legs: the render stream does not wait for the delivery; the host-synchronous e2e leg
                 # waits for its own host copy (it reads the frames right after) but not for the pushes to the policy rank
-                wrap.defer_delivery_join = True if not wrap.sync_each_step else "peers"
+                # (asynchronous legs deliver after the blend: the pushes run beside the next step's kernels, and the
+                # blend carries no completion signals; GSW_BENCH_DELIVER=overlap restores the in-blend delivery)
+                wrap.defer_delivery_join = "peers" if wrap.sync_each_step else (
+                    True if os.environ.get("GSW_BENCH_DELIVER") == "overlap" else "after")
                 out = wrap._render_gsworld()
                 consume(k - 1)  # one step behind, while step k is still being composited
                 xchg.publish(k, wrap._engine)  # after xchg.wait_ready(k), xchg.gathered(k) holds every rank's frames
@@ -587,7 +592,7 @@ def run_ours(args):
         def verify_exchange(env, wrap):
             """Once, before anything is timed: the batch the peer exchange delivers to the policy rank is byte-identical
             to an NCCL all-gather of the same frames (the 2-GPU pytest cannot run on a 1-GPU test box)."""
-            if xchg is None:
+            if xchg is None or NO_DATA:
                 return
             wrap.sync_each_step = False
             ok = True
@@ -627,6 +632,7 @@ def run_ours(args):
             torch.cuda.synchronize(dev)
 
         timed_launches = [0]
+        rank_ms = [0.0]
 
         def timed(env, wrap, steps, warmup, d2h=None):
             for _attempt in range(4):
@@ -681,6 +687,7 @@ def run_ours(args):
             if os.environ.get("GSW_BENCH_DEBUG") and steps > 0:
                 log(f"[rank {rank}] {ms / steps:.3f} ms/step on this rank, host loop {host_ms / steps:.3f} ms/step, "
                     f"D={wrap._engine.last_stats['D']}")
+            rank_ms[0] = ms  # this rank's own device time (the line reports the max over ranks)
             if world > 1:
                 t = torch.tensor([ms], device=dev)
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -702,12 +709,20 @@ def run_ours(args):
             if os.environ.get("GSW_TILE_CULL"):
                 eng.set_tile_culling(os.environ["GSW_TILE_CULL"] == "1")
             if mode == "strict":
-                sampler = ClockSampler(local) if rank == 0 else None
+                sampler = ClockSampler(local)  # every rank samples its own GPU; rank 0 reports them all
                 timed(env, wrap, 0, args.warmup)
-                if sampler is not None:
-                    sampler.start()
+                sampler.start()
                 ms = timed(env, wrap, args.steps, 0)
-                clocks = sampler.stop() if sampler is not None else None
+                clocks = sampler.stop()
+                if world > 1:
+                    every = [None] * world
+                    dist.all_gather_object(every, {"sm_mhz": clocks["sm_mhz"], "reasons": clocks["reasons"],
+                                                   "ms_per_step": rank_ms[0] / max(args.steps, 1)})
+                    clocks["per_rank"] = every
+                    sm_all = [c["sm_mhz"] for c in every if c["sm_mhz"]]
+                    if sm_all:
+                        clocks["sm_mhz_min_over_ranks"] = min(sm_all)
+                    clocks["reasons"] = sorted(set(sum((c["reasons"] for c in every), [])))
                 launches = timed_launches[0]
             else:
                 ms = timed(env, wrap, args.steps, args.warmup)

@@ -706,7 +706,17 @@ int gsw_render_frames(gsw_ctx* c, const gsw_frames_desc* d, gsw_stream stream) {
     }
     return 0;
   };
-  if (deliver && c->wait_value32 != nullptr) {
+  if (deliver && (d->deliver_flags & GSW_DELIVER_AFTER_BLEND)) {
+    // plain blend launch, then everything at once on the delivery streams (which run beside the next step's kernels)
+    if ((rc = launch_blend(c, d->num_views, 0, d->num_frames, c->last.nbins, d->frame_view, c->last.cap, g, d->bg,
+                           nullptr, d->out_rgb_u8, d->out_color, d->out_invdepth, d->out_seg, share, s)))
+      return rc;
+    GSW_CUDA(cudaEventRecord(c->grp_evt[0], s));
+    GSW_CUDA(cudaStreamWaitEvent(c->copy_stream, c->grp_evt[0], 0));
+    if (n_peer > 0) GSW_CUDA(cudaStreamWaitEvent(c->peer_stream, c->grp_evt[0], 0));
+    if ((rc = send_group(0, d->num_frames))) return rc;
+    if ((rc = close_delivery())) return rc;
+  } else if (deliver && c->wait_value32 != nullptr) {
     // ONE blend launch; the frames are cut into groups, the last CTA of a group to finish publishes the launch
     // epoch in the group's flag, and the copy stream waits on that flag (stream memory operation) before it
     // sends the group's uint8 frames to the pinned host buffer and / or the peer GPUs.  Delivery overlaps the compositing of the later

@@ -198,8 +198,9 @@ class Engine:
         else:
             desc.peer_rgb_u8 = None
             desc.num_peer_rgb_u8 = 0
-        # GSW_DELIVER_NO_JOIN (1) / GSW_DELIVER_NO_PEER_JOIN (2, defer_delivery_join="peers")
-        desc.deliver_flags = 2 if defer_delivery_join == "peers" else (1 if defer_delivery_join else 0)
+        # GSW_DELIVER_NO_JOIN (1) / GSW_DELIVER_NO_PEER_JOIN (2, defer_delivery_join="peers") /
+        # GSW_DELIVER_NO_JOIN | GSW_DELIVER_AFTER_BLEND (5, defer_delivery_join="after": asynchronous producers)
+        desc.deliver_flags = {"peers": 2, "after": 5}.get(defer_delivery_join, 1 if defer_delivery_join else 0)
         self._last_inputs = (pose, viewmatrix, projmatrix, campos, tanfov, frame_env, frame_view)
         self._dbg_N = None
         for _attempt in range(4):

@@ -135,6 +135,11 @@ typedef struct gsw_frames_desc {
  * every step then does not sit on the NVLink traffic and the cross-rank flow control behind it; whoever consumes the
  * pushed frames (and whoever overwrites out_rgb_u8) is ordered with gsw_delivery_wait as with GSW_DELIVER_NO_JOIN. */
 #define GSW_DELIVER_NO_PEER_JOIN 2
+/* Deliver AFTER the blend launch instead of group by group while it runs: no completion signals inside the blend
+ * kernel (each of its CTAs otherwise ends with a release operation that waits for its stores: ~12 % of the kernel).
+ * For fully asynchronous producers, where the delivery overlaps the NEXT step's kernels anyway; combine with
+ * GSW_DELIVER_NO_JOIN.  A host that waits for every step wants the default (delivery overlapped with the blend). */
+#define GSW_DELIVER_AFTER_BLEND 4
 
 /* Enqueue transform + rasterization of all frames on `stream`.  Asynchronous.
  * Static-list cache: a leading run of views whose 37 camera words (viewmatrix, projmatrix, campos, tanfov) are bitwise

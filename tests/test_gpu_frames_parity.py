@@ -149,12 +149,13 @@ def test_wrapper_from_ply_config_and_inverse_depth_obs(tmp_path):
         assert d.shape == (2, 48, 48, 1) and d.dtype == torch.float32 and float(d.min()) >= 0.0 and float(d.max()) > 0.0
 
 
-@pytest.mark.parametrize("B,wait_value", [(3, True), (3, False), (11, True)])
+@pytest.mark.parametrize("B,wait_value", [(3, True), (3, False), (11, True), (5, "after")])
 def test_host_delivery_matches_device_output(B, wait_value, monkeypatch):
     """gsw_frames_desc.host_rgb_u8: delivery overlapped with the blend must hand the host exactly the frames the
     plain path leaves on the device.  wait_value=True: one blend launch + in-kernel group flags + a stream memory
     wait on the copy stream (frame counts below and above the 8 groups); False: the fallback, grouped launches
-    with events.  Several steps in a row, so the epoch / counters are reused."""
+    with events; "after": delivery after a plain blend launch, render stream not joined.  Several steps in a row, so
+    the epoch / counters are reused."""
     if not wait_value:
         monkeypatch.setenv("GSW_NO_WAIT_VALUE", "1")  # read by gsw_create
     scene, env, wrap = _make("fr3_umi", "fr3_pnp_box", B, (64, 48), ("006_mustard_bottle",), True)
@@ -167,7 +168,14 @@ def test_host_delivery_matches_device_output(B, wait_value, monkeypatch):
         want = {c: obs["sensor_data"][c]["rgb"].clone() for c in env.cameras}
         pinned.zero_()
         wrap.obs_host = pinned
+        if wait_value == "after":  # GSW_DELIVER_AFTER_BLEND | GSW_DELIVER_NO_JOIN: one copy after a plain blend launch
+            wrap.defer_delivery_join = "after"  # (deferred joins need a caller-owned output buffer)
+            wrap.obs_out = torch.zeros((len(env.cameras), B, 64, 48, 3), dtype=torch.uint8, device="cuda:0")
         out = wrap._render_gsworld()
+        if wait_value == "after":
+            wrap._engine.delivery_wait()  # the render stream did not wait for the copy
+            wrap.defer_delivery_join = False
+            wrap.obs_out = None
         torch.cuda.current_stream().synchronize()
         for i, c in enumerate(env.cameras):
             assert torch.equal(out[c].cpu(), want[c].cpu())

@@ -35,13 +35,13 @@ def _worker(rank, world, port):
         for roots in (None, [0]):
             xchg = PeerObservationExchange((len(cams), B, H, W, 3), dev, roots=roots)
             root = roots is None or rank in roots
-            for mode in ("joined", "deferred"):
+            for mode in ("joined", "deferred", "after"):
                 for k in range(5):  # both buffers are reused
                     xchg.begin(k, wrap._engine)
                     wrap.obs_out = xchg.local_out(k)
                     wrap.obs_peers = xchg.destinations(k)
-                    wrap.defer_delivery_join = mode == "deferred"
-                    wrap.sync_each_step = mode != "deferred"
+                    wrap.defer_delivery_join = {"joined": False, "deferred": True, "after": "after"}[mode]
+                    wrap.sync_each_step = mode == "joined"
                     obs = wrap.step(None)[0]
                     xchg.publish(k, wrap._engine)
                     mine = torch.stack([obs["sensor_data"][c]["rgb"] for c in cams])  # (C,B,H,W,3)
