@@ -759,7 +759,9 @@ def run_ours(args):
             results[mode] = dict(ms=ms, fps=world * F * args.steps / (ms * 1e-3), stages=acc, stats=st, V=Vn,
                                  D_shared_static=d_shared, pairs=pairs, chunks_live=cnts["static_chunks_live"],
                                  vis_s=cnts["visible_static"], vis_d=cnts["visible_dynamic"],
-                                 chunks_total=Vn * ((int((scene_cpu._semantics.reshape(-1) < 0).sum()) + 2047) // 2048))
+                                 chunk_items=cnts["static_chunk_items"],
+                                 chunks_total=Vn * (-(-int((scene_cpu._semantics.reshape(-1) < 0).sum()) //
+                                                      max(cnts["static_chunk_items"], 1))))
             if mode == "strict" and not args.quick and not lean and not os.environ.get("GSW_TILE_CULL"):
                 # the same step with the reference's full tile lists (exact tile culling off); same pixels
                 eng.set_tile_culling(False)
@@ -910,7 +912,8 @@ def run_ours(args):
                                 "views": results["per_env"]["V"],
                                 "stages_ms": {k: round(v, 4) for k, v in results["per_env"]["stages"].items()},
                                 "counts": dict(results["per_env"]["stats"], static_chunks_live=results["per_env"].get("chunks_live"),
-                                               static_chunks_total=results["per_env"].get("chunks_total"))},
+                                               static_chunks_total=results["per_env"].get("chunks_total"),
+                                               static_chunk_items=results["per_env"].get("chunk_items"))},
             "cpu_baseline": cpu,
             "gpu_reference_restated": gpu_ref,
         }

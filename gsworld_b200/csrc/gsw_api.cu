@@ -932,6 +932,7 @@ int gsw_profile_counters(gsw_ctx* c, int64_t* out, int n) {
     out[3] = c->h_status[16];  // visible static Gaussian-views (records written by the static preprocess)
     out[4] = c->h_status[17];  // visible movable Gaussian-frames
   }
+  if (n >= 6) out[5] = c->ipb_static;  // items per chunk of the static layer in that launch
   return GSW_OK;
 }
 

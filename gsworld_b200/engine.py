@@ -290,10 +290,10 @@ class Engine:
 
     def counters(self):
         """Work counters of the last launch: blend pair evaluations, entries staged."""
-        buf = (C.c_int64 * 5)()
-        _lib.check(self.lib.gsw_profile_counters(self._h, buf, 5))
+        buf = (C.c_int64 * 6)()
+        _lib.check(self.lib.gsw_profile_counters(self._h, buf, 6))
         return {"blend_pairs": int(buf[0]), "blend_staged": int(buf[1]), "static_chunks_live": int(buf[2]),
-                "visible_static": int(buf[3]), "visible_dynamic": int(buf[4])}
+                "visible_static": int(buf[3]), "visible_dynamic": int(buf[4]), "static_chunk_items": int(buf[5])}
 
     def kernel_launches(self) -> int:
         return int(self.lib.gsw_kernel_launches())

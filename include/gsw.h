@@ -240,9 +240,11 @@ int gsw_profile_read(gsw_ctx* ctx, float* stage_ms, int n);
 /* Work counters of the last launch (waits for it): out[0] = (splat, pixel) pair evaluations of the blend kernel, i.e.
  * how often the per-pixel alpha / compositing arithmetic ran (after tile culling, the per-warp footprint cull and
  * early termination; the reference evaluates every entry of a tile's list on all 256 pixels until the tile is done),
- * out[1] = tile entries the blend staged; with n >= 3, out[2] = (view, 2048-item chunk) pairs of the static layer that
+ * out[1] = tile entries the blend staged; with n >= 3, out[2] = (view, chunk) pairs of the static layer that
  * survived chunk-level frustum culling (0 when the work list is not in use); with n >= 5, out[3] / out[4] = visible
- * static Gaussian-views / movable Gaussian-frames (records the preprocess wrote).  n >= 2.  Feeds bench.py's rooflines. */
+ * static Gaussian-views / movable Gaussian-frames (records the preprocess wrote); with n >= 6, out[5] = items per
+ * chunk of the static layer in that launch (256 ... 2048, chosen from the number of views).  Views whose static lists
+ * were kept from the previous launch contribute nothing to out[2] / out[3].  n >= 2.  Feeds bench.py's rooflines. */
 int gsw_profile_counters(gsw_ctx* ctx, int64_t* out, int n);
 
 /* ---- parity taps for the LAST gsw_render_frames / gsw_rasterize_forward launch (device outputs) ---- */
