@@ -141,7 +141,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   if ((rc = w.merge_cnt.reserve((size_t)mc * 4)) || (rc = w.merge_off.reserve((size_t)mc * 4))) return rc;
   if ((rc = w.keys.reserve((size_t)cap * 8)) || (rc = w.splats.reserve((size_t)cap * sizeof(Splat)))) return rc;
   if ((rc = w.status.reserve(kStatusBytes))) return rc;
-  ctx->ipb_static = pick_static_ipb(stat, Ns, V);
+  ctx->ipb_static = pick_static_ipb(stat, Ns, V, g.T * g.NB);
   const size_t chs = cta_hist_words(ctx, Ns, V, g, false), chd = dyn ? cta_hist_words(ctx, Nm, F, g, true) : 0;
   if ((rc = w.cta_hist.reserve((chs + chd) * 4 + 16))) return rc;
   uint32_t* const ch_s = chs ? w.cta_hist.as<uint32_t>() : nullptr;

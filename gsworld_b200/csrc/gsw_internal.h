@@ -278,7 +278,7 @@ int launch_cache_prefix(const gsw_ctx* ctx, int32_t V, cudaStream_t s);
 size_t cta_hist_words(const gsw_ctx* ctx, int64_t n_items, int32_t n_lists, const FrameGeom& g, bool dynamic);
 // chunks of a layer (one preprocess / scatter CTA round each); the static layer's chunk size is ctx->ipb_static
 int64_t layer_chunks(const gsw_ctx* ctx, int64_t n_items, bool dynamic);
-int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists);
+int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists, int32_t bins_per_list);
 int launch_scatter(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int64_t n_items, int32_t n_lists,
                    int32_t list_base, int64_t item_base, const FrameGeom& g, int64_t cap, const uint32_t* cta_hist,
                    const uint32_t* chunk_mask, cudaStream_t s, const uint32_t* order = nullptr);

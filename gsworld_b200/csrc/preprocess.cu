@@ -1625,7 +1625,7 @@ bool use_work_list(const gsw_ctx* ctx, bool dynamic, const GaussArrays& ga, int6
 // small chunks only add histogram flushes and per-chunk count rows (per-env cameras 2.95 ms at 2048, 3.40 ms at 256).
 // So: the largest chunk that still yields ~7000 (view, chunk) pairs, 256 at least; always 2048 without a work list
 // (the staged and the plain forms are only instantiated for it).
-int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
+int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists, int32_t bins_per_list) {
   if (ga.bounds == nullptr || n_lists > 65535 || getenv("GSW_NO_WORK_LIST") != nullptr ||
       getenv("GSW_WL_TMA") != nullptr)
     return kIpbStatic;
@@ -1633,10 +1633,17 @@ int pick_static_ipb(const GaussArrays& ga, int64_t n_items, int32_t n_lists) {
     const int v = atoi(e);
     if ((v == 256 || v == 512 || v == 1024 || v == 2048) && (n_items + v - 1) / v <= 65535) return v;
   }
-  for (int ipb = kIpbStatic; ipb > 256; ipb >>= 1)
-    if ((int64_t)n_lists * ((n_items + ipb - 1) / ipb) >= 7000) return ipb;
   int ipb = 256;
-  while (ipb < kIpbStatic && (n_items + ipb - 1) / ipb > 65535) ipb <<= 1;  // 16-bit chunk field of the work list
+  for (int c = kIpbStatic; c > 256; c >>= 1)
+    if ((int64_t)n_lists * ((n_items + c - 1) / c) >= 7000) {
+      ipb = c;
+      break;
+    }
+  // 16-bit chunk field of the work list; and every chunk keeps a row of per-bin counts for the scatter pass (cta_hist):
+  // small chunks on a large tile grid must not turn that into gigabytes
+  while (ipb < kIpbStatic && ((n_items + ipb - 1) / ipb > 65535 ||
+                              (int64_t)n_lists * ((n_items + ipb - 1) / ipb) * (bins_per_list + 1) * 4 > ((int64_t)64 << 20)))
+    ipb <<= 1;
   return ipb;
 }
 
