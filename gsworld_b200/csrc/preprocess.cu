@@ -169,8 +169,8 @@ __device__ __forceinline__ float sh_channel(int deg, float x, float y, float z, 
 
 // Items per CTA round ("chunk") of each layer: 256 threads x chunk / 256 consecutive items of one list.  kIpbStatic is
 // the static layer's LARGEST chunk (and the only one of the forms without a work list); with a work list the launch
-// picks 256 ... kIpbStatic (pick_static_ipb).  The dynamic layer's is fixed (512 measured slower at 64 envs: preprocess
-// 0.29 -> 0.36 ms, and no faster at 8 envs once the static chunk is small).
+// picks 256 ... kIpbStatic (pick_static_ipb).  The dynamic layer's is fixed (measured at 64 envs, step in ms: 512 items
+// 1.10, 1024 items 1.02, 2048 items 1.01, 4096 items 1.05; 512 is no faster at 8 envs once the static chunk is small).
 #ifndef GSW_IPB_DYN
 #define GSW_IPB_DYN 2048
 #endif
