@@ -241,14 +241,29 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
       ((rc = w.dyn_cost.reserve((size_t)n_dyn_ctas * 4)) || (rc = w.dyn_order.reserve((size_t)n_dyn_ctas * 4))))
     return rc;
   const uint32_t* prev_order = (use_order && ctx->dyn_order_n == n_dyn_ctas) ? w.dyn_order.as<uint32_t>() : nullptr;
-  bool have_order = false;
+  bool have_order = false, order_aside = false;
   if (dyn && Nm > 0) {
     if ((rc = launch_preprocess(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, view, proj, campos, tanfov, frame_env,
                                 frame_view, pose, num_slots, ch_d, mask_d, &kept_d, s, prev_order,
                                 use_order ? w.dyn_cost.as<uint32_t>() : nullptr)))
       return rc;
     if (use_order && kept_d) {
-      if ((rc = launch_order_chunks(w.dyn_cost.as<uint32_t>(), n_dyn_ctas, w.dyn_order.as<uint32_t>(), s))) return rc;
+      // The order is first needed by the scatter.  In a small launch, where the step is a chain of launch gaps, the
+      // kernel that makes it runs beside the bin scan instead of before it (8 envs x 2 cameras: 0.360 -> 0.350 ms per
+      // step); in a large one that measured slower (64 envs: 1.008 -> 1.027 ms), so there it stays in line.
+      static const bool inline_order = getenv("GSW_ORDER_INLINE") != nullptr;  // tuning aid
+      cudaStream_t os = (ctx->side2_stream != nullptr && ctx->order_evt[1] != nullptr && !inline_order &&
+                         !ctx->profile && n_dyn_ctas <= 1024)
+                            ? ctx->side2_stream : s;
+      if (os != s) {
+        GSW_CUDA(cudaEventRecord(ctx->order_evt[0], s));
+        GSW_CUDA(cudaStreamWaitEvent(os, ctx->order_evt[0], 0));
+      }
+      if ((rc = launch_order_chunks(w.dyn_cost.as<uint32_t>(), n_dyn_ctas, w.dyn_order.as<uint32_t>(), os))) return rc;
+      if (os != s) {
+        GSW_CUDA(cudaEventRecord(ctx->order_evt[1], os));
+        order_aside = true;
+      }
       ctx->dyn_order_n = n_dyn_ctas;
       have_order = true;
     } else {
@@ -263,6 +278,7 @@ int run_pipeline(gsw_ctx* ctx, const GaussArrays& stat, int64_t N, int64_t Ns, c
   mark(3);
   if ((rc = fork())) return rc;
   if ((rc = launch_scatter(ctx, false, stat, Ns, V, 0, 0, g, cap, kept_s ? ch_s : nullptr, mask_s, ss))) return rc;
+  if (order_aside) GSW_CUDA(cudaStreamWaitEvent(s, ctx->order_evt[1], 0));
   if (dyn && Nm > 0)
     if ((rc = launch_scatter(ctx, true, *dyn, Nm, F, V, (int64_t)V * Ns, g, cap, kept_d ? ch_d : nullptr, mask_d, s,
                              have_order ? w.dyn_order.as<uint32_t>() : nullptr)))
@@ -374,6 +390,7 @@ int gsw_create(int device, gsw_ctx** out) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->side2_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->fork_evt, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->join_evt, cudaEventDisableTiming);
+  for (int k = 0; k < 2 && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->order_evt[k], cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_error("gsw_create: %s", cudaGetErrorString(e));
     delete c;
@@ -406,6 +423,8 @@ int gsw_destroy(gsw_ctx* c) {
   if (c->peer_stream) cudaStreamDestroy(c->peer_stream);
   if (c->fork_evt) cudaEventDestroy(c->fork_evt);
   if (c->join_evt) cudaEventDestroy(c->join_evt);
+  for (int k = 0; k < 2; ++k)
+    if (c->order_evt[k]) cudaEventDestroy(c->order_evt[k]);
   if (c->side_stream) cudaStreamDestroy(c->side_stream);
   if (c->side2_stream) cudaStreamDestroy(c->side2_stream);
   for (int k = 0; k <= kNumStages; ++k)

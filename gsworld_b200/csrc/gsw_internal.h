@@ -241,6 +241,7 @@ struct gsw_ctx {
   cudaStream_t side_stream = nullptr;
   cudaStream_t side2_stream = nullptr;  // the dynamic lists' sort forks onto it while side_stream carries the static chain
   cudaEvent_t fork_evt = nullptr, join_evt = nullptr;
+  cudaEvent_t order_evt[2] = {};  // the dispatch-order kernel of the dynamic layer runs beside the bin scan
   int64_t launches = 0;
   // static-list cache: cache_on = this launch runs the cache logic (scene layers with a chunk work list); cache_ok = and
   // nothing the kept lists depend on has changed on the host side since the previous launch (cache_sig)
